@@ -1,0 +1,184 @@
+/* vr.h -- C ABI of libvr: headless B200 (sm_100a) implementation of VolumeRenderer's many-light hot path.
+ *
+ * This library stands where basalt's Vulkan compute dispatch stands in the reference (chrylt/VolumeRenderer).
+ * There is no plugin API in the reference; the boundary is the descriptor-set contract of
+ * shaders/common_bindings.h:1-34 plus the commands VolumeApp::drawFrame records around the two compute dispatches
+ * (src/main.cpp:712-837). Each entry point below cites the reference mechanism it replaces (paths relative to the
+ * reference checkout). Plain C types only; the caller owns every host pointer, the context owns all device memory.
+ *
+ * Threading: one thread per context at a time (the reference is single-threaded with one queue). Calls enqueue work
+ * on the context's CUDA stream and return; vr_sync and the vr_read_* calls block. No exception crosses this ABI:
+ * every function returns a vr_status and vr_last_error() gives the text (the reference throws std::runtime_error
+ * and exits, src/main.cpp:1217-1227).
+ */
+#ifndef VR_H
+#define VR_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum vr_status {
+    VR_OK = 0,
+    VR_E_ARG = 1,      /* invalid argument (incl. values the reference UI allows but its shaders cannot survive) */
+    VR_E_CUDA = 2,     /* a CUDA runtime call failed */
+    VR_E_BADGRID = 3,  /* buffer is not a NanoVDB float grid */
+    VR_E_CAPACITY = 4, /* maxLights exceeds the light-buffer capacity */
+    VR_E_STATE = 5     /* call order: no grid / no image yet */
+} vr_status;
+
+/* Algorithm enum, order of src/main.cpp:65-68 (selects the *_compute_color / *_light_gen pipeline pair, :192-224). */
+typedef enum vr_algo { VR_ALGO_BEAM = 0, VR_ALGO_RAY = 1, VR_ALGO_POINT = 2, VR_ALGO_SPHERE = 3, VR_ALGO_PATH = 4 } vr_algo;
+
+/* Which light-generation shader body: light_gen.comp (the one the app loads for Beam/Ray/Point/Sphere,
+ * src/main.cpp:47-57; resets ray origin and t on scatter, light_gen.comp:91-92) or the never-loaded
+ * {point,ray,sphere}_light_gen.comp bodies (no reset). PATH always uses path_light_gen.comp (empty main). */
+typedef enum vr_lightgen_variant { VR_LG_RESET_ORIGIN = 0, VR_LG_KEEP_ORIGIN = 1 } vr_lightgen_variant;
+
+/* binding 5: the std140 UBO of shaders/common_bindings.h:19-34, host mirror src/main.cpp:83-98. 96 bytes, bit-for-bit. */
+typedef struct vr_ubo {
+    uint32_t frameCount;          /* @0  */
+    uint32_t _pad0;               /* @4  */
+    uint32_t framebufferDim[2];   /* @8  */
+    float cameraPos[3];           /* @16 */
+    float fov;                    /* @28 */
+    float photonInitialIntensity; /* @32 */
+    float scatteringProbability;  /* @36 */
+    float absorptionCoefficient;  /* @40 */
+    uint32_t maxLights;           /* @44 */
+    float rayMaxDistance;         /* @48 */
+    float rayMarchingStepSize;    /* @52 */
+    uint32_t _pad1[2];            /* @56 */
+    float lightSourceWorldPos[3]; /* @64 */
+    float beamRadius;             /* @76 */
+    float lightRayStepSize;       /* @80 */
+    float radiusFalloff;          /* @84 (unused by every shader) */
+    uint32_t _pad2[2];            /* @88 */
+} vr_ubo;
+
+/* binding 3: struct RayLight (shaders/common_structures.h:4-8) in std430: stride 32 B. */
+typedef struct vr_ray_light {
+    float positionFrom[3]; /* @0  */
+    float _pad0;           /* @12 */
+    float positionTo[3];   /* @16 */
+    float intensity;       /* @28 */
+} vr_ray_light;
+
+/* pixel rectangle for image-tiled multi-GPU rendering (no counterpart in the reference: it dispatches the whole
+ * image, src/main.cpp:835-837) */
+typedef struct vr_tile {
+    uint32_t x0, y0, w, h;
+} vr_tile;
+
+/* work counters of the last vr_dispatch_compute_color */
+typedef struct vr_counters {
+    uint64_t S_ref;        /* camera samples inside the root bbox */
+    uint64_t S_eff;        /* those with density != 0 (the ones that reach the light loop) */
+    uint64_t E;            /* point/sphere evaluations performed = S_eff * (expanded light list length) */
+    uint64_t eval_lights;  /* length of the expanded light list (= lightCount for point/sphere, sum n_i for ray/beam) */
+    uint64_t light_count;  /* lightCount used for the 1/lightCount normalisation */
+} vr_counters;
+
+/* CUDA-event timings (ms) of the passes of the last frame / dispatches */
+typedef struct vr_timings {
+    float light_gen_ms;
+    float march_ms;    /* camera-ray march: count + scan + fill */
+    float prepare_ms;  /* light list expansion */
+    float eval_ms;     /* the sample x light kernel (dominant) */
+    float resolve_ms;  /* per-pixel reduction + progressive average */
+    float total_ms;
+} vr_timings;
+
+typedef struct vr_ctx vr_ctx;
+
+/* ---- device / context: replaces basalt::Instance/Device creation (src/main.cpp:265-270) */
+int vr_create(int cuda_device, vr_ctx** out);
+int vr_destroy(vr_ctx* ctx);
+const char* vr_last_error(const vr_ctx* ctx); /* ctx may be NULL: error of a failed vr_create on this thread */
+
+/* ---- binding 2: the NanoVDB buffer, device-local storage buffer filled through a staging copy
+ * (src/main.cpp:1191-1212). Copies `size` bytes; validates magic, grid type FLOAT and 32-byte size granularity.
+ * Grids >= 4 GiB are accepted (64-bit addressing) but cannot be parity-checked against 32-bit GLSL addressing. */
+int vr_set_grid(vr_ctx* ctx, const void* nanovdb_bytes, uint64_t size);
+
+/* ---- binding 0: rgba8 storage image sized to the swapchain extent, recreated on resize (src/main.cpp:338-378, :950).
+ * Allocates the rgba8 image plus a float4 accumulator and resets the progressive state (frameCount = 0, :937). */
+int vr_resize(vr_ctx* ctx, uint32_t width, uint32_t height);
+
+/* ---- binding 5: uniformBuffer->updateBuffer(&uboData) every frame (src/main.cpp:715). */
+int vr_set_params(vr_ctx* ctx, const vr_ubo* params);
+int vr_get_params(const vr_ctx* ctx, vr_ubo* params);
+/* defaults of src/main.cpp:546-559 for a width x height image */
+void vr_default_params(vr_ubo* params, uint32_t width, uint32_t height);
+
+/* ---- bindings 3/4: light buffer + counter (src/main.cpp:380-398). The reference allocates 100000*28 B, i.e. 87500
+ * lights at the 32 B GPU stride; capacity is explicit here. */
+int vr_set_max_lights_capacity(vr_ctx* ctx, uint32_t n);
+/* vkCmdFillBuffer(counter, 0, 8, 0) (src/main.cpp:722-728) */
+int vr_reset_lights(vr_ctx* ctx);
+/* upload a light list (tests; broadcast in multi-GPU runs). count <= capacity. */
+int vr_write_lights(vr_ctx* ctx, const vr_ray_light* lights, uint32_t count);
+
+/* ---- image clear to (0,0,0,1) when frameCount == 1 (src/main.cpp:731-808) */
+int vr_clear_image(vr_ctx* ctx);
+
+/* ---- vkCmdBindPipeline(lightGen[algo]) + vkCmdDispatch(1,1,1) (src/main.cpp:811-814). Work-groups are 4x4x1
+ * photons (shaders/light_gen.comp:7); gx,gy,gz are the dispatch dimensions (reference: 1,1,1). Lights are appended in
+ * the canonical photon-major order (one legal serialisation of the shader's atomicAdd race). */
+int vr_dispatch_light_gen(vr_ctx* ctx, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant);
+
+/* ---- vkCmdBindPipeline(computeColor[algo]) + vkCmdDispatch(ceil(w/16), ceil(h/16), 1) (src/main.cpp:832-837).
+ * tile == NULL renders the whole image; otherwise only that pixel rectangle is updated. Stream order replaces the
+ * compute->compute barrier of :817-829. */
+int vr_dispatch_compute_color(vr_ctx* ctx, vr_algo algo, const vr_tile* tile_or_null);
+
+/* ---- the compute section of VolumeApp::drawFrame (src/main.cpp:712-837): frameCount++, UBO update, counter reset,
+ * clear when frameCount == 1, light generation (gx,gy,gz as set by vr_set_light_gen_groups, default 1,1,1), gather. */
+int vr_set_light_gen_groups(vr_ctx* ctx, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant);
+int vr_render_frame(vr_ctx* ctx, vr_algo algo, const vr_tile* tile_or_null);
+/* frameCount = 0 (algorithm change :657, "Refresh" :695-698, resize :937) */
+int vr_reset_accumulation(vr_ctx* ctx);
+
+/* ---- read-back (the reference never reads back; the image goes to the swapchain blit) */
+int vr_sync(vr_ctx* ctx);
+int vr_read_lights(vr_ctx* ctx, vr_ray_light* out, uint32_t capacity, uint32_t* count);
+int vr_read_light_counter(vr_ctx* ctx, uint32_t counter[2], uint64_t* total_emitted);
+int vr_read_image_rgba8(vr_ctx* ctx, uint8_t* out);        /* width*height*4 bytes */
+int vr_read_accum_f32(vr_ctx* ctx, float* out);            /* width*height*4 floats (RGBA, linear) */
+int vr_read_frame_color_f32(vr_ctx* ctx, float* out);      /* width*height floats: the last frame's clamp()ed colour, R=G=B */
+int vr_write_accum_f32(vr_ctx* ctx, const float* in, uint32_t frame_count); /* restore a snapshot (resume) */
+int vr_write_image_rgba8(vr_ctx* ctx, const uint8_t* in);
+int vr_get_counters(vr_ctx* ctx, vr_counters* out);
+int vr_get_timings(vr_ctx* ctx, vr_timings* out);
+/* device pointers for zero-copy interop (NCCL): float4 accumulator, rgba8 image, frame colour; CUDA stream */
+int vr_get_device_buffers(vr_ctx* ctx, void** accum_f32, void** image_rgba8, void** frame_color_f32, void** stream);
+/* per-row count of non-zero-density camera samples for the current params (tile balancing across GPUs) */
+int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
+/* 0: re-march camera rays every frame (default, what the reference does); 1: reuse the camera samples while grid,
+ * camera, image size and march parameters are unchanged (progressive accumulation) */
+int vr_set_march_cache(vr_ctx* ctx, int enabled);
+
+/* ---- CPU_test/main.cpp:25-43, 89-126 as a kernel: fixed camera (0,250,-800) in index space, fov 45, 1200 unit
+ * steps, density[j*w+i] = sum of grid values. */
+int vr_cpu_test_render(vr_ctx* ctx, uint32_t width, uint32_t height, float* density_out);
+
+/* ---- host-side NanoVDB float-grid writer (fixtures for configs without a .vdb asset; replaces the
+ * openvdb -> nanovdb::tools::createNanoGrid step of src/main.cpp:1157-1193 for synthetic volumes).
+ * Output is a raw grid buffer in the layout PNanoVDB reads; free with vr_grid_free. */
+int vr_grid_build_cloud(int32_t n, uint32_t seed, double voxel_size, const double translation[3], int nthreads,
+                        void** bytes_out, uint64_t* size_out);
+int vr_grid_build_fog_sphere(double radius_vox, const int32_t center[3], double voxel_size, const double translation[3],
+                             int nthreads, void** bytes_out, uint64_t* size_out);
+/* dense[(i*dims[1]+j)*dims[2]+k] at index (origin+ijk); values equal to background are inactive */
+int vr_grid_build_dense(const float* dense, const int32_t dims[3], const int32_t origin[3], float background,
+                        double voxel_size, const double translation[3], int nthreads, void** bytes_out,
+                        uint64_t* size_out);
+void vr_grid_free(void* bytes);
+
+/* library facts */
+const char* vr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VR_H */
