@@ -175,6 +175,14 @@ int vr_grid_build_dense(const float* dense, const int32_t dims[3], const int32_t
                         uint64_t* size_out);
 void vr_grid_free(void* bytes);
 
+/* ---- measurement helpers: CUDA events on the context's stream (torch.cuda.Event only sees torch's stream) */
+int vr_timer_start(vr_ctx* ctx);
+int vr_timer_stop(vr_ctx* ctx, float* elapsed_ms); /* records, synchronises and returns the device time since start */
+/* microbenchmarks that measure this GPU's non-tensor ceilings for the roofline (FP32 FMA issue, MUFU.RCP):
+ * kind 0: dependent FFMA chains -> TFLOP/s (2 flop per FFMA); kind 1: MUFU.RCP -> 1e12 op/s;
+ * kind 2: the point-light inner loop with operands in registers (3 FADD, FMUL, 2 FFMA, FSETP, MUFU.RCP, FFMA) -> 1e12 eval/s */
+int vr_ubench(vr_ctx* ctx, int kind, double* result);
+
 /* library facts */
 const char* vr_version(void);
 

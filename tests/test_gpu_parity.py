@@ -1,0 +1,207 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json): light lists bit-exact in count and canonical order; radiance max relative error <= 1e-3 and
+RMSE <= 1e-4 on the linear float frame colour (|ref| < 1e-6 -> absolute error); rgba8 accumulation within 1 LSB.
+Work counters (S_ref, S_eff) and everything on the exact-arithmetic paths (march, path mode, CPU_test) bit-exact.
+"""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-3   # max relative error on linear frame colour (north_star)
+RMSE_TOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def renderer(vr):
+    r = vr.VolumeRenderer(0)
+    yield r
+    r.close()
+
+
+def _setup(r, grid, W, H, **ubo):
+    r.set_grid(grid)
+    r.resize(W, H)
+    r.ubo = r.default_ubo()
+    return r.update_ubo(**ubo)
+
+
+@pytest.mark.parametrize("n,groups,max_lights,frame", [(64, (1, 1, 1), 1000, 1), (64, (8, 1, 1), 100, 1),
+                                                       (64, (4, 2, 2), 50, 3), (128, (27, 1, 1), 1000, 1),
+                                                       (128, (16, 1, 1), 37, 9)])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_light_gen_bit_exact(renderer, pyoracle, oracle, cloud, n, groups, max_lights, frame, variant):
+    grid = cloud(n)
+    _setup(renderer, grid, 64, 64, maxLights=max_lights, frameCount=frame)
+    renderer.reset_lights()
+    renderer.dispatch_light_gen("point", groups, variant)
+    lights, count, emitted = renderer.read_lights()
+    u = pyoracle.default_ubo(64, 64, frameCount=frame, maxLights=max_lights)
+    ol, oc, oem, _ = oracle.light_gen(grid, u, groups, variant)
+    assert (count, emitted) == (oc, oem)
+    assert lights.tobytes() == ol.tobytes()
+
+
+def test_path_light_gen_is_empty(renderer, cloud):
+    _setup(renderer, cloud(64), 32, 32, frameCount=1)
+    renderer.reset_lights()
+    renderer.dispatch_light_gen("path", (4, 1, 1))
+    _, count, emitted = renderer.read_lights()
+    assert count == 0 and emitted == 0
+
+
+@pytest.mark.parametrize("algo", ["point", "sphere", "ray", "beam"])
+@pytest.mark.parametrize("n,W,H,max_lights,groups", [(64, 96, 64, 64, (4, 1, 1)), (128, 160, 90, 200, (8, 1, 1))])
+def test_gather_parity(renderer, pyoracle, oracle, cloud, algo, n, W, H, max_lights, groups):
+    grid = cloud(n)
+    u = _setup(renderer, grid, W, H, maxLights=max_lights, frameCount=1)
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=max_lights)
+    ol, oc, _, _ = oracle.light_gen(grid, ou, groups, 0)
+    renderer.write_lights(ol)
+    renderer.clear_image()
+    renderer.dispatch_compute_color(algo)
+    fc = renderer.read_frame_color()
+    cnt = renderer.counters()
+    ofc, ocnt = oracle.gather(grid, ou, algo, ol, skip_zero=True)
+    assert cnt["S_ref"] == ocnt["S_ref"] and cnt["S_eff"] == ocnt["S_eff"]
+    assert cnt["E"] == ocnt["E"]
+    rel, rmse = rel_err(fc, ofc)
+    assert rel <= REL_TOL and rmse <= RMSE_TOL, (rel, rmse)
+    assert ofc.max() > 0.01  # the scene is not black
+
+
+def test_path_mode_bit_exact(renderer, pyoracle, oracle, cloud):
+    grid = cloud(64)
+    W, H = 96, 64
+    for frame in (1, 2, 5):
+        _setup(renderer, grid, W, H, frameCount=frame)
+        renderer.clear_image()
+        renderer.dispatch_compute_color("path")
+        fc = renderer.read_frame_color()
+        ou = pyoracle.default_ubo(W, H, frameCount=frame)
+        ofc, ocnt = oracle.gather(grid, ou, "path", np.zeros(0, pyoracle.LIGHT_DTYPE))
+        cnt = renderer.counters()
+        assert (cnt["S_ref"], cnt["S_eff"]) == (ocnt["S_ref"], ocnt["S_eff"])
+        assert np.array_equal(fc, ofc)
+
+
+def test_progressive_accumulation(renderer, pyoracle, oracle, cloud):
+    """draw_frame x4 (new lights every frame): float accumulator and rgba8 image vs the oracle's running averages."""
+    grid = cloud(64)
+    W, H = 64, 48
+    _setup(renderer, grid, W, H, maxLights=40)
+    renderer.set_light_gen_groups(4, 1, 1)
+    renderer.reset_accumulation()
+    acc = np.zeros((H, W, 4), np.float32)
+    acc[..., 3] = 1.0
+    img8 = np.zeros((H, W, 4), np.uint8)
+    img8[..., 3] = 255
+    for frame in range(1, 5):
+        renderer.draw_frame("point")
+        ou = pyoracle.default_ubo(W, H, frameCount=frame, maxLights=40)
+        ol, oc, _, _ = oracle.light_gen(grid, ou, (4, 1, 1), 0)
+        gl, gc, _ = renderer.read_lights()
+        assert gc == oc and gl.tobytes() == ol.tobytes()
+        ofc, _ = oracle.gather(grid, ou, "point", ol)
+        oracle.accumulate(ofc, frame, acc, img8)
+        rel, rmse = rel_err(renderer.read_accum()[..., 0], acc[..., 0])
+        assert rel <= REL_TOL and rmse <= RMSE_TOL, (frame, rel, rmse)
+        d8 = np.abs(renderer.read_image_rgba8().astype(int) - img8.astype(int)).max()
+        assert d8 <= 1, (frame, d8)
+    assert renderer.ubo.frameCount == 4
+    assert (renderer.read_accum()[..., 3] == 1.0).all() and (renderer.read_image_rgba8()[..., 3] == 255).all()
+
+
+def test_tiles_equal_full_frame(renderer, pyoracle, oracle, cloud):
+    grid = cloud(64)
+    W, H = 100, 70  # not a multiple of the 16x8 block
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=30)
+    ol, _, _, _ = oracle.light_gen(grid, ou, (4, 1, 1), 0)
+    _setup(renderer, grid, W, H, maxLights=30, frameCount=1)
+    renderer.write_lights(ol)
+    renderer.clear_image()
+    renderer.dispatch_compute_color("ray")
+    full = renderer.read_frame_color()
+    renderer.clear_image()
+    for tile in [(0, 0, 37, 70), (37, 0, 63, 33), (37, 33, 63, 37)]:
+        renderer.dispatch_compute_color("ray", tile)
+    tiled = renderer.read_frame_color()
+    assert np.array_equal(full, tiled)
+
+
+def test_cpu_test_bit_exact(renderer, vr, oracle):
+    """Config 1: CPU_test's density ray-march, fog sphere in front of its fixed camera."""
+    grid = vr.build_fog_sphere_grid(32.0, center=(0, 250, -200))
+    renderer.set_grid(grid)
+    d = renderer.cpu_test_render(256, 256)
+    od, _ = oracle.cpu_test(grid, 256, 256, nthreads=8)
+    assert od.max() > 10
+    assert np.array_equal(d, od)
+
+
+def test_edge_cases(renderer, vr, pyoracle, oracle, cloud):
+    grid = cloud(64)
+    W, H = 48, 32
+    # lightCount == 0 -> 0/0 -> frame colour defined as 0
+    _setup(renderer, grid, W, H, frameCount=1)
+    renderer.write_lights(np.zeros(0, pyoracle.LIGHT_DTYPE))
+    renderer.clear_image()
+    renderer.dispatch_compute_color("point")
+    assert (renderer.read_frame_color() == 0).all()
+    # camera looking away from the volume: no pixel hits the bbox
+    _setup(renderer, grid, W, H, frameCount=1, cameraPos=(0.0, 20.0, 200.0))
+    ou = pyoracle.default_ubo(W, H, frameCount=1, cameraPos=(0.0, 20.0, 200.0))
+    ol, _, _, _ = oracle.light_gen(grid, ou, (2, 1, 1), 0)
+    renderer.write_lights(ol)
+    renderer.dispatch_compute_color("point")
+    assert renderer.counters()["S_ref"] == 0 and (renderer.read_frame_color() == 0).all()
+    # camera inside the volume (tmin clamps to 0)
+    _setup(renderer, grid, W, H, frameCount=1, cameraPos=(0.0, 20.0, 0.0))
+    ou = pyoracle.default_ubo(W, H, frameCount=1, cameraPos=(0.0, 20.0, 0.0))
+    renderer.write_lights(ol)
+    renderer.clear_image()
+    renderer.dispatch_compute_color("sphere")
+    ofc, ocnt = oracle.gather(grid, ou, "sphere", ol)
+    rel, rmse = rel_err(renderer.read_frame_color(), ofc)
+    assert renderer.counters()["S_eff"] == ocnt["S_eff"] and rel <= REL_TOL and rmse <= RMSE_TOL
+    # a light closer than the 1e-4 guard to a sample contributes 0, not infinity
+    _setup(renderer, grid, W, H, frameCount=1)
+    near = np.zeros(1, pyoracle.LIGHT_DTYPE)
+    near["to"][0] = (0.0, 20.0, 0.0)
+    near["from"][0] = (0.0, 19.0, 0.0)
+    near["intensity"][0] = 50.0
+    renderer.write_lights(near)
+    renderer.clear_image()
+    renderer.dispatch_compute_color("point")
+    ou = pyoracle.default_ubo(W, H, frameCount=1)
+    ofc, _ = oracle.gather(grid, ou, "point", near)
+    rel, rmse = rel_err(renderer.read_frame_color(), ofc)
+    assert rel <= REL_TOL and rmse <= RMSE_TOL
+
+
+def test_argument_errors(renderer, vr, cloud):
+    grid = cloud(64)
+    _setup(renderer, grid, 32, 32)
+    with pytest.raises(vr.VrError) as e:
+        renderer.update_ubo(rayMarchingStepSize=0.0)
+    assert e.value.code == 1
+    with pytest.raises(vr.VrError) as e:
+        renderer.update_ubo(maxLights=1000000)  # the reference UI allows it and overruns its buffer
+    assert e.value.code == 4
+    renderer.update_ubo(lightRayStepSize=0.0)
+    with pytest.raises(vr.VrError):
+        renderer.dispatch_compute_color("ray")
+    renderer.update_ubo(lightRayStepSize=0.3)
+    with pytest.raises(vr.VrError) as e:
+        renderer.set_grid(np.zeros(4096, np.uint8))
+    assert e.value.code == 3
+    with pytest.raises(vr.VrError):
+        renderer.dispatch_compute_color("point", (0, 0, 64, 64))
+    r2 = vr.VolumeRenderer(0)
+    with pytest.raises(vr.VrError) as e:
+        r2.dispatch_light_gen("point")
+    assert e.value.code == 5
+    r2.close()

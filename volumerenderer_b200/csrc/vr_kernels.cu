@@ -1,0 +1,749 @@
+// vr_kernels.cu -- hand-written sm_100a kernels for VolumeRenderer's many-light hot path.
+//
+// Pass structure of one frame (replaces the two Vulkan dispatches of src/main.cpp:811-837):
+//
+//   light generation   k_lightgen<COUNT> -> scan -> k_lightgen<EMIT>      shaders/light_gen.comp:9-100
+//   light expansion    k_prepare_* (ray/beam sub-points pre-expanded)     shaders/ray_compute_color.comp:13-20
+//   camera march       k_march<COUNT> -> scan -> k_march<FILL>            shaders/point_compute_color.comp:20-94
+//   evaluation (HOT)   k_eval<POINT|SPHERE>: samples x lights             shaders/common_functions.h:182-201
+//   resolve            k_resolve: ordered per-pixel sum, clamp, average   shaders/point_compute_color.comp:97-105
+//
+// The reference nests the light loop inside each pixel's ray march. Because the pixel colour is linear in the
+// per-sample light sums (C = sum_s w_s * L(p_s), w_s = T*val*step, and T does not depend on the lights), the march
+// is split from the light loop: the march emits the samples with val != 0 (skipping val == 0 is exact: the shader
+// multiplies the light sum by val), the evaluation kernel is then a perfectly load-balanced all-pairs kernel
+// (samples x lights) with the light list staged through shared memory by TMA bulk copies, and the resolve pass adds
+// each pixel's terms in march order (the reference's summation order).
+//
+// Exactness: light generation, the march (sample positions, weights, T cut) and path mode use individually rounded
+// FP32 ops in the shader's order -> bit-identical with the CPU checker. The evaluation kernel may contract to FMA
+// and uses MUFU.RCP; its results are within a few ulp per term (tolerance 1e-3 relative on the pixel, BASELINE.json).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vr_kernels.cuh"
+
+namespace {
+
+// =====================================================================================================
+// light generation
+// =====================================================================================================
+// One photon per thread; photon index p = ((z*Ny)+y)*Nx + x is the canonical order.
+// COUNT: number of scatter events of photon p. EMIT: same walk, lights stored at base + offsets[p] + j while the
+// index is below maxLights (the shader's `if (index < maxLights)`); previousPosition only advances on a store.
+template <bool EMIT>
+__global__ void __launch_bounds__(64) k_lightgen(VrGridDev g, vr_ubo u, int keep_origin, uint32_t nx, uint32_t ny,
+                                                  uint32_t nz, uint32_t* __restrict__ counts,
+                                                  const unsigned long long* __restrict__ offsets,
+                                                  const unsigned long long* __restrict__ total,
+                                                  vr_ray_light* __restrict__ lights, const VrLightCounter* counter) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nphot = (uint64_t)nx * ny * nz;
+    if (p >= nphot) return;
+    const uint32_t x = (uint32_t)(p % nx), y = (uint32_t)((p / nx) % ny), z = (uint32_t)(p / ((uint64_t)nx * ny));
+    VrSeed seed = {x * u.frameCount, y * u.frameCount, z * u.frameCount};
+    const vr_f3 originW = vr_make3(u.lightSourceWorldPos[0], u.lightSourceWorldPos[1], u.lightSourceWorldPos[2]);
+    const float r1 = vr_randf_inc(seed);
+    const float r2 = vr_randf_inc(seed);
+    const vr_f3 dirW = vr_random_dir(r1, r2);
+    vr_f3 o = vr_world_to_index(g, originW);
+    vr_f3 d = vr_normalize3(vr_world_to_index_dir(g, dirW));
+    float tmin = 0.0f, tmax = u.rayMaxDistance;
+    const bool hit = vr_intersect_aabb(o, d, g, tmin, tmax);
+    const float step = u.rayMarchingStepSize;
+    float T = 1.0f, t = tmin, I = u.photonInitialIntensity;
+    vr_f3 cur = vr_add3(o, vr_scale3(d, tmin));
+    vr_f3 prev = originW;
+    uint32_t n = 0;
+    // the shader's atomicAdd continues from the counter's current value (0 after the per-frame reset)
+    unsigned long long slot = EMIT ? (unsigned long long)counter->lightCount + offsets[p] : 0ull;
+    VrAcc acc;
+    vr_acc_init(acc);
+    while (hit && t < tmax && T > 0.001f && I > 0.01f) {
+        const int32_t i = (int32_t)vr_floor(cur.x), j = (int32_t)vr_floor(cur.y), k = (int32_t)vr_floor(cur.z);
+        if (vr_in_bbox(g, i, j, k)) {
+            const float val = vr_lookup(g, acc, i, j, k);
+            if (val > 0.0f) {
+                const float att = vr_exp(vr_mul(vr_mul(-val, u.absorptionCoefficient), step));
+                I = vr_mul(I, att);
+                T = vr_mul(T, att);
+                const float roll = vr_randf_inc(seed);
+                if (roll < u.scatteringProbability) {
+                    const float q1 = vr_randf_inc(seed);
+                    const float q2 = vr_randf_inc(seed);
+                    const vr_f3 nd = vr_random_dir(q1, q2);
+                    if (EMIT) {
+                        const vr_f3 w = vr_index_to_world(g, cur);
+                        if (slot < (unsigned long long)u.maxLights) {
+                            vr_ray_light L;
+                            L.positionFrom[0] = prev.x, L.positionFrom[1] = prev.y, L.positionFrom[2] = prev.z;
+                            L._pad0 = 0.0f;
+                            L.positionTo[0] = w.x, L.positionTo[1] = w.y, L.positionTo[2] = w.z;
+                            L.intensity = I;
+                            float4* dst = reinterpret_cast<float4*>(lights + slot);
+                            dst[0] = make_float4(L.positionFrom[0], L.positionFrom[1], L.positionFrom[2], 0.0f);
+                            dst[1] = make_float4(L.positionTo[0], L.positionTo[1], L.positionTo[2], L.intensity);
+                            prev = w;
+                        }
+                        slot++;
+                    }
+                    n++;
+                    d = nd;
+                    if (!keep_origin) {  // light_gen.comp:91-92
+                        o = cur;
+                        t = 0.0f;
+                    }
+                }
+            }
+        }
+        t = vr_add(t, step);
+        cur = vr_add3(o, vr_scale3(d, t));
+    }
+    if (!EMIT) counts[p] = n;
+}
+// Counter value after the dispatch: every scatter did atomicAdd(lightCount, 1); any index >= maxLights stored
+// `lightCount = maxLights` (light_gen.comp:85-87). Net effect: min(old + total, maxLights) once anything was emitted.
+__global__ void k_lightgen_finish(vr_ubo u, const unsigned long long* __restrict__ total, VrLightCounter* counter) {
+    const unsigned long long t = *total;
+    counter->totalEmitted += t;
+    if (t == 0) return;
+    const unsigned long long after = (unsigned long long)counter->lightCount + t;
+    counter->lightCount = (uint32_t)(after < (unsigned long long)u.maxLights ? after : (unsigned long long)u.maxLights);
+}
+
+// =====================================================================================================
+// exclusive scan u32 -> u64
+// =====================================================================================================
+__device__ __forceinline__ unsigned long long warp_incl_scan(unsigned long long v) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned long long t = __shfl_up_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) >= o) v += t;
+    }
+    return v;
+}
+// block-wide exclusive scan of one value per thread (1024 threads); returns exclusive prefix, total in *block_total
+__device__ __forceinline__ unsigned long long block_excl_scan(unsigned long long v, unsigned long long* block_total) {
+    __shared__ unsigned long long wsum[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const unsigned long long incl = warp_incl_scan(v);
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        unsigned long long w = (lane < (int)(blockDim.x >> 5)) ? wsum[lane] : 0ull;
+        const unsigned long long wi = warp_incl_scan(w);
+        wsum[lane] = wi - w;
+        if (lane == 31) *block_total = wi;
+    }
+    __syncthreads();
+    const unsigned long long r = wsum[wid] + incl - v;
+    __syncthreads();
+    return r;
+}
+__global__ void __launch_bounds__(1024) k_scan_blocks(const uint32_t* __restrict__ in, unsigned long long* __restrict__ out,
+                                                       unsigned long long* __restrict__ tmp, uint64_t n) {
+    __shared__ unsigned long long total;
+    const uint64_t base = ((uint64_t)blockIdx.x * 1024 + threadIdx.x) * 4;
+    uint32_t v[4];
+#pragma unroll
+    for (int q = 0; q < 4; q++) v[q] = (base + q < n) ? in[base + q] : 0u;
+    const unsigned long long s = (unsigned long long)v[0] + v[1] + v[2] + v[3];
+    unsigned long long ex = block_excl_scan(s, &total);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        if (base + q < n) out[base + q] = ex;
+        ex += v[q];
+    }
+    if (threadIdx.x == 0) tmp[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(1024) k_scan_tops(unsigned long long* __restrict__ tmp, uint64_t nblocks,
+                                                     unsigned long long* __restrict__ total_out) {
+    __shared__ unsigned long long total;
+    unsigned long long carry = 0;
+    for (uint64_t b0 = 0; b0 < nblocks; b0 += 1024) {
+        const uint64_t idx = b0 + threadIdx.x;
+        const unsigned long long v = idx < nblocks ? tmp[idx] : 0ull;
+        const unsigned long long ex = block_excl_scan(v, &total);
+        if (idx < nblocks) tmp[idx] = carry + ex;
+        carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_out = carry;
+}
+__global__ void __launch_bounds__(1024) k_scan_add(unsigned long long* __restrict__ out, const unsigned long long* __restrict__ tmp,
+                                                    uint64_t n) {
+    const uint64_t base = ((uint64_t)blockIdx.x * 1024 + threadIdx.x) * 4;
+    const unsigned long long add = tmp[blockIdx.x];
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+        if (base + q < n) out[base + q] += add;
+}
+
+// =====================================================================================================
+// light list expansion
+// =====================================================================================================
+#define VR_INV_4PI 0.07957747154594767f
+// point: positionTo (point_compute_color.comp:12); sphere: positionFrom (sphere_compute_color.comp:12)
+__global__ void k_prepare_simple(const vr_ray_light* __restrict__ lights, const VrLightCounter* __restrict__ counter,
+                                 int use_from, VrEvalLight* __restrict__ out, uint32_t capacity) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t n = counter->lightCount;
+    if (n > capacity) n = capacity;
+    if (i >= n) return;
+    const float4* src = reinterpret_cast<const float4*>(lights + i);
+    const float4 a = src[0], b = src[1];
+    VrEvalLight e;
+    if (use_from) e.x = a.x, e.y = a.y, e.z = a.z;
+    else e.x = b.x, e.y = b.y, e.z = b.z;
+    e.i4pi = b.w * VR_INV_4PI;
+    reinterpret_cast<float4*>(out)[i] = make_float4(e.x, e.y, e.z, e.i4pi);
+}
+// amountOfSteps = uint(length(to - from) / lightRayStepSize)   (ray_compute_color.comp:13-15)
+__device__ __forceinline__ uint32_t ray_steps(const float4 a, const float4 b, float lrs, vr_f3* dir) {
+    const vr_f3 rl = vr_make3(vr_sub(b.x, a.x), vr_sub(b.y, a.y), vr_sub(b.z, a.z));
+    *dir = vr_normalize3(rl);
+    const float q = vr_div(vr_length3(rl), lrs);
+    // float -> uint: NaN and negatives give 0; saturate well below the buffer limits
+    return (q >= 1.0f) ? (q < 4.0e9f ? (uint32_t)q : 0xFFFFFFFFu) : 0u;
+}
+__global__ void k_prepare_count_steps(const vr_ray_light* __restrict__ lights, const VrLightCounter* __restrict__ counter,
+                                      float lrs, uint32_t* __restrict__ steps, uint32_t capacity) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= capacity) return;
+    uint32_t n = counter->lightCount;
+    if (n > capacity) n = capacity;
+    uint32_t s = 0;
+    if (i < n) {
+        const float4* src = reinterpret_cast<const float4*>(lights + i);
+        vr_f3 dir;
+        s = ray_steps(src[0], src[1], lrs, &dir);
+    }
+    steps[i] = s;
+}
+// sub-point s of light i: from + (float(s) * lrs) * dir, intensity I / float(n)   (ray_compute_color.comp:16-20)
+__global__ void k_prepare_expand(const vr_ray_light* __restrict__ lights, const VrLightCounter* __restrict__ counter,
+                                 float lrs, const unsigned long long* __restrict__ offsets, VrEvalLight* __restrict__ out,
+                                 uint32_t capacity, uint64_t out_capacity) {
+    const uint32_t i = blockIdx.x;  // one block per light
+    uint32_t n = counter->lightCount;
+    if (n > capacity) n = capacity;
+    if (i >= n) return;
+    const float4* src = reinterpret_cast<const float4*>(lights + i);
+    const float4 a = src[0], b = src[1];
+    vr_f3 dir;
+    const uint32_t steps = ray_steps(a, b, lrs, &dir);
+    if (steps == 0) return;
+    const float pointIntensity = vr_div(b.w, vr_u2f(steps));
+    const float i4pi = pointIntensity * VR_INV_4PI;
+    const unsigned long long off = offsets[i];
+    for (uint32_t s = threadIdx.x; s < steps; s += blockDim.x) {
+        if (off + s >= out_capacity) break;
+        const float f = vr_mul(vr_i2f((int32_t)s), lrs);
+        reinterpret_cast<float4*>(out)[off + s] =
+            make_float4(vr_add(a.x, vr_mul(f, dir.x)), vr_add(a.y, vr_mul(f, dir.y)), vr_add(a.z, vr_mul(f, dir.z)), i4pi);
+    }
+}
+
+// =====================================================================================================
+// camera-ray march
+// =====================================================================================================
+// 128 threads = 16x8 pixels; each warp is an 8x4 pixel packet (neighbouring rays walk the same leaves, so the
+// 4-byte value loads of a warp fall into a handful of 128-byte lines). One thread per pixel.
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
+                                                uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
+                                                VrSample* __restrict__ samples, VrWorkCounters* wc) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const bool active = lx < tile.w && ly < tile.h;
+    uint32_t n = 0, sref = 0;
+    if (active) {
+        const uint32_t px = tile.x0 + lx, py = tile.y0 + ly;
+        const uint64_t pix = (uint64_t)ly * tile.w + lx;
+        const VrCamRay r = vr_camera_ray(g, u, tan_scale, px, py);
+        if (r.hit && r.tmax > 0.0f) {
+            const float step = u.rayMarchingStepSize;
+            float t = vr_max(r.tmin, 0.0f);
+            float T = 1.0f;
+            VrAcc acc;
+            vr_acc_init(acc);
+            float4* dst = FILL ? reinterpret_cast<float4*>(samples + offsets[pix]) : nullptr;
+            while (t < r.tmax && T > 0.001f) {
+                const vr_f3 p = vr_add3(r.o, vr_scale3(r.d, t));
+                const int32_t i = (int32_t)vr_floor(p.x), j = (int32_t)vr_floor(p.y), k = (int32_t)vr_floor(p.z);
+                if (vr_in_bbox(g, i, j, k)) {
+                    const float val = vr_lookup(g, acc, i, j, k);
+                    sref++;
+                    if (val != 0.0f) {
+                        if (FILL) {
+                            const vr_f3 pw = vr_index_to_world(g, p);
+                            dst[n] = make_float4(pw.x, pw.y, pw.z, vr_mul(vr_mul(T, val), step));
+                        }
+                        n++;
+                        T = vr_mul(T, vr_exp(vr_mul(vr_mul(-val, u.absorptionCoefficient), step)));
+                    }
+                }
+                t = vr_add(t, step);
+            }
+        }
+        if (!FILL) counts[pix] = n;
+    }
+    if (!FILL && wc) {
+        unsigned long long a = sref, b = n;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&wc->S_ref, a);
+            atomicAdd(&wc->S_eff, b);
+        }
+    }
+}
+
+// =====================================================================================================
+// evaluation: samples x lights  (the hot kernel)
+// =====================================================================================================
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+constexpr int EVAL_THREADS = 256;
+constexpr int EVAL_TILE = 1024;  // lights per shared-memory stage (16 KB)
+
+// Each thread keeps S samples in registers and walks the light list in list order with ONE accumulator per sample
+// (the reference's summation order, point_compute_color.comp:11-13). The light list is streamed through a
+// two-stage shared-memory ring filled by TMA bulk copies; every LDS.128 of a light is a warp-wide broadcast and is
+// amortised over the S samples of the thread.
+template <bool SPHERE, int S>
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                        const VrEvalLight* __restrict__ lights, uint64_t nlights, float radius,
+                                                        float* __restrict__ out) {
+    __shared__ __align__(128) float4 stage[2][EVAL_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    const uint64_t ntiles = (nlights + EVAL_TILE - 1) / EVAL_TILE;
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && ntiles > 0) {
+        const uint32_t cnt = (uint32_t)(nlights < EVAL_TILE ? nlights : EVAL_TILE);
+        mbar_expect_tx(&bar[0], cnt * 16u);
+        tma_bulk_g2s(&stage[0][0], lights, cnt * 16u, &bar[0]);
+    }
+    float sx[S], sy[S], sz[S], sw[S], acc[S];
+#pragma unroll
+    for (int j = 0; j < S; j++) {
+        const uint64_t idx = base + (uint64_t)j * EVAL_THREADS + tid;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (idx < nsamples) s = __ldg(reinterpret_cast<const float4*>(samples) + idx);
+        sx[j] = s.x, sy[j] = s.y, sz[j] = s.z, sw[j] = s.w, acc[j] = 0.0f;
+    }
+    for (uint64_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = (uint32_t)(tl & 1);
+        if (tid == 0 && tl + 1 < ntiles) {  // prefetch the next tile into the other stage (freed by the barrier below)
+            const uint64_t first = (tl + 1) * EVAL_TILE;
+            const uint32_t cnt = (uint32_t)((nlights - first) < EVAL_TILE ? (nlights - first) : EVAL_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 16u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], lights + first, cnt * 16u, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
+        const uint64_t first = tl * EVAL_TILE;
+        const int cnt = (int)((nlights - first) < EVAL_TILE ? (nlights - first) : EVAL_TILE);
+        const float4* __restrict__ L = stage[buf];
+#pragma unroll 4
+        for (int l = 0; l < cnt; l++) {
+            const float4 q = L[l];
+#pragma unroll
+            for (int j = 0; j < S; j++) {
+                if (SPHERE) {
+                    // getClosestPointOnSphere + getPointLightContribution (common_functions.h:182-201), same op order:
+                    // cur = O + normalize(p - O) * R ; Lv = cur - p
+                    const float vx = sx[j] - q.x, vy = sy[j] - q.y, vz = sz[j] - q.z;
+                    const float l2 = __fadd_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy)), __fmul_rn(vz, vz));
+                    const float inv = rsqrt_approx(l2);
+                    const float cx = __fadd_rn(q.x, __fmul_rn(__fmul_rn(vx, inv), radius));
+                    const float cy = __fadd_rn(q.y, __fmul_rn(__fmul_rn(vy, inv), radius));
+                    const float cz = __fadd_rn(q.z, __fmul_rn(__fmul_rn(vz, inv), radius));
+                    const float dx = cx - sx[j], dy = cy - sy[j], dz = cz - sz[j];
+                    const float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+                    const float r = rcp_approx(d2);
+                    acc[j] = (d2 < 0.0001f) ? acc[j] : fmaf(q.w, r, acc[j]);
+                } else {
+                    const float dx = q.x - sx[j], dy = q.y - sy[j], dz = q.z - sz[j];
+                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float r = rcp_approx(d2);
+                    acc[j] = (d2 < 0.0001f) ? acc[j] : fmaf(q.w, r, acc[j]);
+                }
+            }
+        }
+        __syncthreads();  // everyone is done with stage[buf] before it is refilled two iterations later
+    }
+#pragma unroll
+    for (int j = 0; j < S; j++) {
+        const uint64_t idx = base + (uint64_t)j * EVAL_THREADS + tid;
+        if (idx < nsamples) out[idx] = sw[j] * acc[j];
+    }
+}
+
+// =====================================================================================================
+// resolve
+// =====================================================================================================
+// round-half-even UNORM8 store of a [0,1] value (Vulkan rgba8 conversion)
+__device__ __forceinline__ unsigned char to_unorm8(float v) {
+    v = vr_clamp(v, 0.0f, 1.0f);
+    if (v != v) v = 0.0f;
+    return (unsigned char)__float2int_rn(vr_mul(v, 255.0f));
+}
+// progressive average of point_compute_color.comp:99-105 on the float accumulator and on the rgba8 image
+__device__ __forceinline__ void accumulate_pixel(float fc, float nm1, float nn, float4* accum, uchar4* rgba8, uint64_t gp) {
+    const float4 prev = accum[gp];
+    float4 nw;
+    nw.x = vr_div(vr_add(vr_mul(prev.x, nm1), fc), nn);
+    nw.y = vr_div(vr_add(vr_mul(prev.y, nm1), fc), nn);
+    nw.z = vr_div(vr_add(vr_mul(prev.z, nm1), fc), nn);
+    nw.w = 1.0f;
+    accum[gp] = nw;
+    const uchar4 p8 = rgba8[gp];
+    uchar4 n8;
+    n8.x = to_unorm8(vr_div(vr_add(vr_mul(vr_div(vr_u2f(p8.x), 255.0f), nm1), fc), nn));
+    n8.y = to_unorm8(vr_div(vr_add(vr_mul(vr_div(vr_u2f(p8.y), 255.0f), nm1), fc), nn));
+    n8.z = to_unorm8(vr_div(vr_add(vr_mul(vr_div(vr_u2f(p8.z), 255.0f), nm1), fc), nn));
+    n8.w = 255;
+    rgba8[gp] = n8;
+}
+__global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const uint32_t* __restrict__ counts,
+                                                  const unsigned long long* __restrict__ offsets, const float* __restrict__ contrib,
+                                                  const VrLightCounter* __restrict__ counter, float* __restrict__ frame_color,
+                                                  float4* __restrict__ accum, uchar4* __restrict__ rgba8) {
+    const uint64_t pix = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= (uint64_t)tile.w * tile.h) return;
+    const uint32_t lx = (uint32_t)(pix % tile.w), ly = (uint32_t)(pix / tile.w);
+    const uint64_t gp = (uint64_t)(tile.y0 + ly) * u.framebufferDim[0] + (tile.x0 + lx);
+    const uint32_t n = counts[pix];
+    const float* c = contrib + offsets[pix];
+    float finalColor = 0.0f;
+    for (uint32_t s = 0; s < n; s++) finalColor = vr_add(finalColor, c[s]);  // finalColor += dC, in march order
+    float fc = vr_div(finalColor, vr_u2f(counter->lightCount));
+    fc = vr_clamp(fc, 0.0f, 1.0f);
+    if (fc != fc) fc = 0.0f;  // lightCount == 0 -> 0/0; a NaN stores as 0 (Appendix B)
+    frame_color[gp] = fc;
+    const float total = vr_u2f(u.frameCount);  // float totalInvocations = frameCount * 1
+    accumulate_pixel(fc, vr_sub(total, 1.0f), total, accum, rgba8, gp);
+}
+
+// =====================================================================================================
+// path mode (shaders/path_compute_color.comp), one pixel per thread, exact op order
+// =====================================================================================================
+__global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, float* __restrict__ frame_color,
+                                               float4* __restrict__ accum, uchar4* __restrict__ rgba8, VrWorkCounters* wc) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const bool active = lx < tile.w && ly < tile.h;
+    uint32_t sref = 0, seff = 0;
+    if (active) {
+        const uint32_t px = tile.x0 + lx, py = tile.y0 + ly;
+        VrSeed seed = {px * u.frameCount, py * u.frameCount, 0u};
+        const VrCamRay r = vr_camera_ray(g, u, tan_scale, px, py);
+        const float step = u.rayMarchingStepSize;
+        const float T = 1.0f;  // never updated by the shader
+        float t = r.tmin;
+        vr_f3 o = r.o, d = r.d;
+        vr_f3 cur = vr_add3(o, vr_scale3(d, r.tmin));
+        const vr_f3 ls = vr_world_to_index(g, vr_make3(u.lightSourceWorldPos[0], u.lightSourceWorldPos[1], u.lightSourceWorldPos[2]));
+        const float start = vr_div(u.photonInitialIntensity, 10000.0f);
+        float finalColor = 0.0f;
+        VrAcc acc, acc2;
+        vr_acc_init(acc);
+        vr_acc_init(acc2);
+        while (r.hit && t < r.tmax && T > 0.001f && u.photonInitialIntensity > 0.01f) {
+            const int32_t i = (int32_t)vr_floor(cur.x), j = (int32_t)vr_floor(cur.y), k = (int32_t)vr_floor(cur.z);
+            if (vr_in_bbox(g, i, j, k)) {
+                const float val = vr_lookup(g, acc, i, j, k);
+                sref++;
+                if (val > 0.0f) {
+                    seff++;
+                    const float roll = vr_randf_inc(seed);
+                    if (roll < u.scatteringProbability) {
+                        const float q1 = vr_randf_inc(seed);
+                        const float q2 = vr_randf_inc(seed);
+                        d = vr_random_dir(q1, q2);
+                        o = cur;
+                        t = 0.0f;
+                    }
+                    // computeLightContribution(currentPosLocal, photonInitialIntensity), path_compute_color.comp:9-31
+                    const vr_f3 rl = vr_sub3(ls, cur);
+                    const vr_f3 rd = vr_normalize3(rl);
+                    const float q = vr_div(vr_length3(rl), step);
+                    const uint32_t steps = (q >= 1.0f) ? (q < 4.0e9f ? (uint32_t)q : 0xFFFFFFFFu) : 0u;
+                    float light = start;
+                    if (steps > 0) {
+                        // the loop body reads the same voxel every iteration (:20): hoist the lookup, keep the multiplies
+                        const vr_f3 c2 = vr_add3(ls, vr_scale3(rd, step));
+                        const float v1 = vr_lookup(g, acc2, (int32_t)vr_floor(c2.x), (int32_t)vr_floor(c2.y), (int32_t)vr_floor(c2.z));
+                        const float a = vr_exp(vr_mul(vr_mul(-v1, u.absorptionCoefficient), step));
+                        if (a == 1.0f) {
+                            // x * 1 == x: nothing to do
+                        } else {
+                            for (uint32_t s = 0; s < steps; s++) {
+                                light = vr_mul(light, a);
+                                if (light == 0.0f) break;  // 0 * a stays 0 (a is finite and non-negative)
+                            }
+                        }
+                    }
+                    finalColor = vr_add(finalColor, vr_mul(vr_mul(vr_mul(T, val), step), light));
+                }
+            }
+            t = vr_add(t, step);
+            cur = vr_add3(o, vr_scale3(d, t));
+        }
+        float fc = vr_clamp(finalColor, 0.0f, 1.0f);
+        if (fc != fc) fc = 0.0f;
+        const uint64_t gp = (uint64_t)py * u.framebufferDim[0] + px;
+        frame_color[gp] = fc;
+        // (previousColor * (contributionCount - 1) + frameColor) / contributionCount with uint contributionCount
+        accumulate_pixel(fc, vr_u2f(u.frameCount - 1u), vr_u2f(u.frameCount), accum, rgba8, gp);
+    }
+    if (wc) {
+        unsigned long long a = sref, b = seff;
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o2);
+            b += __shfl_xor_sync(0xffffffffu, b, o2);
+        }
+        if (lane == 0) {
+            atomicAdd(&wc->S_ref, a);
+            atomicAdd(&wc->S_eff, b);
+        }
+    }
+}
+
+// =====================================================================================================
+// CPU_test/main.cpp:25-43, 89-126
+// =====================================================================================================
+__global__ void __launch_bounds__(128) k_cpu_test(VrGridDev g, uint32_t w, uint32_t h, float aspect, float scale, float* __restrict__ density) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t i = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const uint32_t j = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    if (i >= w || j >= h) return;
+    // float x = (2 * (i + 0.5) / width - 1) * aspectRatio * scale;   (double arithmetic, narrowed)
+    const double xd = __dmul_rn(__dmul_rn(__dsub_rn(__ddiv_rn(__dmul_rn(2.0, __dadd_rn((double)(int)i, 0.5)), (double)(int)w), 1.0), (double)aspect), (double)scale);
+    const double yd = __dmul_rn(__dsub_rn(1.0, __ddiv_rn(__dmul_rn(2.0, __dadd_rn((double)(int)j, 0.5)), (double)(int)h)), (double)scale);
+    const float x = (float)xd, y = (float)yd;
+    // glm::normalize(v) = v * inversesqrt(dot(v, v))
+    const float inv = vr_div(1.0f, vr_sqrt(vr_add(vr_add(vr_mul(x, x), vr_mul(y, y)), 1.0f)));
+    const float dx = vr_mul(x, inv), dy = vr_mul(y, inv), dz = vr_mul(1.0f, inv);
+    VrAcc acc;
+    vr_acc_init(acc);
+    float t = 0.0f, dens = 0.0f;
+    while (t < 1200.0f) {
+        const float px = vr_add(0.0f, vr_mul(t, dx)), py = vr_add(250.0f, vr_mul(t, dy)), pz = vr_add(-800.0f, vr_mul(t, dz));
+        const float v = vr_lookup(g, acc, (int32_t)vr_floor(px), (int32_t)vr_floor(py), (int32_t)vr_floor(pz));
+        dens = vr_add(dens, vr_mul(v, 1.0f));
+        t = vr_add(t, 1.0f);
+    }
+    density[(uint64_t)j * w + i] = dens;
+}
+
+__global__ void k_clear(float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    accum[p] = make_float4(0.f, 0.f, 0.f, 1.f);  // vkCmdClearColorImage (0,0,0,1), src/main.cpp:760
+    rgba8[p] = make_uchar4(0, 0, 0, 255);
+    frame_color[p] = 0.0f;
+}
+__global__ void __launch_bounds__(256) k_row_sums(const uint32_t* __restrict__ counts, uint32_t w, unsigned long long* __restrict__ rows) {
+    __shared__ unsigned long long part[8];
+    unsigned long long s = 0;
+    for (uint32_t x = threadIdx.x; x < w; x += blockDim.x) s += counts[(uint64_t)blockIdx.x * w + x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (int q = 0; q < 8; q++) t += part[q];
+        rows[blockIdx.x] = t;
+    }
+}
+
+// =====================================================================================================
+// microbenchmarks: what the FP32 / MUFU pipes of this GPU sustain (roofline denominators)
+// =====================================================================================================
+template <int KIND>
+__global__ void __launch_bounds__(256) k_ubench(float* sink, int iters) {
+    float a[8], s = 1.0f + threadIdx.x * 1e-7f, c = 0.5f + blockIdx.x * 1e-7f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) a[j] = threadIdx.x * 0.001f + j;
+    if (KIND == 0) {
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) a[j] = fmaf(a[j], s, c);
+        }
+    } else if (KIND == 1) {
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) a[j] = rcp_approx(a[j]) + c;
+        }
+    } else {
+        float lx = s, ly = c, lz = s + c, li = 1.0f;
+        float px[8], py[8], pz[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) px[j] = a[j], py[j] = a[j] * 2.0f, pz[j] = a[j] * 3.0f, a[j] = 0.0f;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float dx = lx - px[j], dy = ly - py[j], dz = lz - pz[j];
+                    const float d2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    const float rr = rcp_approx(d2);
+                    a[j] = (d2 < 0.0001f) ? a[j] : fmaf(li, rr, a[j]);
+                }
+                lx += 0.25f, ly -= 0.125f, lz += 0.5f;  // 3 extra FADD per 8 evaluations (stands in for the LDS)
+            }
+        }
+    }
+    float t = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) t += a[j];
+    if (t == 123.456f) sink[0] = t;  // never true: keeps the loop alive
+}
+
+}  // namespace
+
+double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters) {
+    const int blocks = 148 * 8, threads = 256;
+    if (kind == 0) k_ubench<0><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 1) k_ubench<1><<<blocks, threads, 0, st>>>(sink, iters);
+    else k_ubench<2><<<blocks, threads, 0, st>>>(sink, iters);
+    return (double)blocks * threads * (double)iters * 32.0;  // 4 x 8 ops per iteration per thread
+}
+
+// =====================================================================================================
+// launchers
+// =====================================================================================================
+void vrk_lightgen_count(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
+                        uint32_t nz, uint32_t* counts) {
+    const uint64_t n = (uint64_t)nx * ny * nz;
+    k_lightgen<false><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, counts, nullptr, nullptr, nullptr, nullptr);
+}
+void vrk_lightgen_emit(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
+                       uint32_t nz, const unsigned long long* offsets, const unsigned long long* total, vr_ray_light* lights,
+                       VrLightCounter* counter) {
+    const uint64_t n = (uint64_t)nx * ny * nz;
+    k_lightgen<true><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, nullptr, offsets, total, lights, counter);
+    k_lightgen_finish<<<1, 1, 0, st>>>(u, total, counter);
+}
+void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, unsigned long long* total, uint64_t n,
+                  unsigned long long* tmp) {
+    const uint64_t nblocks = (n + 4095) / 4096;
+    if (nblocks == 0) {
+        cudaMemsetAsync(total, 0, sizeof(unsigned long long), st);
+        return;
+    }
+    k_scan_blocks<<<(unsigned)nblocks, 1024, 0, st>>>(in, out, tmp, n);
+    k_scan_tops<<<1, 1024, 0, st>>>(tmp, nblocks, total);
+    k_scan_add<<<(unsigned)nblocks, 1024, 0, st>>>(out, tmp, n);
+}
+void vrk_prepare_simple(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, int use_from,
+                        VrEvalLight* out, uint32_t capacity) {
+    if (!capacity) return;
+    k_prepare_simple<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, use_from, out, capacity);
+}
+void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
+                             uint32_t* steps, uint32_t capacity) {
+    if (!capacity) return;
+    k_prepare_count_steps<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, lrs, steps, capacity);
+}
+void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
+                        const unsigned long long* offsets, VrEvalLight* out, uint32_t capacity, uint64_t out_capacity) {
+    if (!capacity) return;
+    k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, capacity, out_capacity);
+}
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
+               uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
+    dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
+    if (fill)
+        k_march<true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+    else
+        k_march<false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+}
+void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+              uint64_t nlights, float radius, float* out) {
+    if (nsamples == 0) return;
+    constexpr int S = 8;
+    const uint64_t per_cta = (uint64_t)EVAL_THREADS * S;
+    const unsigned grid = (unsigned)((nsamples + per_cta - 1) / per_cta);
+    if (sphere)
+        k_eval<true, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights, radius, out);
+    else
+        k_eval<false, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights, radius, out);
+}
+void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
+                 const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8) {
+    const uint64_t npix = (uint64_t)tile.w * tile.h;
+    if (!npix) return;
+    k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8);
+}
+void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc) {
+    dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
+    k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc);
+}
+void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density) {
+    dim3 grid((w + 15) / 16, (h + 7) / 8);
+    k_cpu_test<<<grid, 128, 0, st>>>(g, w, h, aspect, scale, density);
+}
+void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix) {
+    if (!npix) return;
+    k_clear<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(accum, rgba8, frame_color, npix);
+}
+void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows) {
+    if (!h) return;
+    k_row_sums<<<h, 256, 0, st>>>(counts, w, rows);
+}

@@ -1,0 +1,63 @@
+// vr_kernels.cuh -- launch interface between the C-ABI layer (vr_api.cu) and the sm_100a kernels (vr_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/vr.h"
+#include "vr_device.cuh"
+
+// one camera-ray sample that reaches the light loop: world position + weight T*val*step
+// (shaders/point_compute_color.comp:72-89)
+struct VrSample {
+    float x, y, z, w;
+};
+// one entry of the expanded light list the evaluation kernel loops over: position + intensity/(4*pi)
+struct VrEvalLight {
+    float x, y, z, i4pi;
+};
+
+struct VrLightCounter {  // binding 4 (shaders/common_bindings.h:14-17) + bookkeeping
+    uint32_t lightCount;
+    uint32_t contributionCounter;
+    unsigned long long totalEmitted;  // scatter events before the maxLights cap
+};
+
+struct VrWorkCounters {
+    unsigned long long S_ref, S_eff;
+};
+
+// ---- light generation (shaders/light_gen.comp and variants)
+void vrk_lightgen_count(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
+                        uint32_t nz, uint32_t* counts);
+void vrk_lightgen_emit(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
+                       uint32_t nz, const unsigned long long* offsets, const unsigned long long* total, vr_ray_light* lights,
+                       VrLightCounter* counter);
+// ---- exclusive scan of u32 -> u64 (+ grand total), n up to 2^31; tmp holds ceil(n/4096)+1 entries
+void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, unsigned long long* total, uint64_t n,
+                  unsigned long long* tmp);
+// ---- light list expansion (ray/beam sub-points: shaders/ray_compute_color.comp:13-20)
+void vrk_prepare_simple(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, int use_from,
+                        VrEvalLight* out, uint32_t capacity);
+void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
+                             uint32_t* steps, uint32_t capacity);
+void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
+                        const unsigned long long* offsets, VrEvalLight* out, uint32_t capacity, uint64_t out_capacity);
+// ---- camera-ray march (shaders/point_compute_color.comp:60-94 minus the light loop)
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
+               uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc);
+// ---- the hot kernel: every sample against every entry of the expanded light list
+void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+              uint64_t nlights, float radius, float* out);
+// ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
+void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
+                 const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
+// ---- path mode (shaders/path_compute_color.comp), fully fused per pixel
+void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc);
+// ---- CPU_test/main.cpp:25-43, 89-126
+void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density);
+// ---- helpers
+void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix);
+void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows);
+// ---- microbenchmarks (roofline denominators); returns the op count launched
+double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters);

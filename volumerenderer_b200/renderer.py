@@ -1,0 +1,255 @@
+"""Host-side mirror of the compute section of the reference's VolumeApp (src/main.cpp), on top of the libvr C ABI.
+
+`VolumeRenderer.draw_frame()` is `VolumeApp::drawFrame` (src/main.cpp:620-837) without the window: frameCount++,
+UBO update, light-counter reset, image clear on the first frame, light-generation dispatch, gather dispatch. The
+`ubo` attribute is the 96-byte `uboData` block (src/main.cpp:83-98) with the defaults of :546-559; algorithm names
+follow the `Algorithm` enum (:65-68). All compute runs in libvr's sm_100a kernels; there is no CPU fallback.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import ALGO, LG_KEEP_ORIGIN, LG_RESET_ORIGIN, LIGHT_DTYPE, VrCounters, VrTile, VrTimings, VrUbo
+
+
+class VrError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{_lib.STATUS_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+def _algo(a):
+    return ALGO[a] if isinstance(a, str) else int(a)
+
+
+class VolumeRenderer:
+    """One CUDA device, one stream, one set of bindings (grid, lights, counter, image, UBO)."""
+
+    def __init__(self, device=0):
+        self._L = _lib.load()
+        self._ctx = C.c_void_p()
+        rc = self._L.vr_create(device, C.byref(self._ctx))
+        if rc != 0:
+            raise VrError(rc, self._L.vr_last_error(None).decode())
+        self.device = device
+        self.width = self.height = 0
+        self._grid_keepalive = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _check(self, rc):
+        if rc != 0:
+            raise VrError(rc, self._L.vr_last_error(self._ctx).decode())
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._L.vr_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ------------------------------------------------------------------ bindings
+    def set_grid(self, grid_bytes):
+        """binding 2: raw nanovdb::GridHandle bytes (src/main.cpp:1191-1212)."""
+        g = np.ascontiguousarray(np.frombuffer(grid_bytes, np.uint8) if not isinstance(grid_bytes, np.ndarray) else grid_bytes)
+        self._check(self._L.vr_set_grid(self._ctx, g.ctypes.data_as(C.c_void_p), g.nbytes))
+
+    def resize(self, width, height):
+        """binding 0: storage image sized to the framebuffer; resets the progressive state (src/main.cpp:936-982)."""
+        self._check(self._L.vr_resize(self._ctx, width, height))
+        self.width, self.height = width, height
+
+    @property
+    def ubo(self):
+        u = VrUbo()
+        self._check(self._L.vr_get_params(self._ctx, C.byref(u)))
+        return u
+
+    @ubo.setter
+    def ubo(self, u):
+        self._check(self._L.vr_set_params(self._ctx, C.byref(u)))
+
+    def update_ubo(self, **kw):
+        """uniformBuffer->updateBuffer(&uboData) with some fields changed (the ImGui sliders, src/main.cpp:662-691)."""
+        u = self.ubo
+        for k, v in kw.items():
+            if isinstance(v, (tuple, list, np.ndarray)):
+                getattr(u, k)[:] = [float(x) for x in v] if k != "framebufferDim" else [int(x) for x in v]
+            else:
+                setattr(u, k, v)
+        self.ubo = u
+        return u
+
+    def default_ubo(self):
+        u = VrUbo()
+        self._L.vr_default_params(C.byref(u), self.width, self.height)
+        return u
+
+    def set_max_lights_capacity(self, n):
+        self._check(self._L.vr_set_max_lights_capacity(self._ctx, n))
+
+    def set_light_gen_groups(self, gx=1, gy=1, gz=1, variant=LG_RESET_ORIGIN):
+        self._check(self._L.vr_set_light_gen_groups(self._ctx, gx, gy, gz, variant))
+
+    def set_march_cache(self, enabled):
+        self._check(self._L.vr_set_march_cache(self._ctx, int(bool(enabled))))
+
+    # ------------------------------------------------------------------ commands
+    def reset_lights(self):
+        self._check(self._L.vr_reset_lights(self._ctx))
+
+    def clear_image(self):
+        self._check(self._L.vr_clear_image(self._ctx))
+
+    def write_lights(self, lights):
+        a = np.ascontiguousarray(lights, LIGHT_DTYPE)
+        self._check(self._L.vr_write_lights(self._ctx, a.ctypes.data_as(C.c_void_p), len(a)))
+
+    def dispatch_light_gen(self, algo, groups=(1, 1, 1), variant=LG_RESET_ORIGIN):
+        self._check(self._L.vr_dispatch_light_gen(self._ctx, _algo(algo), groups[0], groups[1], groups[2], variant))
+
+    def dispatch_compute_color(self, algo, tile=None):
+        t = C.byref(VrTile(*tile)) if tile is not None else None
+        self._check(self._L.vr_dispatch_compute_color(self._ctx, _algo(algo), t))
+
+    def draw_frame(self, algo, tile=None):
+        """The compute section of VolumeApp::drawFrame (src/main.cpp:712-837)."""
+        t = C.byref(VrTile(*tile)) if tile is not None else None
+        self._check(self._L.vr_render_frame(self._ctx, _algo(algo), t))
+
+    def reset_accumulation(self):
+        self._check(self._L.vr_reset_accumulation(self._ctx))
+
+    def sync(self):
+        self._check(self._L.vr_sync(self._ctx))
+
+    # ------------------------------------------------------------------ read-back
+    def read_lights(self):
+        cnt = (C.c_uint32 * 2)()
+        total = C.c_uint64()
+        self._check(self._L.vr_read_light_counter(self._ctx, cnt, C.byref(total)))
+        n = C.c_uint32()
+        out = np.zeros(max(cnt[0], 1), LIGHT_DTYPE)
+        self._check(self._L.vr_read_lights(self._ctx, out.ctypes.data_as(C.c_void_p), len(out), C.byref(n)))
+        return out[:min(n.value, len(out))], n.value, total.value
+
+    def read_frame_color(self):
+        out = np.zeros((self.height, self.width), np.float32)
+        self._check(self._L.vr_read_frame_color_f32(self._ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def read_accum(self):
+        out = np.zeros((self.height, self.width, 4), np.float32)
+        self._check(self._L.vr_read_accum_f32(self._ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def read_image_rgba8(self):
+        out = np.zeros((self.height, self.width, 4), np.uint8)
+        self._check(self._L.vr_read_image_rgba8(self._ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def write_accum(self, accum, frame_count):
+        a = np.ascontiguousarray(accum, np.float32)
+        assert a.shape == (self.height, self.width, 4)
+        self._check(self._L.vr_write_accum_f32(self._ctx, a.ctypes.data_as(C.c_void_p), frame_count))
+
+    def write_image_rgba8(self, img):
+        a = np.ascontiguousarray(img, np.uint8)
+        assert a.shape == (self.height, self.width, 4)
+        self._check(self._L.vr_write_image_rgba8(self._ctx, a.ctypes.data_as(C.c_void_p)))
+
+    def counters(self):
+        c = VrCounters()
+        self._check(self._L.vr_get_counters(self._ctx, C.byref(c)))
+        return {k: getattr(c, k) for k, _ in VrCounters._fields_}
+
+    def timings(self):
+        t = VrTimings()
+        self._check(self._L.vr_get_timings(self._ctx, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in VrTimings._fields_}
+
+    def row_sample_counts(self):
+        out = np.zeros(self.height, np.uint64)
+        self._check(self._L.vr_row_sample_counts(self._ctx, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def device_buffers(self):
+        """Raw device pointers (accum float4, rgba8, frame colour) and the CUDA stream, for zero-copy interop."""
+        a, i, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._check(self._L.vr_get_device_buffers(self._ctx, C.byref(a), C.byref(i), C.byref(f), C.byref(s)))
+        return dict(accum=a.value, rgba8=i.value, frame_color=f.value, stream=s.value)
+
+    def timer_start(self):
+        self._check(self._L.vr_timer_start(self._ctx))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self._L.vr_timer_stop(self._ctx, C.byref(ms)))
+        return ms.value
+
+    def ubench(self, kind):
+        """0: FP32 FMA TFLOP/s, 1: MUFU.RCP 1e12 op/s, 2: point-light inner loop 1e12 eval/s (registers only)."""
+        out = C.c_double()
+        self._check(self._L.vr_ubench(self._ctx, {"fma": 0, "rcp": 1, "point": 2}.get(kind, kind), C.byref(out)))
+        return out.value
+
+    def cpu_test_render(self, width=256, height=256):
+        """CPU_test/main.cpp's density ray-march (fixed camera, 1200 unit steps) as a kernel."""
+        out = np.zeros((height, width), np.float32)
+        self._check(self._L.vr_cpu_test_render(self._ctx, width, height, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+
+# ---------------------------------------------------------------------- grid fixtures (host side, no GPU needed)
+def _take(L, p, n):
+    a = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,)).copy()
+    L.vr_grid_free(p)
+    return a
+
+
+def build_cloud_grid(n, seed=1234, voxel_size=None, translation=(-32.0, -12.0, -32.0), nthreads=0):
+    """Procedural cloud of SURVEY 8(d): n^3 voxels, background 0, uniform map voxel 64/n + translation."""
+    L = _lib.load()
+    t = np.asarray(translation, np.float64)
+    p, sz = C.c_void_p(), C.c_uint64()
+    rc = L.vr_grid_build_cloud(n, seed, voxel_size if voxel_size else 64.0 / n, t.ctypes.data_as(C.c_void_p), nthreads,
+                               C.byref(p), C.byref(sz))
+    if rc:
+        raise VrError(rc, "vr_grid_build_cloud")
+    return _take(L, p, sz)
+
+
+def build_fog_sphere_grid(radius, center=(0, 0, 0), voxel_size=1.0, translation=(0.0, 0.0, 0.0), nthreads=0):
+    L = _lib.load()
+    c = np.asarray(center, np.int32)
+    t = np.asarray(translation, np.float64)
+    p, sz = C.c_void_p(), C.c_uint64()
+    rc = L.vr_grid_build_fog_sphere(radius, c.ctypes.data_as(C.c_void_p), voxel_size, t.ctypes.data_as(C.c_void_p), nthreads,
+                                    C.byref(p), C.byref(sz))
+    if rc:
+        raise VrError(rc, "vr_grid_build_fog_sphere")
+    return _take(L, p, sz)
+
+
+def build_dense_grid(dense, origin=(0, 0, 0), background=0.0, voxel_size=1.0, translation=(0.0, 0.0, 0.0), nthreads=0):
+    L = _lib.load()
+    d = np.ascontiguousarray(dense, np.float32)
+    dims = np.asarray(d.shape, np.int32)
+    o = np.asarray(origin, np.int32)
+    t = np.asarray(translation, np.float64)
+    p, sz = C.c_void_p(), C.c_uint64()
+    rc = L.vr_grid_build_dense(d.ctypes.data_as(C.c_void_p), dims.ctypes.data_as(C.c_void_p), o.ctypes.data_as(C.c_void_p),
+                               background, voxel_size, t.ctypes.data_as(C.c_void_p), nthreads, C.byref(p), C.byref(sz))
+    if rc:
+        raise VrError(rc, "vr_grid_build_dense")
+    return _take(L, p, sz)
