@@ -1,0 +1,388 @@
+#!/usr/bin/env python3
+"""bench.py -- BASELINE.json's metric on its configs[1] workload (C2 of SURVEY.md section 8d):
+
+    Point VPLs, maxLights 1000, synthetic 256^3 procedural cloud, 1920x1080, all UBO defaults of the reference.
+
+A step is one frame of the hot path, exactly what VolumeApp::drawFrame's compute section does (src/main.cpp:712-837):
+frameCount++, counter reset, light generation (gx work-groups of 4x4 photons), camera march, light evaluation,
+progressive average. metric = light-pixel contributions per second: C_eff = S_eff * lightCount per frame (camera
+samples with non-zero density x lights) divided by the frame time; ms_per_step is ms/frame.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (N>1: launched by torchrun, NCCL)
+  python bench.py --impl reference [...]                          the reference's shader source on the host cores
+
+N>1 partitions the frame into row bands balanced by per-row sample counts (grid and lights replicated, light
+generation repeated on every rank) and exchanges the bands over NCCL inside the timed region: strong scaling.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (grid N, W, H, algo, maxLights, light-gen groups gx, description)
+    "C2": dict(n=256, W=1920, H=1080, algo="point", max_lights=1000, gx=32,
+               desc="C2: Point VPLs, maxLights 1000, 256^3 procedural cloud (seed 1234, voxel 0.25, 14.2 MB NanoVDB), 1920x1080"),
+    "C3": dict(n=256, W=1920, H=1080, algo="ray", max_lights=4096, gx=128,
+               desc="C3: Ray lights, maxLights 4096, 256^3 procedural cloud, 1920x1080"),
+}
+FLOP_PER_EVAL = {"point": 11, "sphere": 29, "ray": 19, "beam": 37}  # SURVEY 8(d) algorithmic figures
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.QUERY}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for row in self.rows:
+            f = [x.strip() for x in row.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def cpu_workload(cfg, frame):
+    """Grid, UBO and the frame's light list for the CPU arms (built with the product's host-side grid writer and the
+    oracle's light generation; neither is inside a timed region)."""
+    import volumerenderer_b200 as vr
+    from oracle import pyoracle
+    grid = vr.build_cloud_grid(cfg["n"])
+    orc = pyoracle.Oracle()
+    u = pyoracle.default_ubo(cfg["W"], cfg["H"], frameCount=frame, maxLights=cfg["max_lights"])
+    lights, count, _, _ = orc.light_gen(grid, u, (cfg["gx"], 1, 1), 0)
+    return grid, orc, u, lights
+
+
+def sample_ceff(orc, grid, u, algo, n_lights, stride):
+    """C_eff of the pixel-stride sample, counted exactly by a march without lights (outside any timed region)."""
+    from oracle import pyoracle
+    _, cnt = orc.gather(grid, u, algo, np.zeros(0, pyoracle.LIGHT_DTYPE), stride=stride, skip_zero=True)
+    return cnt["S_eff"] * n_lights, cnt
+
+
+def run_cpu(kind, orc, ref, grid, u, algo, lights, stride, threads):
+    t0 = time.perf_counter()
+    if kind == "reference":
+        ref.gather(grid, u, algo, lights, stride=stride, nthreads=threads)
+    else:
+        orc.gather(grid, u, algo, lights, stride=stride, skip_zero=True, nthreads=threads)
+    return time.perf_counter() - t0
+
+
+def pick_stride(t_probe, probe_stride, target_s):
+    s = probe_stride * (t_probe / target_s) ** 0.5
+    for cand in (1, 2, 3, 4, 6, 8, 12, 16, 24, 32):
+        if cand >= s:
+            return cand
+    return 32
+
+
+def reference_arm(args, cfg):
+    """--impl reference: the reference's own shader source (shaders/point_compute_color.comp etc. compiled as C++ in
+    oracle/_ref) on all host threads; falls back to the oracle port when oracle/_ref was never built."""
+    from oracle import pyoracle
+    threads = os.cpu_count() or 1
+    grid, orc, u, lights = cpu_workload(cfg, 1)
+    ref = pyoracle.Ref() if pyoracle.have_ref() else None
+    kind = "reference" if ref is not None else "port"
+    algo = cfg["algo"]
+    t_probe = run_cpu(kind, orc, ref, grid, u, algo, lights, 32, threads)
+    target = max(0.5, min(6.0, 150.0 / (args.steps + args.warmup)))
+    stride = pick_stride(t_probe, 32, target)
+    ceff, cnt = sample_ceff(orc, grid, u, algo, len(lights), stride)
+    for _ in range(args.warmup):
+        run_cpu(kind, orc, ref, grid, u, algo, lights, stride, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        run_cpu(kind, orc, ref, grid, u, algo, lights, stride, threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = ceff / dt
+    sample = (f"every {stride}th pixel in x and y of the {cfg['W']}x{cfg['H']} frame ({cnt['pixels']} pixels, "
+              f"S_eff {cnt['S_eff']}, C_eff {ceff:.3e} per step); "
+              + ("reference shader source evaluates every in-bbox sample (S_ref %d)" % cnt["S_ref"] if kind == "reference"
+                 else "oracle port with the exact zero-density skip"))
+    line = {
+        "impl": "reference", "metric": "light_pixel_contributions_per_s", "value": value, "unit": "contributions/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["desc"], "pixel_stride": stride},
+        "cpu_baseline": {"value": value, "unit": "contributions/s", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "contributions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "full_frame_ms_equiv": dt * 1e3 * stride * stride,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
+    args = ap.parse_args()
+    cfg = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank == 0:
+            reference_arm(args, cfg)
+        return 0
+    if args.warmup < 3:
+        log("note: fewer than 3 warm-up steps requested; using 3")
+        args.warmup = 3
+
+    import torch
+    import volumerenderer_b200 as vr
+    from volumerenderer_b200 import tiles
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: volumerenderer_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    W, H, algo = cfg["W"], cfg["H"], cfg["algo"]
+
+    grid = vr.build_cloud_grid(cfg["n"])
+    r = vr.VolumeRenderer(local_rank)
+    if world > 1:
+        shared = torch.cuda.Stream()
+        torch.cuda.set_stream(shared)
+        r.set_stream(shared.cuda_stream)  # one stream for the kernels and the NCCL band exchange
+    r.set_grid(grid)
+    r.resize(W, H)
+    r.set_max_lights_capacity(max(87500, cfg["max_lights"]))
+    r.ubo = r.default_ubo()
+    r.update_ubo(maxLights=cfg["max_lights"])
+    r.set_light_gen_groups(cfg["gx"], 1, 1)
+
+    # row bands balanced by the number of non-zero-density samples per row (identical on every rank)
+    bands = [(0, H)]
+    if world > 1:
+        bands = tiles.balanced_row_bands(r.row_sample_counts().astype(np.float64) + 2000.0, world)
+    tile = tiles.band_tile(bands[rank], W) if world > 1 else None
+    accum_t = tiles.accum_as_tensor(r) if world > 1 else None
+
+    def step():
+        r.draw_frame(algo, tile)
+        if world > 1:
+            tiles.exchange_bands(accum_t, bands)
+
+    def barrier():
+        r.sync()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # microbenchmarks for the roofline denominators (before the timed region)
+    peak_fma = r.ubench("fma") if rank == 0 else 0.0
+    peak_rcp = r.ubench("rcp") if rank == 0 else 0.0
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    launches0 = r.launch_count()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ceff = 0
+    evals = 0
+    eval_ms = 0.0
+    pass_ms = {k: 0.0 for k in ("light_gen_ms", "march_ms", "prepare_ms", "eval_ms", "resolve_ms")}
+    r.timer_start()
+    t_host0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+        c = r.counters()          # host-side bookkeeping of the frame just enqueued (no extra sync)
+        ceff += c["S_eff"] * c["light_count"]
+        evals += c["E"]
+        tm = r.timings()          # waits for this frame's last event only
+        for k in pass_ms:
+            pass_ms[k] += tm[k]
+    dev_ms = r.timer_stop()
+    barrier()
+    host_ms = (time.perf_counter() - t_host0) * 1e3
+    launches = r.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([dev_ms, float(ceff), float(evals), pass_ms["eval_ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        dev_ms_max, ceff_total, evals_total = float(tmax[0]), float(tsum[1]), float(tsum[2])
+    else:
+        dev_ms_max, ceff_total, evals_total = dev_ms, float(ceff), float(evals)
+    ms_per_step = dev_ms_max / args.steps
+    value = ceff_total / (dev_ms_max * 1e-3)
+
+    # ---- e2e: the same frames through the C ABI with HOST buffers: grid bytes + UBO go host->device and the float
+    # accumulator comes back device->host inside the timed region, every step
+    pinned_grid = torch.empty(grid.nbytes, dtype=torch.uint8, pin_memory=True)
+    pinned_grid.numpy()[:] = grid
+    grid_host = pinned_grid.numpy()
+    out_host_t = torch.empty((H, W, 4), dtype=torch.float32, pin_memory=True)
+    out_host = out_host_t.numpy()
+    L = r._L
+
+    def e2e_step():
+        r.set_grid(grid_host)                       # H2D: the NanoVDB buffer (binding 2)
+        r.ubo = r.ubo                               # H2D: the 96-byte UBO (kernel parameter)
+        step()
+        if rank == 0:
+            r._check(L.vr_read_accum_f32(r._ctx, out_host.ctypes.data_as(ctypes.c_void_p)))  # D2H: linear float image
+        else:
+            r.sync()
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    e2e_ceff = 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+        c = r.counters()
+        e2e_ceff += c["S_eff"] * c["light_count"]
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s, float(e2e_ceff)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = te.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = te.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        e2e_s, e2e_ceff = float(tmax[0]), float(tsum[1])
+    e2e_value = e2e_ceff / e2e_s
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (k_eval): FP32-issue bound, measured live with CUDA events
+        flop = FLOP_PER_EVAL[algo]
+        eval_s = pass_ms["eval_ms"] * 1e-3
+        achieved = evals * flop / eval_s / 1e12 if eval_s > 0 else 0.0
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        samples_per_step = evals / max(1, c["eval_lights"]) / args.steps
+        alg_bytes = samples_per_step * 20.0 + c["eval_lights"] * 16.0   # 16 B sample in + 4 B out, 16 B per light
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "eval_traffic.json")) as f:
+                traffic = json.load(f).get(args.workload)
+        except Exception:
+            pass
+        roofline = {
+            "bound": "fp32", "kernel": f"k_eval<{algo}>", "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s",
+            "frac": achieved / peak_fma if peak_fma else None,
+            "peak_source": "FFMA microbenchmark measured in this run (vr_ubench kind 0); MEASURED_PEAKS.json has no non-tensor FP32 figure",
+            "flop_per_eval": flop, "evals_per_s": evals / eval_s if eval_s > 0 else 0.0,
+            "mufu_rcp_peak_per_s": peak_rcp * 1e12, "mufu_frac": (evals / eval_s) / (peak_rcp * 1e12) if peak_rcp and eval_s > 0 else None,
+            "traffic": traffic,
+            "hbm": {"bound": "hbm", "achieved": alg_bytes / (eval_s / args.steps) / 1e9 if eval_s > 0 else 0.0, "peak": hbm_peak,
+                    "unit": "GB/s", "frac": (alg_bytes / (eval_s / args.steps) / 1e9) / hbm_peak if eval_s > 0 else None,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (of fallback)",
+                    "algorithmic_bytes_per_launch": alg_bytes},
+        }
+        cpu_baseline = None
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import pyoracle
+            threads = os.cpu_count() or 1
+            cgrid, orc, u, lights = cpu_workload(cfg, 1)
+            t_probe = run_cpu("port", orc, None, cgrid, u, algo, lights, 32, threads)
+            stride = pick_stride(t_probe, 32, args.cpu_seconds)
+            cc, cnt = sample_ceff(orc, cgrid, u, algo, len(lights), stride)
+            dt = run_cpu("port", orc, None, cgrid, u, algo, lights, stride, threads)
+            cpu_baseline = {"value": cc / dt, "unit": "contributions/s", "cores": threads, "kind": "port",
+                            "sample": f"oracle port (exact zero-density skip, {threads} threads over rows), every {stride}th pixel in x "
+                                      f"and y of the {W}x{H} frame: {cnt['pixels']} pixels, C_eff {cc:.3e}, {dt:.2f} s"}
+        line = {
+            "metric": "light_pixel_contributions_per_s", "value": value, "unit": "contributions/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": "row bands balanced by S_eff" if world > 1 else "whole frame",
+                       "l2": "per-step working set (1.3 GB of samples + 14 MB grid) exceeds the 126 MB L2; no flush needed",
+                       "bands": bands if world > 1 else None},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "contributions/s", "ms_per_step": e2e_s * 1e3 / args.steps,
+                    "h2d_bytes_per_step": int(grid.nbytes + 96) * world, "d2h_bytes_per_step": int(W * H * 16)},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+            "cpu_baseline": cpu_baseline,
+            "passes_ms_per_step": {k: v / args.steps for k, v in pass_ms.items()},
+            "host_ms_per_step": host_ms / args.steps,
+            "contributions_per_frame": ceff_total / args.steps,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    r.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

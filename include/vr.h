@@ -158,6 +158,10 @@ int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
  * camera, image size and march parameters are unchanged (progressive accumulation) */
 int vr_set_march_cache(vr_ctx* ctx, int enabled);
 
+/* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
+ * (default). Both follow shaders/common_functions.h:186-194; results differ by rounding only. */
+int vr_set_eval_variant(vr_ctx* ctx, int variant);
+
 /* ---- CPU_test/main.cpp:25-43, 89-126 as a kernel: fixed camera (0,250,-800) in index space, fov 45, 1200 unit
  * steps, density[j*w+i] = sum of grid values. */
 int vr_cpu_test_render(vr_ctx* ctx, uint32_t width, uint32_t height, float* density_out);
@@ -175,12 +179,19 @@ int vr_grid_build_dense(const float* dense, const int32_t dims[3], const int32_t
                         uint64_t* size_out);
 void vr_grid_free(void* bytes);
 
+/* run on a caller-owned CUDA stream (e.g. torch's current stream, so that NCCL collectives and these kernels are
+ * ordered on one stream); NULL restores the context's own stream. The caller keeps the stream alive. */
+int vr_set_stream(vr_ctx* ctx, void* cuda_stream);
+/* number of kernel launches this context has issued since creation */
+int vr_get_launch_count(vr_ctx* ctx, uint64_t* launches);
+
 /* ---- measurement helpers: CUDA events on the context's stream (torch.cuda.Event only sees torch's stream) */
 int vr_timer_start(vr_ctx* ctx);
 int vr_timer_stop(vr_ctx* ctx, float* elapsed_ms); /* records, synchronises and returns the device time since start */
 /* microbenchmarks that measure this GPU's non-tensor ceilings for the roofline (FP32 FMA issue, MUFU.RCP):
  * kind 0: dependent FFMA chains -> TFLOP/s (2 flop per FFMA); kind 1: MUFU.RCP -> 1e12 op/s;
- * kind 2: the point-light inner loop with operands in registers (3 FADD, FMUL, 2 FFMA, FSETP, MUFU.RCP, FFMA) -> 1e12 eval/s */
+ * kind 2: the point-light inner loop with operands in registers (3 FADD, FMUL, 2 FFMA, FSETP, MUFU.RCP, FFMA) -> 1e12 eval/s
+ * kind 3: dependent FFMA2 (packed FP32x2) chains -> TFLOP/s; kind 4: the packed point-light inner loop -> 1e12 eval/s */
 int vr_ubench(vr_ctx* ctx, int kind, double* result);
 
 /* library facts */

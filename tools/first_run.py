@@ -8,7 +8,9 @@ import numpy as np
 import volumerenderer_b200 as vr
 
 r = vr.VolumeRenderer(0)
-print("ubench fma TFLOP/s", r.ubench("fma"), "rcp T/s", r.ubench("rcp"), "point Teval/s", r.ubench("point"), flush=True)
+print("ubench fma TFLOP/s", r.ubench(0), "rcp T/s", r.ubench(1), "point Teval/s", r.ubench(2), "ffma2 TFLOP/s", r.ubench(3),
+      "packed point Teval/s", r.ubench(4), flush=True)
+r.set_eval_variant(int(os.environ.get("VR_EVAL_VARIANT", "1")))
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 algo = sys.argv[2] if len(sys.argv) > 2 else "point"
 ml = int(sys.argv[3]) if len(sys.argv) > 3 else 1000

@@ -56,8 +56,8 @@ EXPORTS = [
     "vr_dispatch_light_gen", "vr_dispatch_compute_color", "vr_set_light_gen_groups", "vr_render_frame",
     "vr_reset_accumulation", "vr_sync", "vr_read_lights", "vr_read_light_counter", "vr_read_image_rgba8",
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
-    "vr_get_timings", "vr_get_device_buffers", "vr_row_sample_counts", "vr_set_march_cache", "vr_cpu_test_render",
-    "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
+    "vr_get_timings", "vr_get_device_buffers", "vr_row_sample_counts", "vr_set_march_cache", "vr_set_eval_variant", "vr_cpu_test_render",
+    "vr_set_stream", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
 ]
 
 _lib = None
@@ -111,6 +111,9 @@ def load():
     L.vr_row_sample_counts.argtypes = [P, P]
     L.vr_set_march_cache.argtypes = [P, I]
     L.vr_cpu_test_render.argtypes = [P, U32, U32, P]
+    L.vr_set_eval_variant.argtypes = [P, I]
+    L.vr_set_stream.argtypes = [P, P]
+    L.vr_get_launch_count.argtypes = [P, C.POINTER(U64)]
     L.vr_timer_start.argtypes = [P]
     L.vr_timer_stop.argtypes = [P, C.POINTER(C.c_float)]
     L.vr_ubench.argtypes = [P, I, C.POINTER(C.c_double)]

@@ -60,11 +60,12 @@ struct MarchKey {
 
 struct vr_ctx {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
+    unsigned long long launch_base = 0;
     std::string err;
     // binding 2
     uint8_t* grid = nullptr;
-    uint64_t grid_size = 0, grid_gen = 0;
+    uint64_t grid_size = 0, grid_gen = 0, grid_cap = 0;
     VrGridDev gdev{};
     bool have_grid = false;
     // binding 5
@@ -90,6 +91,8 @@ struct vr_ctx {
     DevBuf<VrSample> samples;
     DevBuf<float> contrib;
     DevBuf<VrEvalLight> eval_lights;
+    DevBuf<float4> eval_lights2;
+    int eval_variant = 1;  // 0: scalar kernel, 1: packed FP32x2 kernel for point/ray lists
     DevBuf<uint32_t> light_steps;
     DevBuf<unsigned long long> light_offsets;
     unsigned long long* totals = nullptr;       // [0] samples, [1] expanded lights (device)
@@ -204,7 +207,9 @@ int vr_create(int cuda_device, vr_ctx** out) {
         }                                                                                       \
     } while (0)
     VR_CREATE_CUDA(cudaSetDevice(cuda_device));
-    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    c->stream = c->own_stream;
+    c->launch_base = vrk_launch_count();
     VR_CREATE_CUDA(cudaMalloc(&c->counter, sizeof(VrLightCounter)));
     VR_CREATE_CUDA(cudaMemsetAsync(c->counter, 0, sizeof(VrLightCounter), c->stream));
     VR_CREATE_CUDA(cudaMalloc(&c->photon_total, sizeof(unsigned long long)));
@@ -242,6 +247,7 @@ int vr_destroy(vr_ctx* c) {
     c->samples.release();
     c->contrib.release();
     c->eval_lights.release();
+    c->eval_lights2.release();
     c->light_steps.release();
     c->light_offsets.release();
     if (c->counter) cudaFree(c->counter);
@@ -257,7 +263,7 @@ int vr_destroy(vr_ctx* c) {
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < 2; i++)
         if (c->tev[i]) cudaEventDestroy(c->tev[i]);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
     return VR_OK;
 }
@@ -302,12 +308,16 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     if (root + 64 + 32ull * tiles > size) return fail(c, VR_E_BADGRID, "root tile table outside the buffer");
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (c->grid) {
+    if (c->grid && c->grid_cap < size) {
         cudaFree(c->grid);
         c->grid = nullptr;
-        c->have_grid = false;
+        c->grid_cap = 0;
     }
-    VR_CUDA(c, cudaMalloc(&c->grid, size));
+    c->have_grid = false;
+    if (!c->grid) {
+        VR_CUDA(c, cudaMalloc(&c->grid, size));
+        c->grid_cap = size;
+    }
     VR_CUDA(c, cudaMemcpyAsync(c->grid, bytes, size, cudaMemcpyHostToDevice, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     VrGridDev g{};
@@ -537,7 +547,12 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     cudaEventRecord(c->ev[5], st);
     // ---- evaluation (hot) + resolve
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
-    vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, neval, c->ubo.beamRadius, c->contrib.p);
+    if (!sphere && c->eval_variant == 1) {
+        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 2));
+        vrk_eval_point_packed(st, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->contrib.p);
+    } else {
+        vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, neval, c->ubo.beamRadius, c->contrib.p);
+    }
     cudaEventRecord(c->ev[6], st);
     vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->frame_color, c->accum, c->rgba8);
     cudaEventRecord(c->ev[7], st);
@@ -691,6 +706,19 @@ int vr_row_sample_counts(vr_ctx* c, uint64_t* rows_out) {
     return check_stream(c);
 }
 
+int vr_set_stream(vr_ctx* c, void* cuda_stream) {
+    if (!c) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return VR_OK;
+}
+int vr_get_launch_count(vr_ctx* c, uint64_t* launches) {
+    if (!c || !launches) return VR_E_ARG;
+    *launches = vrk_launch_count() - c->launch_base;
+    return VR_OK;
+}
+
 int vr_timer_start(vr_ctx* c) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
@@ -707,7 +735,7 @@ int vr_timer_stop(vr_ctx* c, float* ms) {
     return VR_OK;
 }
 int vr_ubench(vr_ctx* c, int kind, double* result) {
-    if (!c || !result || kind < 0 || kind > 2) return VR_E_ARG;
+    if (!c || !result || kind < 0 || kind > 4) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
     float* sink = nullptr;
     VR_CUDA(c, cudaMalloc(&sink, 64));
@@ -724,12 +752,18 @@ int vr_ubench(vr_ctx* c, int kind, double* result) {
         }
         float ms = 0;
         cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
-        const double rate = ops / (ms * 1e-3) * (kind == 0 ? 2.0 : 1.0) / 1e12;
+        const double rate = ops / (ms * 1e-3) * (kind == 0 ? 2.0 : (kind == 3 ? 4.0 : 1.0)) / 1e12;
         if (rate > best) best = rate;
     }
     cudaFree(sink);
     *result = best;
     return check_stream(c);
+}
+
+int vr_set_eval_variant(vr_ctx* c, int variant) {
+    if (!c || variant < 0 || variant > 1) return VR_E_ARG;
+    c->eval_variant = variant;
+    return VR_OK;
 }
 
 int vr_set_march_cache(vr_ctx* c, int enabled) {

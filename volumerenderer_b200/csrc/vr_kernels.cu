@@ -425,6 +425,97 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval(const VrSample* __restric
     }
 }
 
+// ---- packed variant (point lights): two samples per FP32x2 instruction -----------------------------------------
+// Blackwell (sm_100) adds packed FP32 instructions (PTX add/mul/fma.rn.f32x2, SASS FADD2/FMUL2/FFMA2) that carry two
+// FP32 operations per issue slot. The baseline kernel above is issue-bound (ncu r01: 9.3 instructions per evaluation,
+// issue slots 75 % busy, XU pipe 65 %); packing the distance computation of two samples of the same thread halves its
+// issue cost (6 -> 3 slots per evaluation), leaving the MUFU.RCP rate (16/clk/SM) as the next ceiling.
+// The light tile is stored duplicated in shared memory, (x,x,y,y)(z,z,w,w), so that both halves of every register pair
+// come straight from two broadcast LDS.128.
+constexpr int EVAL2_TILE = 512;  // lights per stage: 512 * 32 B = 16 KB
+
+__global__ void k_dup_lights(const VrEvalLight* __restrict__ in, float4* __restrict__ out, uint64_t n) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 q = reinterpret_cast<const float4*>(in)[i];
+    out[2 * i] = make_float4(q.x, q.x, q.y, q.y);
+    out[2 * i + 1] = make_float4(q.z, q.z, q.w, q.w);
+}
+
+template <int S>  // S samples per thread, S even
+__global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                              const float4* __restrict__ lights2, uint64_t nlights,
+                                                              float* __restrict__ out) {
+    constexpr int P = S / 2;
+    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && ntiles > 0) {
+        const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
+        mbar_expect_tx(&bar[0], cnt * 32u);
+        tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
+    }
+    // negated sample coordinates (the packed ISA has add, not sub), pairs (2p, 2p+1)
+    float2 nsx[P], nsy[P], nsz[P], acc[P];
+    float sw[S];
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + i0);
+        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + i1);
+        nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
+        sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
+        acc[p] = make_float2(0.f, 0.f);
+    }
+    for (uint64_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = (uint32_t)(tl & 1);
+        if (tid == 0 && tl + 1 < ntiles) {
+            const uint64_t first = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (uint32_t)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * first, cnt * 32u, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
+        const uint64_t first = tl * EVAL2_TILE;
+        const int cnt = (int)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+        const float4* __restrict__ L = stage[buf];
+#pragma unroll 2
+        for (int l = 0; l < cnt; l++) {
+            const float4 qa = L[2 * l], qb = L[2 * l + 1];
+            const float2 X = make_float2(qa.x, qa.y), Y = make_float2(qa.z, qa.w), Z = make_float2(qb.x, qb.y);
+            const float wI = qb.z;
+#pragma unroll
+            for (int p = 0; p < P; p++) {
+                const float2 dx = __fadd2_rn(X, nsx[p]);
+                const float2 dy = __fadd2_rn(Y, nsy[p]);
+                const float2 dz = __fadd2_rn(Z, nsz[p]);
+                float2 d2 = __fmul2_rn(dx, dx);
+                d2 = __ffma2_rn(dy, dy, d2);
+                d2 = __ffma2_rn(dz, dz, d2);
+                const float r0 = rcp_approx(d2.x), r1 = rcp_approx(d2.y);
+                acc[p].x = (d2.x < 0.0001f) ? acc[p].x : fmaf(wI, r0, acc[p].x);
+                acc[p].y = (d2.y < 0.0001f) ? acc[p].y : fmaf(wI, r1, acc[p].y);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) out[i0] = sw[2 * p] * acc[p].x;
+        if (i1 < nsamples) out[i1] = sw[2 * p + 1] * acc[p].y;
+    }
+}
+
 // =====================================================================================================
 // resolve
 // =====================================================================================================
@@ -629,6 +720,47 @@ __global__ void __launch_bounds__(256) k_ubench(float* sink, int iters) {
 #pragma unroll
                 for (int j = 0; j < 8; j++) a[j] = rcp_approx(a[j]) + c;
         }
+    } else if (KIND == 3) {
+        float2 b[8];
+        const float2 s2 = make_float2(s, s), c2 = make_float2(c, c);
+#pragma unroll
+        for (int j = 0; j < 8; j++) b[j] = make_float2(a[j], a[j] + 0.5f);
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) b[j] = __ffma2_rn(b[j], s2, c2);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) a[j] = b[j].x + b[j].y;
+    } else if (KIND == 4) {
+        float2 X = make_float2(s, s), Y = make_float2(c, c), Z = make_float2(s + c, s + c);
+        const float li = 1.0f;
+        float2 px[4], py[4], pz[4], ac[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            px[j] = make_float2(a[2 * j], a[2 * j + 1]), py[j] = make_float2(a[2 * j] * 2.f, a[2 * j + 1] * 2.f);
+            pz[j] = make_float2(a[2 * j] * 3.f, a[2 * j + 1] * 3.f), ac[j] = make_float2(0.f, 0.f);
+        }
+        const float2 inc = make_float2(0.25f, 0.25f);
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float2 dx = __fadd2_rn(X, px[j]), dy = __fadd2_rn(Y, py[j]), dz = __fadd2_rn(Z, pz[j]);
+                    float2 d2 = __fmul2_rn(dx, dx);
+                    d2 = __ffma2_rn(dy, dy, d2);
+                    d2 = __ffma2_rn(dz, dz, d2);
+                    const float r0 = rcp_approx(d2.x), r1 = rcp_approx(d2.y);
+                    ac[j].x = (d2.x < 0.0001f) ? ac[j].x : fmaf(li, r0, ac[j].x);
+                    ac[j].y = (d2.y < 0.0001f) ? ac[j].y : fmaf(li, r1, ac[j].y);
+                }
+                X = __fadd2_rn(X, inc), Y = __fadd2_rn(Y, inc), Z = __fadd2_rn(Z, inc);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) a[2 * j] = ac[j].x, a[2 * j + 1] = ac[j].y;
     } else {
         float lx = s, ly = c, lz = s + c, li = 1.0f;
         float px[8], py[8], pz[8];
@@ -656,10 +788,17 @@ __global__ void __launch_bounds__(256) k_ubench(float* sink, int iters) {
 
 }  // namespace
 
+static unsigned long long g_launches = 0;
+unsigned long long vrk_launch_count() { return g_launches; }
+#define VR_COUNT(n) (g_launches += (n))
+
 double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters) {
+    VR_COUNT(1);
     const int blocks = 148 * 8, threads = 256;
     if (kind == 0) k_ubench<0><<<blocks, threads, 0, st>>>(sink, iters);
     else if (kind == 1) k_ubench<1><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 3) k_ubench<3><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 4) k_ubench<4><<<blocks, threads, 0, st>>>(sink, iters);
     else k_ubench<2><<<blocks, threads, 0, st>>>(sink, iters);
     return (double)blocks * threads * (double)iters * 32.0;  // 4 x 8 ops per iteration per thread
 }
@@ -669,18 +808,21 @@ double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters) {
 // =====================================================================================================
 void vrk_lightgen_count(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
                         uint32_t nz, uint32_t* counts) {
+    VR_COUNT(1);
     const uint64_t n = (uint64_t)nx * ny * nz;
     k_lightgen<false><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, counts, nullptr, nullptr, nullptr, nullptr);
 }
 void vrk_lightgen_emit(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
                        uint32_t nz, const unsigned long long* offsets, const unsigned long long* total, vr_ray_light* lights,
                        VrLightCounter* counter) {
+    VR_COUNT(2);
     const uint64_t n = (uint64_t)nx * ny * nz;
     k_lightgen<true><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, nullptr, offsets, total, lights, counter);
     k_lightgen_finish<<<1, 1, 0, st>>>(u, total, counter);
 }
 void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, unsigned long long* total, uint64_t n,
                   unsigned long long* tmp) {
+    VR_COUNT(3);
     const uint64_t nblocks = (n + 4095) / 4096;
     if (nblocks == 0) {
         cudaMemsetAsync(total, 0, sizeof(unsigned long long), st);
@@ -692,29 +834,44 @@ void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, 
 }
 void vrk_prepare_simple(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, int use_from,
                         VrEvalLight* out, uint32_t capacity) {
+    VR_COUNT(1);
     if (!capacity) return;
     k_prepare_simple<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, use_from, out, capacity);
 }
 void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
                              uint32_t* steps, uint32_t capacity) {
+    VR_COUNT(1);
     if (!capacity) return;
     k_prepare_count_steps<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, lrs, steps, capacity);
 }
 void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
                         const unsigned long long* offsets, VrEvalLight* out, uint32_t capacity, uint64_t out_capacity) {
+    VR_COUNT(1);
     if (!capacity) return;
     k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, capacity, out_capacity);
 }
 void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
+    VR_COUNT(1);
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
     if (fill)
         k_march<true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
     else
         k_march<false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
 }
+void vrk_eval_point_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                           float4* lights2, uint64_t nlights, float* out) {
+    if (nsamples == 0) return;
+    VR_COUNT(2);
+    constexpr int S = 8;
+    if (nlights) k_dup_lights<<<(unsigned)((nlights + 255) / 256), 256, 0, st>>>(lights, lights2, nlights);
+    const uint64_t per_cta = (uint64_t)EVAL_THREADS * S;
+    const unsigned grid = (unsigned)((nsamples + per_cta - 1) / per_cta);
+    k_eval_point2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, out);
+}
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               uint64_t nlights, float radius, float* out) {
+    VR_COUNT(1);
     if (nsamples == 0) return;
     constexpr int S = 8;
     const uint64_t per_cta = (uint64_t)EVAL_THREADS * S;
@@ -726,24 +883,29 @@ void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsa
 }
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8) {
+    VR_COUNT(1);
     const uint64_t npix = (uint64_t)tile.w * tile.h;
     if (!npix) return;
     k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8);
 }
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
               float4* accum, uchar4* rgba8, VrWorkCounters* wc) {
+    VR_COUNT(1);
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
     k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc);
 }
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density) {
+    VR_COUNT(1);
     dim3 grid((w + 15) / 16, (h + 7) / 8);
     k_cpu_test<<<grid, 128, 0, st>>>(g, w, h, aspect, scale, density);
 }
 void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix) {
+    VR_COUNT(1);
     if (!npix) return;
     k_clear<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(accum, rgba8, frame_color, npix);
 }
 void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows) {
+    VR_COUNT(1);
     if (!h) return;
     k_row_sums<<<h, 256, 0, st>>>(counts, w, rows);
 }

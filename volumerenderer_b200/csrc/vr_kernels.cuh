@@ -48,6 +48,9 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
 // ---- the hot kernel: every sample against every entry of the expanded light list
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               uint64_t nlights, float radius, float* out);
+// packed-FP32x2 variant for point lights; lights2 is scratch for the duplicated list (2 float4 per light)
+void vrk_eval_point_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                           float4* lights2, uint64_t nlights, float* out);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
@@ -61,3 +64,5 @@ void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame
 void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows);
 // ---- microbenchmarks (roofline denominators); returns the op count launched
 double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters);
+// number of kernels launched by the vrk_* functions in this process (monotonic)
+unsigned long long vrk_launch_count();

@@ -101,6 +101,10 @@ class VolumeRenderer:
     def set_light_gen_groups(self, gx=1, gy=1, gz=1, variant=LG_RESET_ORIGIN):
         self._check(self._L.vr_set_light_gen_groups(self._ctx, gx, gy, gz, variant))
 
+    def set_eval_variant(self, variant):
+        """0: scalar FP32 evaluation kernel, 1: packed FP32x2 kernel for point-type lists (default)."""
+        self._check(self._L.vr_set_eval_variant(self._ctx, int(variant)))
+
     def set_march_cache(self, enabled):
         self._check(self._L.vr_set_march_cache(self._ctx, int(bool(enabled))))
 
@@ -188,6 +192,15 @@ class VolumeRenderer:
         a, i, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
         self._check(self._L.vr_get_device_buffers(self._ctx, C.byref(a), C.byref(i), C.byref(f), C.byref(s)))
         return dict(accum=a.value, rgba8=i.value, frame_color=f.value, stream=s.value)
+
+    def set_stream(self, cuda_stream):
+        """Run on a caller-owned CUDA stream (int handle, e.g. torch.cuda.current_stream().cuda_stream); None = own."""
+        self._check(self._L.vr_set_stream(self._ctx, C.c_void_p(cuda_stream) if cuda_stream else None))
+
+    def launch_count(self):
+        n = C.c_uint64()
+        self._check(self._L.vr_get_launch_count(self._ctx, C.byref(n)))
+        return n.value
 
     def timer_start(self):
         self._check(self._L.vr_timer_start(self._ctx))

@@ -1,0 +1,93 @@
+"""Image-tile partitioning across GPUs: pixels are independent given (grid, lights, UBO), so
+each rank renders a band of rows with the grid and the light list replicated (light generation is deterministic and
+is simply repeated on every rank), and the bands are exchanged with one broadcast per band over NCCL.
+
+The reference is single-GPU (one queue, src/main.cpp:265-270); this module is new capability, not a mirror.
+Only the band exchange uses torch.distributed; everything else is plain Python/numpy and is tested on CPU with gloo.
+"""
+import numpy as np
+
+
+def balanced_row_bands(row_cost, n_parts, min_rows=1):
+    """Split rows [0, H) into n_parts contiguous bands of near-equal total cost.
+
+    row_cost: per-row work estimate (e.g. VolumeRenderer.row_sample_counts(): non-zero-density camera samples per row;
+    the evaluation kernel's time is proportional to it). Returns [(y0, h), ...] covering every row exactly once.
+    """
+    cost = np.asarray(row_cost, np.float64)
+    H = len(cost)
+    if n_parts < 1:
+        raise ValueError("n_parts must be >= 1")
+    if H < n_parts * min_rows:
+        raise ValueError(f"{H} rows cannot be split into {n_parts} bands of >= {min_rows} rows")
+    total = float(cost.sum())
+    if total <= 0.0:
+        cost = np.ones(H)
+        total = float(H)
+    prefix = np.concatenate([[0.0], np.cumsum(cost)])
+    cuts = [0]
+    for p in range(1, n_parts):
+        target = total * p / n_parts
+        y = int(np.searchsorted(prefix, target, side="left"))
+        # pick the closer of the two neighbouring cut positions
+        if y > 0 and abs(prefix[y - 1] - target) <= abs(prefix[min(y, H)] - target):
+            y -= 1
+        y = max(y, cuts[-1] + min_rows)
+        y = min(y, H - (n_parts - p) * min_rows)
+        cuts.append(y)
+    cuts.append(H)
+    return [(cuts[i], cuts[i + 1] - cuts[i]) for i in range(n_parts)]
+
+
+def band_tile(band, width):
+    """(y0, h) -> vr_tile tuple (x0, y0, w, h)."""
+    return (0, int(band[0]), int(width), int(band[1]))
+
+
+def exchange_bands(image, bands, group=None):
+    """In-place all-gather of row bands: rank r owns rows bands[r] of `image` (a torch tensor whose first dimension is
+    the image row, identical shape on every rank); afterwards every rank holds the full image.
+
+    One broadcast per band (bands have unequal heights, which rules out a plain all_gather); NCCL runs them back to
+    back on the communicator's stream. Works with CPU tensors over gloo (tests) and CUDA tensors over NCCL.
+    """
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    if len(bands) != world:
+        raise ValueError(f"{len(bands)} bands for world size {world}")
+    works = []
+    for r, (y0, h) in enumerate(bands):
+        if h == 0:
+            continue
+        src = dist.get_global_rank(group, r) if group is not None else r
+        works.append(dist.broadcast(image[y0:y0 + h], src=src, group=group, async_op=True))
+    for w in works:
+        w.wait()
+    return image
+
+
+def reduce_progressive_sums(accum_sum, dst=0, group=None):
+    """Sample-parallel progressive mode: every rank accumulates a float SUM of the frames it rendered;
+    one reduce(sum) to `dst` combines them (divide by the total frame count afterwards). Not available for the
+    rgba8-faithful running average, which is sequential by construction."""
+    import torch.distributed as dist
+
+    dist.reduce(accum_sum, dst=dst, op=dist.ReduceOp.SUM, group=group)
+    return accum_sum
+
+
+class DeviceArray:
+    """Zero-copy view of libvr device memory for torch.as_tensor (CUDA array interface v2)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def accum_as_tensor(renderer):
+    """The renderer's float4 accumulator as a (H, W, 4) float32 CUDA tensor sharing memory with libvr."""
+    import torch
+
+    bufs = renderer.device_buffers()
+    return torch.as_tensor(DeviceArray(bufs["accum"], (renderer.height, renderer.width, 4), "<f4"),
+                           device=f"cuda:{renderer.device}")
