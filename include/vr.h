@@ -158,6 +158,11 @@ int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
  * camera, image size and march parameters are unchanged (progressive accumulation) */
 int vr_set_march_cache(vr_ctx* ctx, int enabled);
 
+/* nearest-voxel grid values at n index coordinates (ijk[3*n]) through the device traversal: what
+ * pnanovdb_readaccessor_get_value_address + pnanovdb_read_float return (shaders/PNanoVDB_GLSL.h:2202-2231, :365-368),
+ * i.e. leaf values, tile values at lower/upper/root level, and the background outside every root tile. */
+int vr_lookup_values(vr_ctx* ctx, const int32_t* ijk, uint64_t n, float* values_out);
+
 /* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
  * (default). Both follow shaders/common_functions.h:186-194; results differ by rounding only. */
 int vr_set_eval_variant(vr_ctx* ctx, int variant);

@@ -1,0 +1,63 @@
+"""Host-side multi-GPU logic: band balancing and the band exchange, the latter with world_size 2 over gloo on CPU."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_balanced_row_bands_cover_and_balance():
+    from volumerenderer_b200.tiles import balanced_row_bands, band_tile
+    rng = np.random.default_rng(0)
+    cost = np.concatenate([np.zeros(100), rng.integers(1000, 90000, 800), np.zeros(180)]).astype(np.float64)
+    for n in (1, 2, 3, 4, 8):
+        bands = balanced_row_bands(cost, n)
+        assert len(bands) == n and bands[0][0] == 0 and sum(h for _, h in bands) == len(cost)
+        for (y0, h), (y1, _) in zip(bands, bands[1:]):
+            assert y0 + h == y1 and h >= 1
+        loads = [cost[y:y + h].sum() for y, h in bands]
+        assert max(loads) <= cost.sum() / n + cost.max() + 1e-9
+    assert band_tile((10, 5), 1920) == (0, 10, 1920, 5)
+    assert balanced_row_bands(np.zeros(16), 4) == [(0, 4), (4, 4), (8, 4), (12, 4)]
+    with pytest.raises(ValueError):
+        balanced_row_bands(np.ones(3), 4)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, H, W):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    from volumerenderer_b200.tiles import balanced_row_bands, exchange_bands, reduce_progressive_sums
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cost = np.arange(H, dtype=np.float64) + 1.0
+    bands = balanced_row_bands(cost, world)
+    full = torch.arange(H * W * 4, dtype=torch.float32).reshape(H, W, 4)
+    img = torch.full((H, W, 4), -1.0)
+    y0, h = bands[rank]
+    img[y0:y0 + h] = full[y0:y0 + h]          # this rank "rendered" only its band
+    exchange_bands(img, bands)
+    assert torch.equal(img, full), f"rank {rank}: band exchange did not reassemble the frame"
+    s = torch.full((H, W, 4), float(rank + 1))
+    reduce_progressive_sums(s, dst=0)
+    if rank == 0:
+        assert torch.equal(s, torch.full((H, W, 4), float(sum(range(1, world + 1)))))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_band_exchange_gloo_world2():
+    import torch.multiprocessing as mp
+    mp.spawn(_worker, args=(2, _free_port(), 37, 16), nprocs=2, join=True)

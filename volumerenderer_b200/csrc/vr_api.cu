@@ -760,6 +760,28 @@ int vr_ubench(vr_ctx* c, int kind, double* result) {
     return check_stream(c);
 }
 
+int vr_lookup_values(vr_ctx* c, const int32_t* ijk, uint64_t n, float* values_out) {
+    if (!c) return VR_E_ARG;
+    if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
+    if (n == 0) return VR_OK;
+    if (!ijk || !values_out) return fail(c, VR_E_ARG, "vr_lookup_values: NULL buffer");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    int32_t* d_ijk = nullptr;
+    float* d_out = nullptr;
+    VR_CUDA(c, cudaMalloc(&d_ijk, n * 12));
+    cudaError_t e = cudaMalloc(&d_out, n * 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_ijk, ijk, n * 12, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        vrk_lookup(c->stream, c->gdev, d_ijk, n, d_out);
+        e = cudaMemcpyAsync(values_out, d_out, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_ijk);
+    if (d_out) cudaFree(d_out);
+    if (e != cudaSuccess) return fail(c, VR_E_CUDA, "vr_lookup_values failed: %s", cudaGetErrorString(e));
+    return check_stream(c);
+}
+
 int vr_set_eval_variant(vr_ctx* c, int variant) {
     if (!c || variant < 0 || variant > 1) return VR_E_ARG;
     c->eval_variant = variant;

@@ -676,6 +676,18 @@ __global__ void __launch_bounds__(128) k_cpu_test(VrGridDev g, uint32_t w, uint3
     density[(uint64_t)j * w + i] = dens;
 }
 
+// nearest-voxel lookups for a list of coordinates; each thread walks `per_thread` consecutive entries with one accessor
+// so the cached-leaf / cached-lower / cached-upper / root paths are all exercised (test hook for the traversal)
+__global__ void k_lookup(VrGridDev g, const int32_t* __restrict__ ijk, uint64_t n, uint32_t per_thread, float* __restrict__ out) {
+    const uint64_t first = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * per_thread;
+    VrAcc acc;
+    vr_acc_init(acc);
+    for (uint32_t q = 0; q < per_thread && first + q < n; q++) {
+        const uint64_t e = first + q;
+        out[e] = vr_lookup(g, acc, ijk[3 * e], ijk[3 * e + 1], ijk[3 * e + 2]);
+    }
+}
+
 __global__ void k_clear(float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix) {
     const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npix) return;
@@ -898,6 +910,13 @@ void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, f
     VR_COUNT(1);
     dim3 grid((w + 15) / 16, (h + 7) / 8);
     k_cpu_test<<<grid, 128, 0, st>>>(g, w, h, aspect, scale, density);
+}
+void vrk_lookup(cudaStream_t st, const VrGridDev& g, const int32_t* ijk, uint64_t n, float* out) {
+    VR_COUNT(1);
+    if (!n) return;
+    const uint32_t per_thread = 8;
+    const uint64_t threads = (n + per_thread - 1) / per_thread;
+    k_lookup<<<(unsigned)((threads + 127) / 128), 128, 0, st>>>(g, ijk, n, per_thread, out);
 }
 void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix) {
     VR_COUNT(1);

@@ -59,6 +59,8 @@ void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_sc
               float4* accum, uchar4* rgba8, VrWorkCounters* wc);
 // ---- CPU_test/main.cpp:25-43, 89-126
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density);
+// ---- traversal test hook
+void vrk_lookup(cudaStream_t st, const VrGridDev& g, const int32_t* ijk, uint64_t n, float* out);
 // ---- helpers
 void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame_color, uint64_t npix);
 void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows);

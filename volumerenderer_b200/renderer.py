@@ -202,6 +202,13 @@ class VolumeRenderer:
         self._check(self._L.vr_get_launch_count(self._ctx, C.byref(n)))
         return n.value
 
+    def lookup_values(self, ijk):
+        """Grid values at integer index coordinates through the device traversal."""
+        a = np.ascontiguousarray(ijk, np.int32).reshape(-1, 3)
+        out = np.zeros(len(a), np.float32)
+        self._check(self._L.vr_lookup_values(self._ctx, a.ctypes.data_as(C.c_void_p), len(a), out.ctypes.data_as(C.c_void_p)))
+        return out
+
     def timer_start(self):
         self._check(self._L.vr_timer_start(self._ctx))
 
