@@ -164,8 +164,16 @@ int vr_set_march_cache(vr_ctx* ctx, int enabled);
 int vr_lookup_values(vr_ctx* ctx, const int32_t* ijk, uint64_t n, float* values_out);
 
 /* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
- * (default). Both follow shaders/common_functions.h:186-194; results differ by rounding only. */
+ * with the d2 < 1e-4 guard in the loop, 2 = packed kernel that runs the loop unguarded and repeats a thread block with the
+ * guard when one of its threads saw d2 < 1e-4 (same results as 1; default), 3 = as 2 with 6 samples per thread. All follow
+ * shaders/common_functions.h:186-194; results differ by rounding only. */
 int vr_set_eval_variant(vr_ctx* ctx, int variant);
+/* the camera samples of the last vr_dispatch_compute_color (point/sphere/ray/beam) that reached the light loop, in pixel-major
+ * march order: world x, y, z and weight T*val*step per sample (shaders/point_compute_color.comp:72-89). *count receives
+ * the total; at most `capacity` samples (4 floats each) are copied. Diagnostic / test hook. */
+int vr_read_samples(vr_ctx* ctx, float* out, uint64_t capacity, uint64_t* count);
+/* thread blocks of variants >= 2 that had to repeat their light loop with the guard, since vr_create (diagnostic) */
+int vr_get_eval_redo_count(vr_ctx* ctx, uint64_t* ctas);
 
 /* ---- CPU_test/main.cpp:25-43, 89-126 as a kernel: fixed camera (0,250,-800) in index space, fov 45, 1200 unit
  * steps, density[j*w+i] = sum of grid values. */

@@ -182,6 +182,51 @@ def test_edge_cases(renderer, vr, pyoracle, oracle, cloud):
     assert rel <= REL_TOL and rmse <= RMSE_TOL
 
 
+@pytest.mark.parametrize("algo", ["point", "ray"])
+def test_near_light_guard_all_eval_variants(renderer, pyoracle, oracle, cloud, algo):
+    """Lights placed ON camera samples (d2 = 0), inside the guard radius (d2 < 1e-4, contributes 0) and just outside it
+    (huge but finite): every evaluation kernel must agree with the oracle, and the speculative kernels (2, 3) must
+    take their guarded repeat path and still equal the guarded packed kernel (1) bit for bit."""
+    grid = cloud(64)
+    W, H = 96, 64
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=64)
+    base, _, _, _ = oracle.light_gen(grid, ou, (4, 1, 1), 0)
+    _setup(renderer, grid, W, H, maxLights=64, frameCount=1)
+    renderer.write_lights(base)
+    renderer.clear_image()
+    renderer.dispatch_compute_color("point")
+    smp = renderer.read_samples()
+    assert len(smp) == renderer.counters()["S_eff"] > 1000
+    picks = smp[[len(smp) // 7, len(smp) // 2, (len(smp) * 6) // 7], :3]
+    near = np.zeros(4, pyoracle.LIGHT_DTYPE)
+    near["intensity"] = 25.0
+    pos = np.stack([picks[0],                                     # exactly on a sample: d2 = 0
+                    picks[1] + np.float32([0.004, 0.0, 0.0]),     # d2 ~ 1.6e-5 < 1e-4: contributes 0
+                    picks[2] + np.float32([0.0, 0.03, 0.0]),      # d2 ~ 9e-4: contributes I/(4 pi d2), large
+                    picks[2] + np.float32([0.0, 0.0, 0.5])])
+    if algo == "ray":   # the sub-points of a ray light start at `from` (s = 0, ray_compute_color.comp:16-20)
+        near["from"], near["to"] = pos, pos + np.float32([0.7, 0.2, 0.1])
+    else:               # point lights sit at `to` (point_compute_color.comp:12)
+        near["to"], near["from"] = pos, pos - np.float32([0.7, 0.2, 0.1])
+    lights = np.concatenate([base[:20], near, base[20:40]])
+    ofc, _ = oracle.gather(grid, ou, algo, lights, skip_zero=True)
+    out = {}
+    for variant in (0, 1, 2, 3):
+        renderer.set_eval_variant(variant)
+        redo0 = renderer.eval_redo_count()
+        renderer.write_lights(lights)
+        renderer.clear_image()
+        renderer.dispatch_compute_color(algo)
+        out[variant] = renderer.read_frame_color()
+        rel, rmse = rel_err(out[variant], ofc)
+        assert rel <= REL_TOL and rmse <= RMSE_TOL, (variant, rel, rmse)
+        assert np.isfinite(out[variant]).all()
+        if variant >= 2:
+            assert renderer.eval_redo_count() > redo0, "the guarded repeat path was not exercised"
+    renderer.set_eval_variant(2)
+    assert np.array_equal(out[1], out[2]) and np.array_equal(out[1], out[3])
+
+
 def test_argument_errors(renderer, vr, cloud):
     grid = cloud(64)
     _setup(renderer, grid, 32, 32)

@@ -92,13 +92,14 @@ struct vr_ctx {
     DevBuf<float> contrib;
     DevBuf<VrEvalLight> eval_lights;
     DevBuf<float4> eval_lights2;
-    int eval_variant = 1;  // 0: scalar kernel, 1: packed FP32x2 kernel for point/ray lists
+    int eval_variant = 2;  // 0: scalar kernel, 1: packed FP32x2 kernel, 2/3: packed speculative kernel (point/ray lists)
     DevBuf<uint32_t> light_steps;
     DevBuf<unsigned long long> light_offsets;
     unsigned long long* totals = nullptr;       // [0] samples, [1] expanded lights (device)
     unsigned long long* totals_host = nullptr;  // pinned
     VrWorkCounters* wc = nullptr;
     VrWorkCounters* wc_host = nullptr;  // pinned
+    unsigned long long* eval_redo = nullptr;  // CTAs of the speculative eval kernel that repeated with the guard (cumulative)
     vr_counters last_counters{};
     bool march_cache = false;
     MarchKey march_key;
@@ -217,6 +218,8 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaMallocHost(&c->totals_host, 4 * sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMalloc(&c->wc, sizeof(VrWorkCounters)));
     VR_CREATE_CUDA(cudaMallocHost(&c->wc_host, sizeof(VrWorkCounters)));
+    VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
+    VR_CREATE_CUDA(cudaMemsetAsync(c->eval_redo, 0, sizeof(unsigned long long), c->stream));
     for (int i = 0; i < 8; i++) VR_CREATE_CUDA(cudaEventCreate(&c->ev[i]));
     for (int i = 0; i < 2; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tev[i]));
 #undef VR_CREATE_CUDA
@@ -256,6 +259,7 @@ int vr_destroy(vr_ctx* c) {
     if (c->totals_host) cudaFreeHost(c->totals_host);
     if (c->wc) cudaFree(c->wc);
     if (c->wc_host) cudaFreeHost(c->wc_host);
+    if (c->eval_redo) cudaFree(c->eval_redo);
     if (c->accum) cudaFree(c->accum);
     if (c->rgba8) cudaFree(c->rgba8);
     if (c->frame_color) cudaFree(c->frame_color);
@@ -547,9 +551,10 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     cudaEventRecord(c->ev[5], st);
     // ---- evaluation (hot) + resolve
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
-    if (!sphere && c->eval_variant == 1) {
-        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 2));
-        vrk_eval_point_packed(st, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->contrib.p);
+    if (!sphere && c->eval_variant >= 1) {
+        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 10));
+        vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->contrib.p,
+                              c->eval_redo);
     } else {
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, neval, c->ubo.beamRadius, c->contrib.p);
     }
@@ -783,8 +788,33 @@ int vr_lookup_values(vr_ctx* c, const int32_t* ijk, uint64_t n, float* values_ou
 }
 
 int vr_set_eval_variant(vr_ctx* c, int variant) {
-    if (!c || variant < 0 || variant > 1) return VR_E_ARG;
+    if (!c || variant < 0 || variant > 3) return VR_E_ARG;
     c->eval_variant = variant;
+    return VR_OK;
+}
+
+int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {
+    if (!c) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint64_t n = c->cached_samples;
+    if (count) *count = n;
+    const uint64_t m = n < capacity ? n : capacity;
+    if (m && !out) return fail(c, VR_E_ARG, "vr_read_samples: NULL output buffer");
+    if (m) {
+        VR_CUDA(c, cudaMemcpyAsync(out, c->samples.p, m * sizeof(VrSample), cudaMemcpyDeviceToHost, c->stream));
+        VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return VR_OK;
+}
+
+int vr_get_eval_redo_count(vr_ctx* c, uint64_t* ctas) {
+    if (!c || !ctas) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    unsigned long long h = 0;
+    VR_CUDA(c, cudaMemcpyAsync(&h, c->eval_redo, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    *ctas = h;
     return VR_OK;
 }
 

@@ -434,10 +434,11 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval(const VrSample* __restric
 // come straight from two broadcast LDS.128.
 constexpr int EVAL2_TILE = 512;  // lights per stage: 512 * 32 B = 16 KB
 
-__global__ void k_dup_lights(const VrEvalLight* __restrict__ in, float4* __restrict__ out, uint64_t n) {
+// entries [n, npad) are padding: zero intensity, far away (d2 ~ 3e12, contribution +0)
+__global__ void k_dup_lights(const VrEvalLight* __restrict__ in, float4* __restrict__ out, uint64_t n, uint64_t npad) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float4 q = reinterpret_cast<const float4*>(in)[i];
+    if (i >= npad) return;
+    const float4 q = i < n ? reinterpret_cast<const float4*>(in)[i] : make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.0f);
     out[2 * i] = make_float4(q.x, q.x, q.y, q.y);
     out[2 * i + 1] = make_float4(q.z, q.z, q.w, q.w);
 }
@@ -507,6 +508,122 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
             }
         }
         __syncthreads();
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) out[i0] = sw[2 * p] * acc[p].x;
+        if (i1 < nsamples) out[i1] = sw[2 * p + 1] * acc[p].y;
+    }
+}
+
+// ---- speculative variant: no per-evaluation guard in the main pass -------------------------------------------------
+// ncu (profiles/r01b): k_eval_point2 is bound by the XU pipe (MUFU.RCP, 82.6 % busy) with the FMA pipe at 72 % and the
+// issue slots at 70 %: three resources within 15 % of each other, so the scheduler cannot keep the XU pipe full. The
+// guard `d2 < 1e-4 ? 0 : ...` (common_functions.h:190) costs two of the 6.7 issue slots per evaluation (FSETP + a
+// predicated scalar FFMA instead of half an FFMA2), yet it fires in about 6 of 32 000 thread blocks per C2 frame (a sample
+// within 0.01 world units of a light). This kernel therefore runs the light loop without the guard, tracking the
+// minimum d2 each thread has seen with one 3-input FMNMX per two evaluations (sm_100 `min.f32 d,a,b,c`), and
+// accumulates with FFMA2. If any thread of the CTA saw d2 < 1e-4 the CTA repeats its light loop with the guarded body
+// (the result of the first pass is discarded), so the output is identical to k_eval_point2's in every case.
+// Measured on C2 (profiles/README.md, r01c): 16.55 ms vs 17.12 ms. Moving a fraction of the reciprocals to the FMA pipe
+// (integer seed + Newton steps) was tried and is slower (17.7-18.5 ms): the FMA pipe is as loaded as the XU pipe.
+__device__ __forceinline__ float fmin3(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+template <int P, bool GUARD>
+__device__ __forceinline__ void eval_light_packed(const float4 qa, const float4 qb, const float2 (&nsx)[P], const float2 (&nsy)[P],
+                                                  const float2 (&nsz)[P], float2 (&acc)[P], float& dmin) {
+    const float2 X = make_float2(qa.x, qa.y), Y = make_float2(qa.z, qa.w), Z = make_float2(qb.x, qb.y);
+    const float2 W = make_float2(qb.z, qb.w);
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        const float2 dx = __fadd2_rn(X, nsx[p]);
+        const float2 dy = __fadd2_rn(Y, nsy[p]);
+        const float2 dz = __fadd2_rn(Z, nsz[p]);
+        float2 d2 = __fmul2_rn(dx, dx);
+        d2 = __ffma2_rn(dy, dy, d2);
+        d2 = __ffma2_rn(dz, dz, d2);
+        if (GUARD) {
+            const float r0 = rcp_approx(d2.x), r1 = rcp_approx(d2.y);
+            acc[p].x = (d2.x < 0.0001f) ? acc[p].x : fmaf(W.x, r0, acc[p].x);
+            acc[p].y = (d2.y < 0.0001f) ? acc[p].y : fmaf(W.y, r1, acc[p].y);
+        } else {
+            dmin = fmin3(dmin, d2.x, d2.y);
+            acc[p] = __ffma2_rn(W, make_float2(rcp_approx(d2.x), rcp_approx(d2.y)), acc[p]);
+        }
+    }
+}
+
+// one pass over the whole light list through the two-stage TMA ring; `it` counts the tiles consumed so far by this CTA
+// (stage = it & 1, mbarrier phase parity = (it >> 1) & 1) so that a second pass continues the ring where the first ended
+template <int P, bool GUARD, int UNROLL>
+__device__ __forceinline__ void eval_pass_packed(float4 (&stage)[2][2 * EVAL2_TILE], uint64_t (&bar)[2], const float4* __restrict__ lights2,
+                                                 uint64_t nlights, uint32_t& it, const float2 (&nsx)[P], const float2 (&nsy)[P],
+                                                 const float2 (&nsz)[P], float2 (&acc)[P], float& dmin) {
+    const uint32_t tid = threadIdx.x;
+    const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
+    if (tid == 0 && ntiles > 0) {
+        const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
+        mbar_expect_tx(&bar[it & 1], cnt * 32u);
+        tma_bulk_g2s(&stage[it & 1][0], lights2, cnt * 32u, &bar[it & 1]);
+    }
+    for (uint64_t tl = 0; tl < ntiles; tl++, it++) {
+        const uint32_t buf = it & 1;
+        if (tid == 0 && tl + 1 < ntiles) {
+            const uint64_t first = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (uint32_t)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * first, cnt * 32u, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (it >> 1) & 1);
+        const uint64_t first = tl * EVAL2_TILE;
+        const int cnt = (int)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+        const float4* __restrict__ L = stage[buf];
+#pragma unroll UNROLL
+        for (int l = 0; l < cnt; l++) eval_light_packed<P, GUARD>(L[2 * l], L[2 * l + 1], nsx, nsy, nsz, acc, dmin);
+        __syncthreads();  // everyone is done with stage[buf] before it is refilled two tiles later
+    }
+}
+
+template <int S, int MINB, int UNROLL>  // S samples per thread (even), MINB resident CTAs per SM
+__global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                              const float4* __restrict__ lights2, uint64_t nlights,
+                                                              float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
+    constexpr int P = S / 2;
+    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    float2 nsx[P], nsy[P], nsz[P], acc[P];
+    float sw[S];
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        // samples beyond the end sit far away (d2 ~ 3e12): they never trip the d2 check and are never stored
+        float4 a = make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.f), b = a;
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + i0);
+        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + i1);
+        nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
+        sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
+        acc[p] = make_float2(0.f, 0.f);
+    }
+    uint32_t it = 0;
+    float dmin = 3.0e38f;
+    eval_pass_packed<P, false, UNROLL>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
+    if (__syncthreads_or(!(dmin >= 0.0001f))) {  // also true for a NaN d2 (non-finite input)
+        if (tid == 0 && redo_count) atomicAdd(redo_count, 1ull);
+#pragma unroll
+        for (int p = 0; p < P; p++) acc[p] = make_float2(0.f, 0.f);
+        eval_pass_packed<P, true, 2>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
     }
 #pragma unroll
     for (int p = 0; p < P; p++) {
@@ -871,15 +988,18 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
     else
         k_march<false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
 }
-void vrk_eval_point_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                           float4* lights2, uint64_t nlights, float* out) {
+void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                           float4* lights2, uint64_t nlights, float* out, unsigned long long* redo_count) {
     if (nsamples == 0) return;
     VR_COUNT(2);
-    constexpr int S = 8;
-    if (nlights) k_dup_lights<<<(unsigned)((nlights + 255) / 256), 256, 0, st>>>(lights, lights2, nlights);
-    const uint64_t per_cta = (uint64_t)EVAL_THREADS * S;
-    const unsigned grid = (unsigned)((nsamples + per_cta - 1) / per_cta);
-    k_eval_point2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, out);
+    const uint64_t npad = (nlights + 3) / 4 * 4;
+    if (nlights) k_dup_lights<<<(unsigned)((npad + 255) / 256), 256, 0, st>>>(lights, lights2, nlights, npad);
+    auto grid = [&](int S) { return (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S)); };
+    switch (variant) {
+        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, npad, out, redo_count); break;
+        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, npad, out, redo_count); break;
+        default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, out); break;
+    }
 }
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               uint64_t nlights, float radius, float* out) {

@@ -49,8 +49,10 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               uint64_t nlights, float radius, float* out);
 // packed-FP32x2 variant for point lights; lights2 is scratch for the duplicated list (2 float4 per light)
-void vrk_eval_point_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                           float4* lights2, uint64_t nlights, float* out);
+// variant 1: guarded k_eval_point2; 2, 3: speculative k_eval_point3 with 8 / 6 samples per thread (see vr_kernels.cu); redo_count (device, may be
+// NULL) counts CTAs that had to repeat their light loop with the guard
+void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                           float4* lights2, uint64_t nlights, float* out, unsigned long long* redo_count);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);

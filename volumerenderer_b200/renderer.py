@@ -102,8 +102,23 @@ class VolumeRenderer:
         self._check(self._L.vr_set_light_gen_groups(self._ctx, gx, gy, gz, variant))
 
     def set_eval_variant(self, variant):
-        """0: scalar FP32 evaluation kernel, 1: packed FP32x2 kernel for point-type lists (default)."""
+        """0: scalar FP32 evaluation kernel, 1: packed FP32x2 kernel with the guard in the loop, 2: packed speculative
+        kernel (unguarded loop, guarded repeat when needed; same results as 1; default), 3: as 2, 6 samples per thread."""
         self._check(self._L.vr_set_eval_variant(self._ctx, int(variant)))
+
+    def read_samples(self):
+        """(n, 4) float32: world x, y, z, weight of the last gather's camera samples (pixel-major, march order)."""
+        n = C.c_uint64(0)
+        self._check(self._L.vr_read_samples(self._ctx, None, 0, C.byref(n)))
+        out = np.zeros((int(n.value), 4), np.float32)
+        if n.value:
+            self._check(self._L.vr_read_samples(self._ctx, out.ctypes.data_as(C.c_void_p), n.value, C.byref(n)))
+        return out
+
+    def eval_redo_count(self):
+        n = C.c_uint64(0)
+        self._check(self._L.vr_get_eval_redo_count(self._ctx, C.byref(n)))
+        return int(n.value)
 
     def set_march_cache(self, enabled):
         self._check(self._L.vr_set_march_cache(self._ctx, int(bool(enabled))))
