@@ -84,11 +84,33 @@ def test_tiles_linearity_determinism(scene, pyoracle, oracle):
     twice = r.read_frame_color()
     m = (twice < 1.0) & (full > 0)
     assert m.sum() > 100000 and np.array_equal(twice[m], 2.0 * full[m])
-    # scalar and packed evaluation kernels agree to rounding
-    r.set_eval_variant(0)
-    r.write_lights(ol)
-    r.clear_image()
-    r.dispatch_compute_color("point")
-    rel, rmse = rel_err(r.read_frame_color(), full)
-    r.set_eval_variant(1)
-    assert rel <= 1e-5 and rmse <= 1e-7
+    # scalar and packed evaluation kernels agree to rounding; the guarded and speculative packed kernels bit for bit
+    for variant, bitwise in ((0, False), (1, True), (3, True)):
+        r.set_eval_variant(variant)
+        r.write_lights(ol)
+        r.clear_image()
+        r.dispatch_compute_color("point")
+        other = r.read_frame_color()
+        r.set_eval_variant(2)
+        rel, rmse = rel_err(other, full)
+        assert rel <= 1e-5 and rmse <= 1e-7, (variant, rel, rmse)
+        assert not bitwise or np.array_equal(other, full), variant
+
+
+def test_sphere_kernels_agree(scene, pyoracle, oracle):
+    """packed sphere kernel (merged roundings) against the scalar kernel that keeps every rounding of the shader"""
+    r, grid = scene
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=300)
+    ol, _, _, _ = oracle.light_gen(grid, ou, (8, 1, 1), 0)
+    r.ubo = r.default_ubo()
+    r.update_ubo(frameCount=1, maxLights=300)
+    res = {}
+    for variant in (0, 2):
+        r.set_eval_variant(variant)
+        r.write_lights(ol)
+        r.clear_image()
+        r.dispatch_compute_color("sphere")
+        res[variant] = r.read_frame_color()
+    r.set_eval_variant(2)
+    rel, rmse = rel_err(res[2], res[0])
+    assert rel <= REL_TOL and rmse <= 1e-6, (rel, rmse)

@@ -555,6 +555,9 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 10));
         vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->contrib.p,
                               c->eval_redo);
+    } else if (sphere && c->eval_variant >= 1) {
+        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 10));
+        vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->ubo.beamRadius, c->contrib.p);
     } else {
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, neval, c->ubo.beamRadius, c->contrib.p);
     }

@@ -517,6 +517,98 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
     }
 }
 
+// ---- packed variant (sphere lights, also the sub-points of beams) ---------------------------------------------------
+// getClosestPointOnSphere + getPointLightContribution (common_functions.h:182-201) on two samples per FP32x2
+// instruction. The scalar kernel k_eval<SPHERE> spends ~30 issue slots per evaluation (it keeps every rounding of the
+// shader separate); here the roundings that cannot matter are merged:
+//   l2  = |p - O|^2 as fmul + 2 fma                      (1 ulp of l2 -> 1 ulp of inv -> R * 6e-8 = 6e-9 in `cur`)
+//   s   = inv * R once per evaluation, cur = fma(v, s, O) (inner roundings are at the 1e-8 scale)
+//   d2  = |cur - p|^2 as fmul + 2 fma
+// What is kept is the ONE rounding that dominates the result: `cur` rounded at the magnitude of the light position
+// (ulp(50) = 4e-6, amplified by 1/|cur - p| near the sphere surface), so the kernel tracks the reference's own
+// arithmetic noise instead of the ideal (|v| - R)^2. 16 packed + 4 MUFU + 4 guard/accumulate slots per pair of
+// evaluations: FMA pipe 17 cycles, XU pipe 16 cycles per evaluation.
+template <int S>
+__global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                                   const float4* __restrict__ lights2, uint64_t nlights, float radius,
+                                                                   float* __restrict__ out) {
+    constexpr int P = S / 2;
+    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0 && ntiles > 0) {
+        const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
+        mbar_expect_tx(&bar[0], cnt * 32u);
+        tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
+    }
+    float2 nsx[P], nsy[P], nsz[P], acc[P];
+    float sw[S];
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + i0);
+        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + i1);
+        nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
+        sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
+        acc[p] = make_float2(0.f, 0.f);
+    }
+    const float2 nR = make_float2(-radius, -radius);
+    for (uint64_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = (uint32_t)(tl & 1);
+        if (tid == 0 && tl + 1 < ntiles) {
+            const uint64_t first = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (uint32_t)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * first, cnt * 32u, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
+        const uint64_t first = tl * EVAL2_TILE;
+        const int cnt = (int)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
+        const float4* __restrict__ L = stage[buf];
+#pragma unroll 2
+        for (int l = 0; l < cnt; l++) {
+            const float4 qa = L[2 * l], qb = L[2 * l + 1];
+            const float2 X = make_float2(qa.x, qa.y), Y = make_float2(qa.z, qa.w), Z = make_float2(qb.x, qb.y);
+            const float wI = qb.z;
+#pragma unroll
+            for (int p = 0; p < P; p++) {
+                // v = O - p (the negated p - O: squares and the product with the negated radius absorb the sign exactly)
+                const float2 vx = __fadd2_rn(X, nsx[p]), vy = __fadd2_rn(Y, nsy[p]), vz = __fadd2_rn(Z, nsz[p]);
+                float2 l2 = __fmul2_rn(vx, vx);
+                l2 = __ffma2_rn(vy, vy, l2);
+                l2 = __ffma2_rn(vz, vz, l2);
+                const float2 sc = __fmul2_rn(make_float2(rsqrt_approx(l2.x), rsqrt_approx(l2.y)), nR);  // -R / |p - O|
+                // cur = O + normalize(p - O) * R ; Lv = cur - p
+                const float2 lx = __fadd2_rn(__ffma2_rn(vx, sc, X), nsx[p]);
+                const float2 ly = __fadd2_rn(__ffma2_rn(vy, sc, Y), nsy[p]);
+                const float2 lz = __fadd2_rn(__ffma2_rn(vz, sc, Z), nsz[p]);
+                float2 d2 = __fmul2_rn(lx, lx);
+                d2 = __ffma2_rn(ly, ly, d2);
+                d2 = __ffma2_rn(lz, lz, d2);
+                const float r0 = rcp_approx(d2.x), r1 = rcp_approx(d2.y);
+                acc[p].x = (d2.x < 0.0001f) ? acc[p].x : fmaf(wI, r0, acc[p].x);
+                acc[p].y = (d2.y < 0.0001f) ? acc[p].y : fmaf(wI, r1, acc[p].y);
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int p = 0; p < P; p++) {
+        const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+        if (i0 < nsamples) out[i0] = sw[2 * p] * acc[p].x;
+        if (i1 < nsamples) out[i1] = sw[2 * p + 1] * acc[p].y;
+    }
+}
+
 // ---- speculative variant: no per-evaluation guard in the main pass -------------------------------------------------
 // ncu (profiles/r01b): k_eval_point2 is bound by the XU pipe (MUFU.RCP, 82.6 % busy) with the FMA pipe at 72 % and the
 // issue slots at 70 %: three resources within 15 % of each other, so the scheduler cannot keep the XU pipe full. The
@@ -1000,6 +1092,15 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
         case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, npad, out, redo_count); break;
         default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, out); break;
     }
+}
+void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                            float4* lights2, uint64_t nlights, float radius, float* out) {
+    if (nsamples == 0) return;
+    VR_COUNT(2);
+    constexpr int S = 8;
+    if (nlights) k_dup_lights<<<(unsigned)((nlights + 255) / 256), 256, 0, st>>>(lights, lights2, nlights, nlights);
+    const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S));
+    k_eval_sphere2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, radius, out);
 }
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               uint64_t nlights, float radius, float* out) {

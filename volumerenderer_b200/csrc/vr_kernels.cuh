@@ -53,6 +53,9 @@ void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsa
 // NULL) counts CTAs that had to repeat their light loop with the guard
 void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
                            float4* lights2, uint64_t nlights, float* out, unsigned long long* redo_count);
+// packed-FP32x2 kernel for sphere lights / beam sub-points (common_functions.h:182-201)
+void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
+                            float4* lights2, uint64_t nlights, float radius, float* out);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
