@@ -81,12 +81,12 @@ typedef struct vr_counters {
 
 /* CUDA-event timings (ms) of the passes of the last frame / dispatches */
 typedef struct vr_timings {
-    float light_gen_ms;
+    float light_gen_ms; /* on the auxiliary stream in vr_render_frame: overlaps march_ms */
     float march_ms;    /* camera-ray march: count + scan + fill */
-    float prepare_ms;  /* light list expansion */
+    float prepare_ms;  /* light list expansion, incl. any wait for light generation to finish */
     float eval_ms;     /* the sample x light kernel (dominant) */
     float resolve_ms;  /* per-pixel reduction + progressive average */
-    float total_ms;
+    float total_ms;    /* gather start to resolve end (light generation runs inside this window in vr_render_frame) */
 } vr_timings;
 
 typedef struct vr_ctx vr_ctx;
@@ -150,6 +150,10 @@ int vr_write_accum_f32(vr_ctx* ctx, const float* in, uint32_t frame_count); /* r
 int vr_write_image_rgba8(vr_ctx* ctx, const uint8_t* in);
 int vr_get_counters(vr_ctx* ctx, vr_counters* out);
 int vr_get_timings(vr_ctx* ctx, vr_timings* out);
+/* per-pass times summed over every frame finished since the last reset, and the number of frames. Frames are timed
+ * through a small ring of CUDA-event sets that is read lazily, so collecting these costs no host synchronisation per
+ * frame (this call itself waits for the frames still in flight). reset != 0 clears the sums afterwards. */
+int vr_get_timings_sum(vr_ctx* ctx, vr_timings* sum, uint64_t* frames, int reset);
 /* device pointers for zero-copy interop (NCCL): float4 accumulator, rgba8 image, frame colour; CUDA stream */
 int vr_get_device_buffers(vr_ctx* ctx, void** accum_f32, void** image_rgba8, void** frame_color_f32, void** stream);
 /* per-row count of non-zero-density camera samples for the current params (tile balancing across GPUs) */

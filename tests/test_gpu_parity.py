@@ -45,6 +45,24 @@ def test_light_gen_bit_exact(renderer, pyoracle, oracle, cloud, n, groups, max_l
     assert lights.tobytes() == ol.tobytes()
 
 
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("max_lights", [5000, 300])
+def test_light_gen_many_lights_per_photon(renderer, pyoracle, oracle, cloud, variant, max_lights):
+    """scatteringProbability 0.9: photons emit far more lights than the kernel's private slab holds (the overflow
+    walk), with and without the maxLights cap cutting into a photon's list."""
+    grid = cloud(64)
+    kw = dict(maxLights=max_lights, frameCount=2, scatteringProbability=0.9)
+    _setup(renderer, grid, 64, 64, **kw)
+    renderer.reset_lights()
+    renderer.dispatch_light_gen("beam", (3, 1, 1), variant)
+    lights, count, emitted = renderer.read_lights()
+    ol, oc, oem, _ = oracle.light_gen(grid, pyoracle.default_ubo(64, 64, **kw), (3, 1, 1), variant)
+    if variant == 0:
+        assert emitted > 48 * 20, "the case must overflow the per-photon slab"
+    assert (count, emitted) == (oc, oem)
+    assert lights.tobytes() == ol.tobytes()
+
+
 def test_path_light_gen_is_empty(renderer, cloud):
     _setup(renderer, cloud(64), 32, 32, frameCount=1)
     renderer.reset_lights()

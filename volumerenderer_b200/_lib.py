@@ -56,7 +56,7 @@ EXPORTS = [
     "vr_dispatch_light_gen", "vr_dispatch_compute_color", "vr_set_light_gen_groups", "vr_render_frame",
     "vr_reset_accumulation", "vr_sync", "vr_read_lights", "vr_read_light_counter", "vr_read_image_rgba8",
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
-    "vr_get_timings", "vr_get_device_buffers", "vr_row_sample_counts", "vr_set_march_cache", "vr_set_eval_variant", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
+    "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_set_march_cache", "vr_set_eval_variant", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
     "vr_set_stream", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
 ]
 
@@ -107,6 +107,7 @@ def load():
     L.vr_write_image_rgba8.argtypes = [P, P]
     L.vr_get_counters.argtypes = [P, C.POINTER(VrCounters)]
     L.vr_get_timings.argtypes = [P, C.POINTER(VrTimings)]
+    L.vr_get_timings_sum.argtypes = [P, C.POINTER(VrTimings), C.POINTER(U64), I]
     L.vr_get_device_buffers.argtypes = [P, C.POINTER(P), C.POINTER(P), C.POINTER(P), C.POINTER(P)]
     L.vr_row_sample_counts.argtypes = [P, P]
     L.vr_set_march_cache.argtypes = [P, I]

@@ -76,7 +76,15 @@ struct vr_ctx {
     VrLightCounter* counter = nullptr;
     DevBuf<uint32_t> photon_counts;
     DevBuf<unsigned long long> photon_offsets;
+    DevBuf<unsigned long long> lg_scan_tmp;  // light generation runs on the auxiliary stream: own scan scratch
+    DevBuf<float4> lg_slab;                  // per-photon private light lists (vrk_lightgen)
     unsigned long long* photon_total = nullptr;
+    bool lights_external = false;            // list came from vr_write_lights: no bound on the segment lengths
+    uint32_t external_count = 0;
+    // light generation of vr_render_frame overlaps the camera march on this stream
+    cudaStream_t aux_stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_lg_done = nullptr;
+    bool lg_in_flight = false;
     uint32_t lg_groups[3] = {1, 1, 1};
     vr_lightgen_variant lg_variant = VR_LG_RESET_ORIGIN;
     // binding 0 (+ float accumulator and last frame colour)
@@ -96,19 +104,37 @@ struct vr_ctx {
     DevBuf<uint32_t> light_steps;
     DevBuf<unsigned long long> light_offsets;
     unsigned long long* totals = nullptr;       // [0] samples, [1] expanded lights (device)
-    unsigned long long* totals_host = nullptr;  // pinned
+    unsigned long long* totals_host = nullptr;  // pinned: blocking read-backs on the slow paths
     VrWorkCounters* wc = nullptr;
-    VrWorkCounters* wc_host = nullptr;  // pinned
+    uint32_t* expand_overflow = nullptr;        // device flag: the expanded light list did not fit its buffer
+    // per-frame scalars copied to pinned memory without blocking; vr_get_counters waits for ev_scalars only
+    struct Scalars {
+        unsigned long long nsamples, neval, S_ref, S_eff;
+        uint32_t light_count, overflow;
+    };
+    Scalars* scalars_host = nullptr;
+    cudaEvent_t ev_scalars = nullptr;
+    bool counters_pending = false, counters_have_march = false;
+    uint64_t nsamples_used = 0;
     unsigned long long* eval_redo = nullptr;  // CTAs of the speculative eval kernel that repeated with the guard (cumulative)
     vr_counters last_counters{};
+    vr_algo last_algo = VR_ALGO_POINT;
     bool march_cache = false;
     MarchKey march_key;
     uint64_t cached_samples = 0;
-    // timing
-    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint64_t cached_S[2] = {0, 0};  // S_ref, S_eff of the cached march
+    // timing: a ring of event sets so that per-pass times can be collected without a host sync per frame
+    struct TimingSet {
+        cudaEvent_t ev[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        // [0],[1] light generation (its own stream) . [2] gather start . [3] march done . [4] list ready . [5] eval done . [6] resolve done
+        bool pending = false, lg_timed = false, open = false;
+    };
+    static constexpr int kTimingSets = 4;
+    TimingSet tset[kTimingSets];
+    int tcur = 0;
     cudaEvent_t tev[2] = {nullptr, nullptr};
-    vr_timings timings{};
-    bool timings_pending = false, lg_timed = false;
+    vr_timings timings{}, timings_sum{};
+    uint64_t timings_frames = 0;
 };
 
 namespace {
@@ -155,27 +181,139 @@ int validate_tile(vr_ctx* c, const vr_tile* t, vr_tile* out) {
     return VR_OK;
 }
 
-int finalize_timings(vr_ctx* c) {
-    if (!c->timings_pending) return VR_OK;
-    VR_CUDA(c, cudaEventSynchronize(c->ev[7]));
+// ---- timing ring. A frame (or a lone dispatch) owns one TimingSet; its events are read when the set is reused or when
+// the caller asks, so collecting per-pass times costs no host synchronisation per frame.
+int finalize_set(vr_ctx* c, vr_ctx::TimingSet& t) {
+    if (!t.pending) return VR_OK;
+    VR_CUDA(c, cudaEventSynchronize(t.ev[6]));
+    if (t.lg_timed) VR_CUDA(c, cudaEventSynchronize(t.ev[1]));
+    vr_timings m{};
     float ms = 0;
-    if (c->lg_timed) {
-        cudaEventElapsedTime(&ms, c->ev[0], c->ev[1]);
-        c->timings.light_gen_ms = ms;
+    if (t.lg_timed) {
+        cudaEventElapsedTime(&ms, t.ev[0], t.ev[1]);
+        m.light_gen_ms = ms;
     }
-    cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]);
-    c->timings.prepare_ms = ms;
-    cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]);
-    float m1 = ms;
-    cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]);
-    c->timings.march_ms = m1 + ms;
-    cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]);
-    c->timings.eval_ms = ms;
-    cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]);
-    c->timings.resolve_ms = ms;
-    cudaEventElapsedTime(&ms, c->lg_timed ? c->ev[0] : c->ev[2], c->ev[7]);
-    c->timings.total_ms = ms;
-    c->timings_pending = false;
+    cudaEventElapsedTime(&ms, t.ev[2], t.ev[3]);
+    m.march_ms = ms;
+    cudaEventElapsedTime(&ms, t.ev[3], t.ev[4]);
+    m.prepare_ms = ms;
+    cudaEventElapsedTime(&ms, t.ev[4], t.ev[5]);
+    m.eval_ms = ms;
+    cudaEventElapsedTime(&ms, t.ev[5], t.ev[6]);
+    m.resolve_ms = ms;
+    cudaEventElapsedTime(&ms, t.ev[2], t.ev[6]);
+    m.total_ms = ms;
+    c->timings = m;
+    c->timings_sum.light_gen_ms += m.light_gen_ms, c->timings_sum.march_ms += m.march_ms;
+    c->timings_sum.prepare_ms += m.prepare_ms, c->timings_sum.eval_ms += m.eval_ms;
+    c->timings_sum.resolve_ms += m.resolve_ms, c->timings_sum.total_ms += m.total_ms;
+    c->timings_frames++;
+    t.pending = t.lg_timed = t.open = false;
+    return VR_OK;
+}
+int finalize_timings(vr_ctx* c) {
+    for (int k = 1; k <= vr_ctx::kTimingSets; k++) {  // oldest first
+        int rc = finalize_set(c, c->tset[(c->tcur + k) % vr_ctx::kTimingSets]);
+        if (rc != VR_OK) return rc;
+    }
+    return VR_OK;
+}
+// the set the next dispatch records into: the open one (light generation already recorded), else a fresh one
+int open_timing_set(vr_ctx* c, vr_ctx::TimingSet** out) {
+    vr_ctx::TimingSet* t = &c->tset[c->tcur];
+    if (!t->open) {
+        c->tcur = (c->tcur + 1) % vr_ctx::kTimingSets;
+        t = &c->tset[c->tcur];
+        int rc = finalize_set(c, *t);
+        if (rc != VR_OK) return rc;
+        t->open = true;
+    }
+    *out = t;
+    return VR_OK;
+}
+
+// Upper bound of the expanded ray/beam list, so that its buffer can be sized without reading the device: every light
+// end point is the light source or a scatter position inside the root bbox (light_gen.comp:74-84), hence no segment is
+// longer than the diagonal of the world-space box around both. 0 = no usable bound.
+uint64_t expand_bound(const vr_ctx* c) {
+    if (c->lights_external) return 0;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    const VrGridDev& g = c->gdev;
+    for (int corner = 0; corner < 8; corner++) {
+        const double i = (corner & 1) ? (double)g.bmax[0] + 1.0 : (double)g.bmin[0];
+        const double j = (corner & 2) ? (double)g.bmax[1] + 1.0 : (double)g.bmin[1];
+        const double k = (corner & 4) ? (double)g.bmax[2] + 1.0 : (double)g.bmin[2];
+        for (int a = 0; a < 3; a++) {
+            const double w = i * g.mat[3 * a] + j * g.mat[3 * a + 1] + k * g.mat[3 * a + 2] + g.vec[a];
+            lo[a] = w < lo[a] ? w : lo[a], hi[a] = w > hi[a] ? w : hi[a];
+        }
+    }
+    for (int a = 0; a < 3; a++) {
+        const double w = c->ubo.lightSourceWorldPos[a];
+        lo[a] = w < lo[a] ? w : lo[a], hi[a] = w > hi[a] ? w : hi[a];
+    }
+    const double diag = sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
+    const double steps = floor(diag * 1.001 / (double)c->ubo.lightRayStepSize) + 2.0;
+    const double bound = steps * (double)c->ubo.maxLights;
+    if (!(bound == bound) || bound > (double)(1ull << 26)) return 0;
+    return (uint64_t)bound;
+}
+
+// light generation on stream `st` (shaders/light_gen.comp), timed into `t`
+int enqueue_light_gen(vr_ctx* c, cudaStream_t st, vr_ctx::TimingSet* t, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz,
+                      vr_lightgen_variant variant) {
+    const uint64_t nphot = (uint64_t)gx * 4 * gy * 4 * gz;
+    cudaEventRecord(t->ev[0], st);
+    t->lg_timed = true;
+    if (algo != VR_ALGO_PATH) {  // path_light_gen.comp has an empty main (shaders/path_light_gen.comp:9-11)
+        const uint32_t nx = gx * 4, ny = gy * 4, nz = gz;  // local_size 4x4x1 (shaders/light_gen.comp:7)
+        VR_CUDA(c, c->photon_counts.reserve(nphot));
+        VR_CUDA(c, c->photon_offsets.reserve(nphot));
+        VR_CUDA(c, c->lg_scan_tmp.reserve((nphot + 4095) / 4096 + 1));
+        VR_CUDA(c, c->lg_slab.reserve(nphot * vrk_lightgen_local_capacity() * 2));
+        const int keep = (variant == VR_LG_KEEP_ORIGIN) ? 1 : 0;
+        vrk_lightgen(st, c->gdev, c->ubo, keep, nx, ny, nz, c->photon_counts.p, c->photon_offsets.p, c->photon_total,
+                     c->lg_scan_tmp.p, c->lg_slab.p, c->lights.p, c->counter);
+        c->lights_external = false;
+    }
+    cudaEventRecord(t->ev[1], st);
+    return VR_OK;
+}
+
+// per-frame scalars -> pinned host memory, without blocking (vr_get_counters waits for ev_scalars)
+int enqueue_scalars(vr_ctx* c, cudaStream_t st, bool have_march) {
+    vr_ctx::Scalars* h = c->scalars_host;
+    VR_CUDA(c, cudaMemcpyAsync(&h->nsamples, c->totals, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    if (have_march) VR_CUDA(c, cudaMemcpyAsync(&h->S_ref, c->wc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    VR_CUDA(c, cudaMemcpyAsync(&h->light_count, &c->counter->lightCount, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    VR_CUDA(c, cudaMemcpyAsync(&h->overflow, c->expand_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    VR_CUDA(c, cudaEventRecord(c->ev_scalars, st));
+    c->counters_pending = true;
+    c->counters_have_march = have_march;
+    return VR_OK;
+}
+int finalize_counters(vr_ctx* c) {
+    if (!c->counters_pending) return VR_OK;
+    VR_CUDA(c, cudaEventSynchronize(c->ev_scalars));
+    c->counters_pending = false;
+    const vr_ctx::Scalars& h = *c->scalars_host;
+    if (c->counters_have_march) {
+        c->last_counters.S_ref = c->cached_S[0] = h.S_ref;
+        c->last_counters.S_eff = c->cached_S[1] = h.S_eff;
+    }
+    if (h.overflow) return fail(c, VR_E_STATE, "internal: the expanded light list overflowed its buffer");
+    if (c->last_algo == VR_ALGO_PATH) {
+        c->last_counters.E = h.S_eff;
+        return VR_OK;
+    }
+    if (c->counters_have_march && h.nsamples != c->nsamples_used)
+        return fail(c, VR_E_STATE, "internal: camera sample count %llu differs from the cached %llu", (unsigned long long)h.nsamples,
+                    (unsigned long long)c->nsamples_used);
+    uint32_t lc = h.light_count;
+    if (lc > c->light_capacity) lc = c->light_capacity;
+    c->last_counters.light_count = lc;
+    c->last_counters.eval_lights = h.neval;
+    c->last_counters.E = c->nsamples_used * h.neval;
     return VR_OK;
 }
 
@@ -217,10 +355,20 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaMalloc(&c->totals, 2 * sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMallocHost(&c->totals_host, 4 * sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMalloc(&c->wc, sizeof(VrWorkCounters)));
-    VR_CREATE_CUDA(cudaMallocHost(&c->wc_host, sizeof(VrWorkCounters)));
+    VR_CREATE_CUDA(cudaMalloc(&c->expand_overflow, sizeof(uint32_t)));
+    VR_CREATE_CUDA(cudaMemsetAsync(c->expand_overflow, 0, sizeof(uint32_t), c->stream));
+    VR_CREATE_CUDA(cudaMemsetAsync(c->totals, 0, 2 * sizeof(unsigned long long), c->stream));
+    VR_CREATE_CUDA(cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), c->stream));
+    VR_CREATE_CUDA(cudaMallocHost(&c->scalars_host, sizeof(vr_ctx::Scalars)));
+    memset(c->scalars_host, 0, sizeof(vr_ctx::Scalars));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_scalars, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMemsetAsync(c->eval_redo, 0, sizeof(unsigned long long), c->stream));
-    for (int i = 0; i < 8; i++) VR_CREATE_CUDA(cudaEventCreate(&c->ev[i]));
+    for (int k = 0; k < vr_ctx::kTimingSets; k++)
+        for (int i = 0; i < 7; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tset[k].ev[i]));
     for (int i = 0; i < 2; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tev[i]));
 #undef VR_CREATE_CUDA
     vr_default_params(&c->ubo, 0, 0);
@@ -240,7 +388,10 @@ int vr_destroy(vr_ctx* c) {
     if (!c) return VR_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
     if (c->grid) cudaFree(c->grid);
+    c->lg_scan_tmp.release();
+    c->lg_slab.release();
     c->lights.release();
     c->photon_counts.release();
     c->photon_offsets.release();
@@ -258,13 +409,19 @@ int vr_destroy(vr_ctx* c) {
     if (c->totals) cudaFree(c->totals);
     if (c->totals_host) cudaFreeHost(c->totals_host);
     if (c->wc) cudaFree(c->wc);
-    if (c->wc_host) cudaFreeHost(c->wc_host);
+    if (c->expand_overflow) cudaFree(c->expand_overflow);
+    if (c->scalars_host) cudaFreeHost(c->scalars_host);
+    if (c->ev_scalars) cudaEventDestroy(c->ev_scalars);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_lg_done) cudaEventDestroy(c->ev_lg_done);
+    if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     if (c->eval_redo) cudaFree(c->eval_redo);
     if (c->accum) cudaFree(c->accum);
     if (c->rgba8) cudaFree(c->rgba8);
     if (c->frame_color) cudaFree(c->frame_color);
-    for (int i = 0; i < 8; i++)
-        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (int k = 0; k < vr_ctx::kTimingSets; k++)
+        for (int i = 0; i < 7; i++)
+            if (c->tset[k].ev[i]) cudaEventDestroy(c->tset[k].ev[i]);
     for (int i = 0; i < 2; i++)
         if (c->tev[i]) cudaEventDestroy(c->tev[i]);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -413,6 +570,8 @@ int vr_write_lights(vr_ctx* c, const vr_ray_light* lights, uint32_t count) {
     if (count && !lights) return fail(c, VR_E_ARG, "vr_write_lights: NULL lights");
     VR_CUDA(c, cudaSetDevice(c->device));
     if (count) VR_CUDA(c, cudaMemcpyAsync(c->lights.p, lights, (size_t)count * sizeof(vr_ray_light), cudaMemcpyHostToDevice, c->stream));
+    c->lights_external = true;
+    c->external_count = count;
     VrLightCounter h{count, 0u, (unsigned long long)count};
     VR_CUDA(c, cudaMemcpyAsync(c->counter, &h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -427,28 +586,26 @@ int vr_clear_image(vr_ctx* c) {
     return check_stream(c);
 }
 
-int vr_dispatch_light_gen(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant) {
-    if (!c) return VR_E_ARG;
+static int check_light_gen_args(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz) {
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if ((int)algo < 0 || (int)algo > 4) return fail(c, VR_E_ARG, "unknown algorithm %d", (int)algo);
     if (gx == 0 || gy == 0 || gz == 0) return fail(c, VR_E_ARG, "dispatch dimensions must be >= 1");
     const uint64_t nphot = (uint64_t)gx * 4 * gy * 4 * gz;
     if (nphot > (1ull << 28)) return fail(c, VR_E_ARG, "%llu photons exceed the supported dispatch size", (unsigned long long)nphot);
     if (c->ubo.maxLights > c->light_capacity) return fail(c, VR_E_CAPACITY, "maxLights %u exceeds capacity %u", c->ubo.maxLights, c->light_capacity);
+    return VR_OK;
+}
+
+int vr_dispatch_light_gen(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant) {
+    if (!c) return VR_E_ARG;
+    int rc = check_light_gen_args(c, algo, gx, gy, gz);
+    if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
-    cudaEventRecord(c->ev[0], c->stream);
-    c->lg_timed = true;
-    if (algo != VR_ALGO_PATH) {  // path_light_gen.comp has an empty main (shaders/path_light_gen.comp:9-11)
-        const uint32_t nx = gx * 4, ny = gy * 4, nz = gz;  // local_size 4x4x1 (shaders/light_gen.comp:7)
-        VR_CUDA(c, c->photon_counts.reserve(nphot));
-        VR_CUDA(c, c->photon_offsets.reserve(nphot));
-        VR_CUDA(c, c->scan_tmp.reserve((nphot + 4095) / 4096 + 1));
-        const int keep = (variant == VR_LG_KEEP_ORIGIN) ? 1 : 0;
-        vrk_lightgen_count(c->stream, c->gdev, c->ubo, keep, nx, ny, nz, c->photon_counts.p);
-        vrk_scan_u32(c->stream, c->photon_counts.p, c->photon_offsets.p, c->photon_total, nphot, c->scan_tmp.p);
-        vrk_lightgen_emit(c->stream, c->gdev, c->ubo, keep, nx, ny, nz, c->photon_offsets.p, c->photon_total, c->lights.p, c->counter);
-    }
-    cudaEventRecord(c->ev[1], c->stream);
+    vr_ctx::TimingSet* t = nullptr;
+    rc = open_timing_set(c, &t);
+    if (rc != VR_OK) return rc;
+    rc = enqueue_light_gen(c, c->stream, t, algo, gx, gy, gz, variant);
+    if (rc != VR_OK) return rc;
     return check_stream(c);
 }
 
@@ -467,107 +624,119 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     cudaStream_t st = c->stream;
     const float tan_scale = vr_fov_scale(c->ubo.fov);
     const uint64_t npix = (uint64_t)tile.w * tile.h;
+    vr_ctx::TimingSet* t = nullptr;
+    rc = open_timing_set(c, &t);
+    if (rc != VR_OK) return rc;
+    rc = finalize_counters(c);  // a pending error of the previous frame surfaces here
+    if (rc != VR_OK) return rc;
     memset(&c->last_counters, 0, sizeof(c->last_counters));
+    c->last_algo = algo;
 
     if (algo == VR_ALGO_PATH) {
-        cudaEventRecord(c->ev[2], st);
-        cudaEventRecord(c->ev[3], st);
-        cudaEventRecord(c->ev[4], st);
-        cudaEventRecord(c->ev[5], st);
+        cudaEventRecord(t->ev[2], st);
+        cudaEventRecord(t->ev[3], st);
+        if (c->lg_in_flight) {
+            VR_CUDA(c, cudaStreamWaitEvent(st, c->ev_lg_done, 0));
+            c->lg_in_flight = false;
+        }
+        cudaEventRecord(t->ev[4], st);
         VR_CUDA(c, cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), st));
         vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->frame_color, c->accum, c->rgba8, c->wc);
-        cudaEventRecord(c->ev[6], st);
-        VR_CUDA(c, cudaMemcpyAsync(c->wc_host, c->wc, sizeof(VrWorkCounters), cudaMemcpyDeviceToHost, st));
-        cudaEventRecord(c->ev[7], st);
-        c->timings_pending = true;
-        VR_CUDA(c, cudaStreamSynchronize(st));
-        c->last_counters.S_ref = c->wc_host->S_ref;
-        c->last_counters.S_eff = c->wc_host->S_eff;
-        c->last_counters.E = c->wc_host->S_eff;
+        cudaEventRecord(t->ev[5], st);
+        cudaEventRecord(t->ev[6], st);
+        t->pending = true, t->open = false;
+        rc = enqueue_scalars(c, st, true);
+        if (rc != VR_OK) return rc;
         return check_stream(c);
     }
 
-    // ---- light list for the evaluation kernel
-    cudaEventRecord(c->ev[2], st);
-    const bool expand = (algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM);
-    // lightCount lives on the device; launches that must not wait for it are sized by the buffer capacity
-    const uint32_t nl_launch = c->light_capacity;
-    if (expand) {
-        VR_CUDA(c, c->light_steps.reserve(nl_launch));
-        VR_CUDA(c, c->light_offsets.reserve(nl_launch));
-        VR_CUDA(c, c->scan_tmp.reserve((nl_launch + 4095) / 4096 + 1));
-        vrk_prepare_count_steps(st, c->lights.p, c->counter, c->ubo.lightRayStepSize, c->light_steps.p, nl_launch);
-        vrk_scan_u32(st, c->light_steps.p, c->light_offsets.p, c->totals + 1, nl_launch, c->scan_tmp.p);
-    }
-    cudaEventRecord(c->ev[3], st);
-
-    // ---- camera march: count -> scan (or reuse)
+    // ---- camera march first: it does not depend on the lights, so it overlaps light generation on the other stream
+    cudaEventRecord(t->ev[2], st);
     MarchKey key;
     key.grid_gen = c->grid_gen, key.tile = tile;
     key.dim[0] = c->width, key.dim[1] = c->height;
     memcpy(key.cam, c->ubo.cameraPos, sizeof(key.cam));
     key.fov = c->ubo.fov, key.maxd = c->ubo.rayMaxDistance, key.step = c->ubo.rayMarchingStepSize, key.absorb = c->ubo.absorptionCoefficient;
     key.valid = true;
-    const bool reuse = c->march_cache && (key == c->march_key);
+    const bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
+    const bool reuse = c->march_cache && same_key;
+    uint64_t nsamples = c->cached_samples;
     if (!reuse) {
-        c->march_key.valid = false;
         VR_CUDA(c, c->px_counts.reserve(npix));
         VR_CUDA(c, c->px_offsets.reserve(npix));
         VR_CUDA(c, c->scan_tmp.reserve((npix + 4095) / 4096 + 1));
         VR_CUDA(c, cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), st));
         vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, c->px_counts.p, nullptr, nullptr, c->wc);
         vrk_scan_u32(st, c->px_counts.p, c->px_offsets.p, c->totals + 0, npix, c->scan_tmp.p);
-        VR_CUDA(c, cudaMemcpyAsync(c->wc_host, c->wc, sizeof(VrWorkCounters), cudaMemcpyDeviceToHost, st));
-    }
-    cudaEventRecord(c->ev[4], st);
-    // one host round trip per frame: the two totals size the launches and buffers below
-    VR_CUDA(c, cudaMemcpyAsync(c->totals_host, c->totals, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-    VR_CUDA(c, cudaMemcpyAsync(c->totals_host + 2, &c->counter->lightCount, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    VR_CUDA(c, cudaStreamSynchronize(st));
-    uint32_t light_count_host = (uint32_t)(c->totals_host[2] & 0xFFFFFFFFull);
-    rc = check_stream(c);
-    if (rc != VR_OK) return rc;
-    const uint64_t nsamples = reuse ? c->cached_samples : c->totals_host[0];
-    if (light_count_host > c->light_capacity) light_count_host = c->light_capacity;
-    const uint64_t neval = expand ? c->totals_host[1] : (uint64_t)light_count_host;
-    if (neval > (1ull << 32)) return fail(c, VR_E_ARG, "expanded light list of %llu entries is too large (lightRayStepSize too small?)", (unsigned long long)neval);
-    VR_CUDA(c, c->eval_lights.reserve(neval + 1));
-    if (expand)
-        vrk_prepare_expand(st, c->lights.p, c->counter, c->ubo.lightRayStepSize, c->light_offsets.p, c->eval_lights.p, light_count_host, neval);
-    else
-        vrk_prepare_simple(st, c->lights.p, c->counter, algo == VR_ALGO_SPHERE ? 1 : 0, c->eval_lights.p, light_count_host);
-    if (!reuse) {
-        VR_CUDA(c, c->samples.reserve(nsamples + 1));
+        if (!same_key) {
+            // first gather with these rays: the sample total sizes the buffers, one blocking read. Later frames with
+            // the same camera/grid/tile march again (count and fill) but the total is known: no host round trip.
+            c->march_key.valid = false;
+            VR_CUDA(c, cudaMemcpyAsync(c->totals_host, c->totals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            VR_CUDA(c, cudaStreamSynchronize(st));
+            rc = check_stream(c);
+            if (rc != VR_OK) return rc;
+            nsamples = c->totals_host[0];
+            VR_CUDA(c, c->samples.reserve(nsamples + 1));
+        }
         vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
         c->cached_samples = nsamples;
         c->march_key = key;
-        c->last_counters.S_ref = c->wc_host->S_ref;
-        c->last_counters.S_eff = c->wc_host->S_eff;
-    } else {
-        c->last_counters.S_ref = c->wc_host->S_ref;
-        c->last_counters.S_eff = c->wc_host->S_eff;
     }
     VR_CUDA(c, c->contrib.reserve(nsamples + 1));
-    cudaEventRecord(c->ev[5], st);
+    c->nsamples_used = nsamples;
+    cudaEventRecord(t->ev[3], st);
+
+    // ---- light list for the evaluation kernels (needs the lights: join the light-generation stream)
+    if (c->lg_in_flight) {
+        VR_CUDA(c, cudaStreamWaitEvent(st, c->ev_lg_done, 0));
+        c->lg_in_flight = false;
+    }
+    const bool expand = (algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM);
+    // lightCount lives on the device: launches are sized by maxLights (the shader's cap), kernels read the counter
+    uint32_t nl_launch = c->lights_external ? c->external_count : c->ubo.maxLights;
+    if (nl_launch > c->light_capacity) nl_launch = c->light_capacity;
+    VR_CUDA(c, cudaMemsetAsync(c->expand_overflow, 0, sizeof(uint32_t), st));
+    if (expand) {
+        VR_CUDA(c, c->light_steps.reserve(nl_launch + 1));
+        VR_CUDA(c, c->light_offsets.reserve(nl_launch + 1));
+        VR_CUDA(c, c->scan_tmp.reserve((nl_launch + 4095) / 4096 + 1));
+        vrk_prepare_count_steps(st, c->lights.p, c->counter, c->ubo.lightRayStepSize, c->light_steps.p, nl_launch);
+        vrk_scan_u32(st, c->light_steps.p, c->light_offsets.p, c->totals + 1, nl_launch, c->scan_tmp.p);
+        uint64_t cap = expand_bound(c);
+        if (cap == 0) {  // no bound (lights written by the caller, or a tiny lightRayStepSize): read the total
+            VR_CUDA(c, cudaMemcpyAsync(c->totals_host + 1, c->totals + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+            VR_CUDA(c, cudaStreamSynchronize(st));
+            cap = c->totals_host[1];
+            if (cap > (1ull << 32)) return fail(c, VR_E_ARG, "expanded light list of %llu entries is too large (lightRayStepSize too small?)", (unsigned long long)cap);
+        }
+        VR_CUDA(c, c->eval_lights.reserve(cap + 1));
+        VR_CUDA(c, c->eval_lights2.reserve(2 * cap + 2));
+        vrk_prepare_expand(st, c->lights.p, c->counter, c->ubo.lightRayStepSize, c->light_offsets.p, c->eval_lights.p,
+                           c->eval_lights2.p, nl_launch, cap, c->expand_overflow);
+    } else {
+        VR_CUDA(c, c->eval_lights.reserve((uint64_t)nl_launch + 1));
+        VR_CUDA(c, c->eval_lights2.reserve(2 * (uint64_t)nl_launch + 2));
+        vrk_prepare_simple(st, c->lights.p, c->counter, algo == VR_ALGO_SPHERE ? 1 : 0, c->eval_lights.p, c->eval_lights2.p,
+                           nl_launch, c->totals + 1);
+    }
+    cudaEventRecord(t->ev[4], st);
+    rc = enqueue_scalars(c, st, !reuse);
+    if (rc != VR_OK) return rc;
+    if (reuse) c->last_counters.S_ref = c->cached_S[0], c->last_counters.S_eff = c->cached_S[1];
+
     // ---- evaluation (hot) + resolve
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
-    if (!sphere && c->eval_variant >= 1) {
-        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 10));
-        vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->contrib.p,
-                              c->eval_redo);
-    } else if (sphere && c->eval_variant >= 1) {
-        VR_CUDA(c, c->eval_lights2.reserve(2 * neval + 10));
-        vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights.p, c->eval_lights2.p, neval, c->ubo.beamRadius, c->contrib.p);
-    } else {
-        vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, neval, c->ubo.beamRadius, c->contrib.p);
-    }
-    cudaEventRecord(c->ev[6], st);
+    if (c->eval_variant == 0)
+        vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
+    else if (sphere)
+        vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
+    else
+        vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->contrib.p, c->eval_redo);
+    cudaEventRecord(t->ev[5], st);
     vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->frame_color, c->accum, c->rgba8);
-    cudaEventRecord(c->ev[7], st);
-    c->timings_pending = true;
-    c->last_counters.eval_lights = neval;
-    c->last_counters.light_count = light_count_host;
-    c->last_counters.E = nsamples * neval;
+    cudaEventRecord(t->ev[6], st);
+    t->pending = true, t->open = false;
     return check_stream(c);
 }
 
@@ -583,16 +752,29 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
     if (!c) return VR_E_ARG;
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    int rc = check_light_gen_args(c, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2]);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaSetDevice(c->device));
     c->ubo.frameCount += 1;  // src/main.cpp:712
-    int rc = vr_reset_lights(c);  // :722-728
+    rc = vr_reset_lights(c);  // :722-728
     if (rc != VR_OK) return rc;
     if (c->ubo.frameCount == 1) {  // :731
         rc = vr_clear_image(c);
         if (rc != VR_OK) return rc;
     }
-    rc = vr_dispatch_light_gen(c, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2], c->lg_variant);  // :811-814
+    // light generation (:811-814) runs on the auxiliary stream, concurrently with the camera march of the gather
+    // (:832-837), which does not read the lights; the gather joins before it builds its light list. The reference's
+    // compute->compute barrier (:817-829) is that join.
+    vr_ctx::TimingSet* t = nullptr;
+    rc = open_timing_set(c, &t);
     if (rc != VR_OK) return rc;
-    return vr_dispatch_compute_color(c, algo, tile_or_null);  // :832-837
+    VR_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+    VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+    rc = enqueue_light_gen(c, c->aux_stream, t, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2], c->lg_variant);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaEventRecord(c->ev_lg_done, c->aux_stream));
+    c->lg_in_flight = true;
+    return vr_dispatch_compute_color(c, algo, tile_or_null);
 }
 
 int vr_reset_accumulation(vr_ctx* c) {
@@ -604,7 +786,10 @@ int vr_reset_accumulation(vr_ctx* c) {
 int vr_sync(vr_ctx* c) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    int rc = finalize_counters(c);
+    if (rc != VR_OK) return rc;
     return check_stream(c);
 }
 
@@ -671,6 +856,9 @@ int vr_write_image_rgba8(vr_ctx* c, const uint8_t* in) {
 
 int vr_get_counters(vr_ctx* c, vr_counters* out) {
     if (!c || !out) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    int rc = finalize_counters(c);  // waits for the frame's scalars only (ready before the evaluation kernel starts)
+    if (rc != VR_OK) return rc;
     *out = c->last_counters;
     return VR_OK;
 }
@@ -681,6 +869,20 @@ int vr_get_timings(vr_ctx* c, vr_timings* out) {
     int rc = finalize_timings(c);
     if (rc != VR_OK) return rc;
     *out = c->timings;
+    return VR_OK;
+}
+
+int vr_get_timings_sum(vr_ctx* c, vr_timings* sum, uint64_t* frames, int reset) {
+    if (!c) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    int rc = finalize_timings(c);
+    if (rc != VR_OK) return rc;
+    if (sum) *sum = c->timings_sum;
+    if (frames) *frames = c->timings_frames;
+    if (reset) {
+        memset(&c->timings_sum, 0, sizeof(c->timings_sum));
+        c->timings_frames = 0;
+    }
     return VR_OK;
 }
 
@@ -717,6 +919,7 @@ int vr_row_sample_counts(vr_ctx* c, uint64_t* rows_out) {
 int vr_set_stream(vr_ctx* c, void* cuda_stream) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return VR_OK;
@@ -839,16 +1042,16 @@ int vr_cpu_test_render(vr_ctx* c, uint32_t width, uint32_t height, float* densit
     const float fov = 45.0;
     const float aspect = static_cast<float>(width) / height;
     const float scale = (float)tan(fov * 0.5 * M_PI / 180.0);
-    cudaEventRecord(c->ev[5], c->stream);
+    cudaEventRecord(c->tev[0], c->stream);
     vrk_cpu_test(c->stream, c->gdev, width, height, aspect, scale, d);
-    cudaEventRecord(c->ev[6], c->stream);
+    cudaEventRecord(c->tev[1], c->stream);
     cudaError_t e = cudaMemcpyAsync(density_out, d, (size_t)width * height * 4, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     float ms = 0;
-    cudaEventElapsedTime(&ms, c->ev[5], c->ev[6]);
+    cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
+    finalize_timings(c);
     memset(&c->timings, 0, sizeof(c->timings));
     c->timings.eval_ms = ms, c->timings.total_ms = ms;
-    c->timings_pending = false;
     cudaFree(d);
     if (e != cudaSuccess) return fail(c, VR_E_CUDA, "cpu_test render failed: %s", cudaGetErrorString(e));
     return check_stream(c);

@@ -2,7 +2,7 @@
 //
 // Pass structure of one frame (replaces the two Vulkan dispatches of src/main.cpp:811-837):
 //
-//   light generation   k_lightgen<COUNT> -> scan -> k_lightgen<EMIT>      shaders/light_gen.comp:9-100
+//   light generation   k_lightgen<LOCAL> -> scan -> k_lightgen_compact    shaders/light_gen.comp:9-100
 //   light expansion    k_prepare_* (ray/beam sub-points pre-expanded)     shaders/ray_compute_color.comp:13-20
 //   camera march       k_march<COUNT> -> scan -> k_march<FILL>            shaders/point_compute_color.comp:20-94
 //   evaluation (HOT)   k_eval<POINT|SPHERE>: samples x lights             shaders/common_functions.h:182-201
@@ -29,17 +29,25 @@ namespace {
 // light generation
 // =====================================================================================================
 // One photon per thread; photon index p = ((z*Ny)+y)*Nx + x is the canonical order.
-// COUNT: number of scatter events of photon p. EMIT: same walk, lights stored at base + offsets[p] + j while the
-// index is below maxLights (the shader's `if (index < maxLights)`); previousPosition only advances on a store.
-template <bool EMIT>
+// The shader appends with atomicAdd (light_gen.comp:79-87); a deterministic order needs every photon's light count
+// before any light can be placed. Instead of walking every photon twice (count, then emit), the walk runs ONCE:
+//   LOCAL    each photon stores its first VR_LG_LOCAL lights in a private slab and counts all its scatter events
+//   (scan of the counts -> offsets)
+//   k_lightgen_compact   copies slab entries whose global slot (base + offsets[p] + j) is below maxLights
+//   OVERFLOW photons with more than VR_LG_LOCAL events (rare: the mean is 2.4) walk again and store directly
+// A photon's `from` is the position of its previous STORED light; stored lights are a prefix of the photon's list (the
+// slot grows with j), so the slab's from/to chain equals the shader's `previousPosition` bookkeeping.
+#define VR_LG_LOCAL 16
+enum { VR_LG_MODE_LOCAL = 0, VR_LG_MODE_OVERFLOW = 1 };
+template <int MODE>
 __global__ void __launch_bounds__(64) k_lightgen(VrGridDev g, vr_ubo u, int keep_origin, uint32_t nx, uint32_t ny,
-                                                  uint32_t nz, uint32_t* __restrict__ counts,
+                                                  uint32_t nz, uint32_t* __restrict__ counts, float4* __restrict__ slab,
                                                   const unsigned long long* __restrict__ offsets,
-                                                  const unsigned long long* __restrict__ total,
                                                   vr_ray_light* __restrict__ lights, const VrLightCounter* counter) {
     const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t nphot = (uint64_t)nx * ny * nz;
     if (p >= nphot) return;
+    if (MODE == VR_LG_MODE_OVERFLOW && counts[p] <= VR_LG_LOCAL) return;
     const uint32_t x = (uint32_t)(p % nx), y = (uint32_t)((p / nx) % ny), z = (uint32_t)(p / ((uint64_t)nx * ny));
     VrSeed seed = {x * u.frameCount, y * u.frameCount, z * u.frameCount};
     const vr_f3 originW = vr_make3(u.lightSourceWorldPos[0], u.lightSourceWorldPos[1], u.lightSourceWorldPos[2]);
@@ -56,7 +64,8 @@ __global__ void __launch_bounds__(64) k_lightgen(VrGridDev g, vr_ubo u, int keep
     vr_f3 prev = originW;
     uint32_t n = 0;
     // the shader's atomicAdd continues from the counter's current value (0 after the per-frame reset)
-    unsigned long long slot = EMIT ? (unsigned long long)counter->lightCount + offsets[p] : 0ull;
+    unsigned long long slot = MODE == VR_LG_MODE_OVERFLOW ? (unsigned long long)counter->lightCount + offsets[p] : 0ull;
+    float4* mine = MODE == VR_LG_MODE_LOCAL ? slab + p * (2 * VR_LG_LOCAL) : nullptr;
     VrAcc acc;
     vr_acc_init(acc);
     while (hit && t < tmax && T > 0.001f && I > 0.01f) {
@@ -72,17 +81,18 @@ __global__ void __launch_bounds__(64) k_lightgen(VrGridDev g, vr_ubo u, int keep
                     const float q1 = vr_randf_inc(seed);
                     const float q2 = vr_randf_inc(seed);
                     const vr_f3 nd = vr_random_dir(q1, q2);
-                    if (EMIT) {
-                        const vr_f3 w = vr_index_to_world(g, cur);
-                        if (slot < (unsigned long long)u.maxLights) {
-                            vr_ray_light L;
-                            L.positionFrom[0] = prev.x, L.positionFrom[1] = prev.y, L.positionFrom[2] = prev.z;
-                            L._pad0 = 0.0f;
-                            L.positionTo[0] = w.x, L.positionTo[1] = w.y, L.positionTo[2] = w.z;
-                            L.intensity = I;
+                    const vr_f3 w = vr_index_to_world(g, cur);
+                    if (MODE == VR_LG_MODE_LOCAL) {
+                        if (n < VR_LG_LOCAL) {
+                            mine[2 * n] = make_float4(prev.x, prev.y, prev.z, 0.0f);
+                            mine[2 * n + 1] = make_float4(w.x, w.y, w.z, I);
+                            prev = w;
+                        }
+                    } else {
+                        if (slot < (unsigned long long)u.maxLights) {  // light_gen.comp:80-84
                             float4* dst = reinterpret_cast<float4*>(lights + slot);
-                            dst[0] = make_float4(L.positionFrom[0], L.positionFrom[1], L.positionFrom[2], 0.0f);
-                            dst[1] = make_float4(L.positionTo[0], L.positionTo[1], L.positionTo[2], L.intensity);
+                            dst[0] = make_float4(prev.x, prev.y, prev.z, 0.0f);
+                            dst[1] = make_float4(w.x, w.y, w.z, I);
                             prev = w;
                         }
                         slot++;
@@ -99,7 +109,22 @@ __global__ void __launch_bounds__(64) k_lightgen(VrGridDev g, vr_ubo u, int keep
         t = vr_add(t, step);
         cur = vr_add3(o, vr_scale3(d, t));
     }
-    if (!EMIT) counts[p] = n;
+    if (MODE == VR_LG_MODE_LOCAL) counts[p] = n;
+}
+// slab entry j of photon p -> lights[base + offsets[p] + j] while that slot is below maxLights
+__global__ void __launch_bounds__(256) k_lightgen_compact(vr_ubo u, uint64_t nphot, const uint32_t* __restrict__ counts,
+                                                          const unsigned long long* __restrict__ offsets,
+                                                          const float4* __restrict__ slab, vr_ray_light* __restrict__ lights,
+                                                          const VrLightCounter* counter) {
+    const uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t p = e / VR_LG_LOCAL;
+    const uint32_t j = (uint32_t)(e % VR_LG_LOCAL);
+    if (p >= nphot || j >= counts[p]) return;
+    const unsigned long long slot = (unsigned long long)counter->lightCount + offsets[p] + j;
+    if (slot >= (unsigned long long)u.maxLights) return;
+    float4* dst = reinterpret_cast<float4*>(lights + slot);
+    dst[0] = slab[e * 2];
+    dst[1] = slab[e * 2 + 1];
 }
 // Counter value after the dispatch: every scatter did atomicAdd(lightCount, 1); any index >= maxLights stored
 // `lightCount = maxLights` (light_gen.comp:85-87). Net effect: min(old + total, maxLights) once anything was emitted.
@@ -183,20 +208,29 @@ __global__ void __launch_bounds__(1024) k_scan_add(unsigned long long* __restric
 // light list expansion
 // =====================================================================================================
 #define VR_INV_4PI 0.07957747154594767f
-// point: positionTo (point_compute_color.comp:12); sphere: positionFrom (sphere_compute_color.comp:12)
+// The evaluation kernels read two layouts of the expanded list: VrEvalLight (x,y,z,I/4pi; scalar kernel) and the
+// duplicated form (x,x,y,y)(z,z,w,w) whose register pairs feed the FP32x2 instructions directly from broadcast LDS.128.
+__device__ __forceinline__ void store_eval_light(VrEvalLight* __restrict__ out, float4* __restrict__ out2, uint64_t i, float x,
+                                                 float y, float z, float w) {
+    reinterpret_cast<float4*>(out)[i] = make_float4(x, y, z, w);
+    out2[2 * i] = make_float4(x, x, y, y);
+    out2[2 * i + 1] = make_float4(z, z, w, w);
+}
+// point: positionTo (point_compute_color.comp:12); sphere: positionFrom (sphere_compute_color.comp:12).
+// Launched over the buffer capacity (lightCount lives on the device); *neval receives the list length.
 __global__ void k_prepare_simple(const vr_ray_light* __restrict__ lights, const VrLightCounter* __restrict__ counter,
-                                 int use_from, VrEvalLight* __restrict__ out, uint32_t capacity) {
+                                 int use_from, VrEvalLight* __restrict__ out, float4* __restrict__ out2, uint32_t capacity,
+                                 unsigned long long* __restrict__ neval) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t n = counter->lightCount;
     if (n > capacity) n = capacity;
+    if (i == 0) *neval = n;
     if (i >= n) return;
     const float4* src = reinterpret_cast<const float4*>(lights + i);
     const float4 a = src[0], b = src[1];
-    VrEvalLight e;
-    if (use_from) e.x = a.x, e.y = a.y, e.z = a.z;
-    else e.x = b.x, e.y = b.y, e.z = b.z;
-    e.i4pi = b.w * VR_INV_4PI;
-    reinterpret_cast<float4*>(out)[i] = make_float4(e.x, e.y, e.z, e.i4pi);
+    const float w = b.w * VR_INV_4PI;
+    if (use_from) store_eval_light(out, out2, i, a.x, a.y, a.z, w);
+    else store_eval_light(out, out2, i, b.x, b.y, b.z, w);
 }
 // amountOfSteps = uint(length(to - from) / lightRayStepSize)   (ray_compute_color.comp:13-15)
 __device__ __forceinline__ uint32_t ray_steps(const float4 a, const float4 b, float lrs, vr_f3* dir) {
@@ -221,10 +255,11 @@ __global__ void k_prepare_count_steps(const vr_ray_light* __restrict__ lights, c
     steps[i] = s;
 }
 // sub-point s of light i: from + (float(s) * lrs) * dir, intensity I / float(n)   (ray_compute_color.comp:16-20)
+// One block per light slot (launched over the capacity). *overflow is set when the list does not fit out_capacity.
 __global__ void k_prepare_expand(const vr_ray_light* __restrict__ lights, const VrLightCounter* __restrict__ counter,
                                  float lrs, const unsigned long long* __restrict__ offsets, VrEvalLight* __restrict__ out,
-                                 uint32_t capacity, uint64_t out_capacity) {
-    const uint32_t i = blockIdx.x;  // one block per light
+                                 float4* __restrict__ out2, uint32_t capacity, uint64_t out_capacity, uint32_t* __restrict__ overflow) {
+    const uint32_t i = blockIdx.x;
     uint32_t n = counter->lightCount;
     if (n > capacity) n = capacity;
     if (i >= n) return;
@@ -236,11 +271,12 @@ __global__ void k_prepare_expand(const vr_ray_light* __restrict__ lights, const 
     const float pointIntensity = vr_div(b.w, vr_u2f(steps));
     const float i4pi = pointIntensity * VR_INV_4PI;
     const unsigned long long off = offsets[i];
+    if (off + steps > out_capacity && threadIdx.x == 0) *overflow = 1u;
     for (uint32_t s = threadIdx.x; s < steps; s += blockDim.x) {
         if (off + s >= out_capacity) break;
         const float f = vr_mul(vr_i2f((int32_t)s), lrs);
-        reinterpret_cast<float4*>(out)[off + s] =
-            make_float4(vr_add(a.x, vr_mul(f, dir.x)), vr_add(a.y, vr_mul(f, dir.y)), vr_add(a.z, vr_mul(f, dir.z)), i4pi);
+        store_eval_light(out, out2, off + s, vr_add(a.x, vr_mul(f, dir.x)), vr_add(a.y, vr_mul(f, dir.y)),
+                         vr_add(a.z, vr_mul(f, dir.z)), i4pi);
     }
 }
 
@@ -352,9 +388,11 @@ constexpr int EVAL_TILE = 1024;  // lights per shared-memory stage (16 KB)
 // amortised over the S samples of the thread.
 template <bool SPHERE, int S>
 __global__ void __launch_bounds__(EVAL_THREADS) k_eval(const VrSample* __restrict__ samples, uint64_t nsamples,
-                                                        const VrEvalLight* __restrict__ lights, uint64_t nlights, float radius,
+                                                        const VrEvalLight* __restrict__ lights,
+                                                        const unsigned long long* __restrict__ nlights_dev, float radius,
                                                         float* __restrict__ out) {
     __shared__ __align__(128) float4 stage[2][EVAL_TILE];
+    const uint64_t nlights = *nlights_dev;  // list length lives on the device (no host round trip per frame)
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
     const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
@@ -430,24 +468,17 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval(const VrSample* __restric
 // FP32 operations per issue slot. The baseline kernel above is issue-bound (ncu r01: 9.3 instructions per evaluation,
 // issue slots 75 % busy, XU pipe 65 %); packing the distance computation of two samples of the same thread halves its
 // issue cost (6 -> 3 slots per evaluation), leaving the MUFU.RCP rate (16/clk/SM) as the next ceiling.
-// The light tile is stored duplicated in shared memory, (x,x,y,y)(z,z,w,w), so that both halves of every register pair
-// come straight from two broadcast LDS.128.
+// The light list is stored duplicated, (x,x,y,y)(z,z,w,w) (store_eval_light), so that both halves of every register
+// pair come straight from two broadcast LDS.128.
 constexpr int EVAL2_TILE = 512;  // lights per stage: 512 * 32 B = 16 KB
-
-// entries [n, npad) are padding: zero intensity, far away (d2 ~ 3e12, contribution +0)
-__global__ void k_dup_lights(const VrEvalLight* __restrict__ in, float4* __restrict__ out, uint64_t n, uint64_t npad) {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npad) return;
-    const float4 q = i < n ? reinterpret_cast<const float4*>(in)[i] : make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.0f);
-    out[2 * i] = make_float4(q.x, q.x, q.y, q.y);
-    out[2 * i + 1] = make_float4(q.z, q.z, q.w, q.w);
-}
 
 template <int S>  // S samples per thread, S even
 __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __restrict__ samples, uint64_t nsamples,
-                                                              const float4* __restrict__ lights2, uint64_t nlights,
+                                                              const float4* __restrict__ lights2,
+                                                              const unsigned long long* __restrict__ nlights_dev,
                                                               float* __restrict__ out) {
     constexpr int P = S / 2;
+    const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
@@ -530,9 +561,11 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
 // evaluations: FMA pipe 17 cycles, XU pipe 16 cycles per evaluation.
 template <int S>
 __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample* __restrict__ samples, uint64_t nsamples,
-                                                                   const float4* __restrict__ lights2, uint64_t nlights, float radius,
+                                                                   const float4* __restrict__ lights2,
+                                                                   const unsigned long long* __restrict__ nlights_dev, float radius,
                                                                    float* __restrict__ out) {
     constexpr int P = S / 2;
+    const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
@@ -682,9 +715,11 @@ __device__ __forceinline__ void eval_pass_packed(float4 (&stage)[2][2 * EVAL2_TI
 
 template <int S, int MINB, int UNROLL>  // S samples per thread (even), MINB resident CTAs per SM
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSample* __restrict__ samples, uint64_t nsamples,
-                                                              const float4* __restrict__ lights2, uint64_t nlights,
+                                                              const float4* __restrict__ lights2,
+                                                              const unsigned long long* __restrict__ nlights_dev,
                                                               float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
     constexpr int P = S / 2;
+    const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
@@ -1027,20 +1062,19 @@ double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters) {
 // =====================================================================================================
 // launchers
 // =====================================================================================================
-void vrk_lightgen_count(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
-                        uint32_t nz, uint32_t* counts) {
-    VR_COUNT(1);
+void vrk_lightgen(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny, uint32_t nz,
+                  uint32_t* counts, unsigned long long* offsets, unsigned long long* total, unsigned long long* scan_tmp,
+                  float4* slab, vr_ray_light* lights, VrLightCounter* counter) {
+    VR_COUNT(4);
     const uint64_t n = (uint64_t)nx * ny * nz;
-    k_lightgen<false><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, counts, nullptr, nullptr, nullptr, nullptr);
-}
-void vrk_lightgen_emit(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
-                       uint32_t nz, const unsigned long long* offsets, const unsigned long long* total, vr_ray_light* lights,
-                       VrLightCounter* counter) {
-    VR_COUNT(2);
-    const uint64_t n = (uint64_t)nx * ny * nz;
-    k_lightgen<true><<<(unsigned)((n + 63) / 64), 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, nullptr, offsets, total, lights, counter);
+    const unsigned blocks = (unsigned)((n + 63) / 64);
+    k_lightgen<VR_LG_MODE_LOCAL><<<blocks, 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, counts, slab, nullptr, nullptr, nullptr);
+    vrk_scan_u32(st, counts, offsets, total, n, scan_tmp);
+    k_lightgen_compact<<<(unsigned)((n * VR_LG_LOCAL + 255) / 256), 256, 0, st>>>(u, n, counts, offsets, slab, lights, counter);
+    k_lightgen<VR_LG_MODE_OVERFLOW><<<blocks, 64, 0, st>>>(g, u, keep_origin, nx, ny, nz, counts, nullptr, offsets, lights, counter);
     k_lightgen_finish<<<1, 1, 0, st>>>(u, total, counter);
 }
+uint32_t vrk_lightgen_local_capacity() { return VR_LG_LOCAL; }
 void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, unsigned long long* total, uint64_t n,
                   unsigned long long* tmp) {
     VR_COUNT(3);
@@ -1054,10 +1088,9 @@ void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, 
     k_scan_add<<<(unsigned)nblocks, 1024, 0, st>>>(out, tmp, n);
 }
 void vrk_prepare_simple(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, int use_from,
-                        VrEvalLight* out, uint32_t capacity) {
+                        VrEvalLight* out, float4* out2, uint32_t capacity, unsigned long long* neval) {
     VR_COUNT(1);
-    if (!capacity) return;
-    k_prepare_simple<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, use_from, out, capacity);
+    k_prepare_simple<<<(capacity + 255) / 256 + (capacity == 0), 256, 0, st>>>(lights, counter, use_from, out, out2, capacity, neval);
 }
 void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
                              uint32_t* steps, uint32_t capacity) {
@@ -1066,10 +1099,11 @@ void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const 
     k_prepare_count_steps<<<(capacity + 255) / 256, 256, 0, st>>>(lights, counter, lrs, steps, capacity);
 }
 void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
-                        const unsigned long long* offsets, VrEvalLight* out, uint32_t capacity, uint64_t out_capacity) {
+                        const unsigned long long* offsets, VrEvalLight* out, float4* out2, uint32_t capacity,
+                        uint64_t out_capacity, uint32_t* overflow) {
     VR_COUNT(1);
     if (!capacity) return;
-    k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, capacity, out_capacity);
+    k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, out2, capacity, out_capacity, overflow);
 }
 void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
@@ -1080,39 +1114,36 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
     else
         k_march<false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
 }
-void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                           float4* lights2, uint64_t nlights, float* out, unsigned long long* redo_count) {
+void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const float4* lights2,
+                           const unsigned long long* nlights_dev, float* out, unsigned long long* redo_count) {
     if (nsamples == 0) return;
-    VR_COUNT(2);
-    const uint64_t npad = (nlights + 3) / 4 * 4;
-    if (nlights) k_dup_lights<<<(unsigned)((npad + 255) / 256), 256, 0, st>>>(lights, lights2, nlights, npad);
+    VR_COUNT(1);
     auto grid = [&](int S) { return (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S)); };
     switch (variant) {
-        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, npad, out, redo_count); break;
-        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, npad, out, redo_count); break;
-        default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, out); break;
+        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out, redo_count); break;
+        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out, redo_count); break;
+        default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out); break;
     }
 }
-void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                            float4* lights2, uint64_t nlights, float radius, float* out) {
+void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
+                            const unsigned long long* nlights_dev, float radius, float* out) {
     if (nsamples == 0) return;
-    VR_COUNT(2);
+    VR_COUNT(1);
     constexpr int S = 8;
-    if (nlights) k_dup_lights<<<(unsigned)((nlights + 255) / 256), 256, 0, st>>>(lights, lights2, nlights, nlights);
     const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S));
-    k_eval_sphere2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights, radius, out);
+    k_eval_sphere2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, radius, out);
 }
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-              uint64_t nlights, float radius, float* out) {
-    VR_COUNT(1);
+              const unsigned long long* nlights_dev, float radius, float* out) {
     if (nsamples == 0) return;
+    VR_COUNT(1);
     constexpr int S = 8;
     const uint64_t per_cta = (uint64_t)EVAL_THREADS * S;
     const unsigned grid = (unsigned)((nsamples + per_cta - 1) / per_cta);
     if (sphere)
-        k_eval<true, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights, radius, out);
+        k_eval<true, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights_dev, radius, out);
     else
-        k_eval<false, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights, radius, out);
+        k_eval<false, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights_dev, radius, out);
 }
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8) {

@@ -26,36 +26,40 @@ struct VrWorkCounters {
     unsigned long long S_ref, S_eff;
 };
 
-// ---- light generation (shaders/light_gen.comp and variants)
-void vrk_lightgen_count(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
-                        uint32_t nz, uint32_t* counts);
-void vrk_lightgen_emit(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny,
-                       uint32_t nz, const unsigned long long* offsets, const unsigned long long* total, vr_ray_light* lights,
-                       VrLightCounter* counter);
+// ---- light generation (shaders/light_gen.comp and variants): one walk per photon into a private slab of
+// vrk_lightgen_local_capacity() lights, scan, compaction in canonical photon order, second walk only for photons that
+// overflowed the slab, counter update. slab holds nphot * capacity * 2 float4; scan_tmp ceil(nphot/4096)+1 entries.
+void vrk_lightgen(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, int keep_origin, uint32_t nx, uint32_t ny, uint32_t nz,
+                  uint32_t* counts, unsigned long long* offsets, unsigned long long* total, unsigned long long* scan_tmp,
+                  float4* slab, vr_ray_light* lights, VrLightCounter* counter);
+uint32_t vrk_lightgen_local_capacity();
 // ---- exclusive scan of u32 -> u64 (+ grand total), n up to 2^31; tmp holds ceil(n/4096)+1 entries
 void vrk_scan_u32(cudaStream_t st, const uint32_t* in, unsigned long long* out, unsigned long long* total, uint64_t n,
                   unsigned long long* tmp);
-// ---- light list expansion (ray/beam sub-points: shaders/ray_compute_color.comp:13-20)
+// ---- light list expansion (ray/beam sub-points: shaders/ray_compute_color.comp:13-20). Every kernel is launched over
+// the buffer capacity and reads lightCount on the device; out = VrEvalLight list, out2 = duplicated (x,x,y,y)(z,z,w,w)
+// list for the packed kernels; *neval = list length (prepare_simple) / scan total (expand).
 void vrk_prepare_simple(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, int use_from,
-                        VrEvalLight* out, uint32_t capacity);
+                        VrEvalLight* out, float4* out2, uint32_t capacity, unsigned long long* neval);
 void vrk_prepare_count_steps(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
                              uint32_t* steps, uint32_t capacity);
 void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLightCounter* counter, float lrs,
-                        const unsigned long long* offsets, VrEvalLight* out, uint32_t capacity, uint64_t out_capacity);
+                        const unsigned long long* offsets, VrEvalLight* out, float4* out2, uint32_t capacity,
+                        uint64_t out_capacity, uint32_t* overflow);
 // ---- camera-ray march (shaders/point_compute_color.comp:60-94 minus the light loop)
 void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc);
-// ---- the hot kernel: every sample against every entry of the expanded light list
+// ---- the hot kernels: every sample against every entry of the expanded light list (length read from *nlights_dev)
+// scalar FP32 kernels (point / sphere), every rounding of the shader kept
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-              uint64_t nlights, float radius, float* out);
-// packed-FP32x2 variant for point lights; lights2 is scratch for the duplicated list (2 float4 per light)
-// variant 1: guarded k_eval_point2; 2, 3: speculative k_eval_point3 with 8 / 6 samples per thread (see vr_kernels.cu); redo_count (device, may be
-// NULL) counts CTAs that had to repeat their light loop with the guard
-void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                           float4* lights2, uint64_t nlights, float* out, unsigned long long* redo_count);
-// packed-FP32x2 kernel for sphere lights / beam sub-points (common_functions.h:182-201)
-void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
-                            float4* lights2, uint64_t nlights, float radius, float* out);
+              const unsigned long long* nlights_dev, float radius, float* out);
+// packed FP32x2 kernels for point-type lists. variant 1: guard in the loop (k_eval_point2); 2, 3: speculative
+// k_eval_point3 with 8 / 6 samples per thread; redo_count (device, may be NULL) counts CTAs that repeated with the guard
+void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const float4* lights2,
+                           const unsigned long long* nlights_dev, float* out, unsigned long long* redo_count);
+// packed FP32x2 kernel for sphere lights / beam sub-points (common_functions.h:182-201)
+void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
+                            const unsigned long long* nlights_dev, float radius, float* out);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);

@@ -197,6 +197,12 @@ class VolumeRenderer:
         self._check(self._L.vr_get_timings(self._ctx, C.byref(t)))
         return {k: getattr(t, k) for k, _ in VrTimings._fields_}
 
+    def timings_sum(self, reset=False):
+        """Per-pass times summed over the frames finished since the last reset, and the frame count (no per-frame sync)."""
+        t, n = VrTimings(), C.c_uint64()
+        self._check(self._L.vr_get_timings_sum(self._ctx, C.byref(t), C.byref(n), int(bool(reset))))
+        return {k: getattr(t, k) for k, _ in VrTimings._fields_}, int(n.value)
+
     def row_sample_counts(self):
         out = np.zeros(self.height, np.uint64)
         self._check(self._L.vr_row_sample_counts(self._ctx, out.ctypes.data_as(C.c_void_p)))
