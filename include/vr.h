@@ -196,6 +196,28 @@ int vr_grid_build_dense(const float* dense, const int32_t dims[3], const int32_t
                         uint64_t* size_out);
 void vr_grid_free(void* bytes);
 
+/* ---- NanoVDB files. The reference reads an OpenVDB .vdb and converts it with createNanoGrid
+ * (src/main.cpp:1157-1193); this library takes the converted volume: an uncompressed .nvdb file (segments of
+ * FileHeader + FileMetaData + names + grids, external/openvdb/nanovdb/nanovdb/io/IO.h:381-437, NanoVDB.h:6286-6325) or a
+ * raw grid buffer. Picks the first float grid, like src/main.cpp:1173-1181, or the float grid called grid_name.
+ * ZIP/BLOSC-compressed files are rejected (VR_E_BADGRID). Free the buffer with vr_grid_free. */
+int vr_grid_load_nvdb(const char* path, const char* grid_name_or_null, void** bytes_out, uint64_t* size_out);
+/* write a grid buffer as a one-grid uncompressed .nvdb (raw == 0; readable by nanovdb::io::readGrid) or as the raw buffer */
+int vr_grid_save_nvdb(const char* path, const void* bytes, uint64_t size, int raw);
+
+/* ---- image files (row N1). PPM: binary P6 of the rgba8 image's RGB, the format CPU_test writes
+ * (CPU_test/main.cpp:128-132). PFM: little-endian float, channels = 1 (Pf), 3 or 4 (PF, alpha dropped), rows bottom-up. */
+int vr_image_write_ppm(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+int vr_image_write_pfm(const char* path, const float* data, uint32_t width, uint32_t height, uint32_t channels);
+
+/* ---- snapshots of the progressive state (row N4): UBO incl. frameCount + float4 accumulator + rgba8 image. The
+ * reference keeps this state only in the storage image and uboData.frameCount (src/main.cpp:657, :695-698, :937).
+ * vr_snapshot_load resizes the context's image if needed; rendering continues at frameCount + 1. */
+int vr_snapshot_save(vr_ctx* ctx, const char* path);
+int vr_snapshot_load(vr_ctx* ctx, const char* path);
+/* message of the last failed file call above on this thread (they have no context to attach it to) */
+const char* vr_io_last_error(void);
+
 /* run on a caller-owned CUDA stream (e.g. torch's current stream, so that NCCL collectives and these kernels are
  * ordered on one stream); NULL restores the context's own stream. The caller keeps the stream alive. */
 int vr_set_stream(vr_ctx* ctx, void* cuda_stream);

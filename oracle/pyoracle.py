@@ -195,6 +195,8 @@ class Ref:
         L.vrr_get_values.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
         L.vrr_grid_facts.argtypes = [C.c_void_p] * 5
         L.vrr_cpu_test.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.vrr_write_nvdb.argtypes = [C.c_void_p, C.c_uint64, C.c_char_p]
+        L.vrr_read_nvdb.argtypes = [C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         self._grid = None
 
     def _take(self, p, n):
@@ -236,6 +238,18 @@ class Ref:
         bg = C.c_float()
         assert self.lib.vrr_grid_facts(_ptr(grid), _ptr(bbox), C.byref(active), _ptr(counts), C.byref(bg)) == 0
         return dict(bbox_min=bbox[:3].copy(), bbox_max=bbox[3:].copy(), active=active.value, node_counts=counts, background=bg.value)
+
+    def write_nvdb(self, grid, path):
+        """nanovdb::io::writeGrid(path, handle, Codec::NONE)"""
+        assert self.lib.vrr_write_nvdb(_ptr(grid), grid.nbytes, os.fsencode(path)) == 0
+
+    def read_nvdb(self, path):
+        """nanovdb::io::readGrid(path, 0) -> grid bytes"""
+        p, n = C.c_void_p(), C.c_uint64()
+        rc = self.lib.vrr_read_nvdb(os.fsencode(path), C.byref(p), C.byref(n))
+        if rc:
+            raise ValueError(f"nanovdb::io::readGrid failed on {path} (code {rc})")
+        return self._take(p, n)
 
     def set_grid(self, grid):
         self._grid = grid  # keep alive

@@ -10,6 +10,7 @@
 #include <nanovdb/tools/CreateNanoGrid.h>
 #include <nanovdb/tools/CreatePrimitives.h>
 #include <nanovdb/tools/GridBuilder.h>
+#include <nanovdb/io/IO.h>
 
 #include <atomic>
 #include <cmath>
@@ -131,6 +132,31 @@ int vrr_cpu_test(const void* grid_bytes, int width, int height, int nthreads, fl
     worker();
     for (auto& t : th) t.join();
     return 0;
+}
+
+// nanovdb::io::writeGrid (uncompressed) / readGrid: the .nvdb container the product's vr_grid_load_nvdb / vr_grid_save_nvdb
+// must interoperate with (external/openvdb/nanovdb/nanovdb/io/IO.h:427-470, :560-600)
+int vrr_write_nvdb(const void* grid_bytes, uint64_t size, const char* path) {
+    try {
+        auto buffer = nanovdb::HostBuffer::create(size);
+        memcpy(buffer.data(), grid_bytes, size);
+        nanovdb::GridHandle<> h(std::move(buffer));
+        nanovdb::io::writeGrid(path, h, nanovdb::io::Codec::NONE);
+        return 0;
+    } catch (const std::exception& e) {
+        fprintf(stderr, "vrr_write_nvdb: %s\n", e.what());
+        return 1;
+    }
+}
+int vrr_read_nvdb(const char* path, void** bytes, uint64_t* size) {
+    try {
+        auto h = nanovdb::io::readGrid(path, 0);
+        if (!h.grid<float>()) return 2;
+        return copy_out(h, bytes, size);
+    } catch (const std::exception& e) {
+        fprintf(stderr, "vrr_read_nvdb: %s\n", e.what());
+        return 1;
+    }
 }
 
 }  // extern "C"

@@ -58,6 +58,8 @@ EXPORTS = [
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
     "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_set_march_cache", "vr_set_eval_variant", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
     "vr_set_stream", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
+    "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
+    "vr_io_last_error",
 ]
 
 _lib = None
@@ -126,5 +128,12 @@ def load():
     L.vr_grid_build_dense.argtypes = [P, P, P, C.c_float, C.c_double, P, I, C.POINTER(P), C.POINTER(U64)]
     L.vr_grid_free.argtypes = [P]
     L.vr_grid_free.restype = None
+    L.vr_grid_load_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(P), C.POINTER(U64)]
+    L.vr_grid_save_nvdb.argtypes = [C.c_char_p, P, U64, I]
+    L.vr_image_write_ppm.argtypes = [C.c_char_p, P, U32, U32]
+    L.vr_image_write_pfm.argtypes = [C.c_char_p, P, U32, U32, U32]
+    L.vr_snapshot_save.argtypes = [P, C.c_char_p]
+    L.vr_snapshot_load.argtypes = [P, C.c_char_p]
+    L.vr_io_last_error.restype = C.c_char_p
     _lib = L
     return L

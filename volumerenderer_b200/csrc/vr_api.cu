@@ -100,6 +100,7 @@ struct vr_ctx {
     DevBuf<float> contrib;
     DevBuf<VrEvalLight> eval_lights;
     DevBuf<float4> eval_lights2;
+    DevBuf<float> path_tab;  // path mode: shadow-term table (k_path_table)
     int eval_variant = 2;  // 0: scalar kernel, 1: packed FP32x2 kernel, 2/3: packed speculative kernel (point/ray lists)
     DevBuf<uint32_t> light_steps;
     DevBuf<unsigned long long> light_offsets;
@@ -402,6 +403,7 @@ int vr_destroy(vr_ctx* c) {
     c->contrib.release();
     c->eval_lights.release();
     c->eval_lights2.release();
+    c->path_tab.release();
     c->light_steps.release();
     c->light_offsets.release();
     if (c->counter) cudaFree(c->counter);
@@ -641,7 +643,24 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         }
         cudaEventRecord(t->ev[4], st);
         VR_CUDA(c, cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), st));
-        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->frame_color, c->accum, c->rgba8, c->wc);
+        // shadow-term table (see k_path_table): usable when the voxel next to the light is one of its 27 neighbours
+        // (step <= 1 index unit) and the step count to the farthest bbox corner is moderate
+        uint32_t nmax = 0;
+        if (c->ubo.rayMarchingStepSize <= 1.0f) {
+            const VrGridDev& g = c->gdev;
+            double ls[3], far2 = 0.0;
+            for (int a = 0; a < 3; a++) {
+                const double sx = c->ubo.lightSourceWorldPos[0] - g.vec[0], sy = c->ubo.lightSourceWorldPos[1] - g.vec[1],
+                             sz = c->ubo.lightSourceWorldPos[2] - g.vec[2];
+                ls[a] = sx * g.inv[3 * a] + sy * g.inv[3 * a + 1] + sz * g.inv[3 * a + 2];
+                const double lo = fabs(ls[a] - (double)g.bmin[a]), hi = fabs((double)g.bmax[a] + 1.0 - ls[a]);
+                far2 += (lo > hi ? lo : hi) * (lo > hi ? lo : hi);
+            }
+            const double n = sqrt(far2) * 1.001 / (double)c->ubo.rayMarchingStepSize + 4.0;
+            if (n < 65536.0) nmax = (uint32_t)n;
+        }
+        if (nmax) VR_CUDA(c, c->path_tab.reserve((uint64_t)27 * (nmax + 1)));
+        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->frame_color, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax);
         cudaEventRecord(t->ev[5], st);
         cudaEventRecord(t->ev[6], st);
         t->pending = true, t->open = false;

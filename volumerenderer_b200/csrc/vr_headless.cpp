@@ -1,0 +1,336 @@
+// vr_headless.cpp -- headless frame driver on top of the C ABI.
+//
+// Stands where VolumeApp::mainLoop / drawFrame stand in the reference (src/main.cpp:601-607, 620-837) minus everything
+// that needs a window: per frame it bumps frameCount, regenerates the virtual lights and gathers, exactly the compute
+// section of drawFrame; at the end it writes the image instead of presenting it. The ImGui "Settings" panel
+// (src/main.cpp:649-700) becomes a flat JSON object / --set name=value pairs with the same names and slider ranges.
+//
+//   vr_headless --grid cloud:256 --algo point --frames 16 --size 1920x1080 --set maxLights=1000 --lightgen 32 --ppm out.ppm
+//   vr_headless --config scene.json            {"grid": "bunny.nvdb", "algo": "beam", "frames": 64, "beamRadius": 0.1, ...}
+//   vr_headless --grid sphere:32 --cpu-test density.ppm      (CPU_test/main.cpp: fixed camera, 256x256, 1200 steps)
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <chrono>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/vr.h"
+
+namespace {
+
+struct Options {
+    std::string grid = "cloud:64", algo = "point", ppm, pfm, snap_in, snap_out, cpu_test, grid_name, save_nvdb;
+    uint32_t width = 1024, height = 1024;  // the reference window (src/main.cpp:40-41)
+    uint32_t frames = 1, gx = 1, gy = 1, gz = 1;
+    int device = 0, keep_origin = 0, quiet = 0, march_cache = 0;
+    std::map<std::string, std::vector<double>> sets;  // UBO overrides
+};
+
+[[noreturn]] void die(const std::string& msg) {
+    fprintf(stderr, "vr_headless: %s\n", msg.c_str());
+    exit(2);
+}
+void check(int rc, vr_ctx* ctx, const char* what) {
+    if (rc == VR_OK) return;
+    const char* e = vr_last_error(ctx);  // ctx == NULL: the message of a failed vr_create
+    if (!e || !*e) e = vr_io_last_error();
+    fprintf(stderr, "vr_headless: %s failed (status %d): %s\n", what, rc, e ? e : "");
+    exit(1);
+}
+
+// ---- the settings surface: UBO member -> (offset in floats/uints, count, is_uint, slider min, slider max) src/main.cpp:662-691
+struct Field {
+    const char* name;
+    int count;
+    bool is_uint;
+    double lo, hi;
+};
+const Field kFields[] = {
+    {"cameraPos", 3, false, -200.0, 200.0},          {"fov", 1, false, 1.0, 179.0},
+    {"photonInitialIntensity", 1, false, 0.0, 500.0}, {"scatteringProbability", 1, false, 0.0, 1.0},
+    {"absorptionCoefficient", 1, false, 0.0, 1.0},    {"maxLights", 1, true, 0.0, 1000000.0},
+    {"rayMaxDistance", 1, false, 0.0, 20000.0},       {"rayMarchingStepSize", 1, false, 0.0, 10.0},
+    {"lightSourceWorldPos", 3, false, -100.0, 100.0}, {"beamRadius", 1, false, 0.0, 10.0},
+    {"lightRayStepSize", 1, false, 0.0, 10.0},        {"radiusFalloff", 1, false, 0.0, 1.0},
+};
+void apply_field(vr_ubo& u, const std::string& name, const std::vector<double>& v, bool quiet) {
+    const Field* f = nullptr;
+    for (const Field& k : kFields)
+        if (name == k.name) f = &k;
+    if (!f) die("unknown setting '" + name + "'");
+    if ((int)v.size() != f->count) die("setting '" + name + "' takes " + std::to_string(f->count) + " value(s)");
+    for (double x : v)
+        if (!quiet && (x < f->lo || x > f->hi))
+            fprintf(stderr, "vr_headless: note: %s = %g is outside the reference UI range [%g, %g]\n", f->name, x, f->lo, f->hi);
+    if (name == "cameraPos") for (int i = 0; i < 3; i++) u.cameraPos[i] = (float)v[i];
+    else if (name == "fov") u.fov = (float)v[0];
+    else if (name == "photonInitialIntensity") u.photonInitialIntensity = (float)v[0];
+    else if (name == "scatteringProbability") u.scatteringProbability = (float)v[0];
+    else if (name == "absorptionCoefficient") u.absorptionCoefficient = (float)v[0];
+    else if (name == "maxLights") u.maxLights = (uint32_t)v[0];
+    else if (name == "rayMaxDistance") u.rayMaxDistance = (float)v[0];
+    else if (name == "rayMarchingStepSize") u.rayMarchingStepSize = (float)v[0];
+    else if (name == "lightSourceWorldPos") for (int i = 0; i < 3; i++) u.lightSourceWorldPos[i] = (float)v[i];
+    else if (name == "beamRadius") u.beamRadius = (float)v[0];
+    else if (name == "lightRayStepSize") u.lightRayStepSize = (float)v[0];
+    else if (name == "radiusFalloff") u.radiusFalloff = (float)v[0];
+}
+
+std::vector<double> parse_numbers(const std::string& s) {
+    std::vector<double> out;
+    const char* p = s.c_str();
+    while (*p) {
+        while (*p == ',' || *p == ' ' || *p == '[' || *p == ']' || *p == 'x') p++;
+        if (!*p) break;
+        char* end = nullptr;
+        const double v = strtod(p, &end);
+        if (end == p) die("cannot parse number in '" + s + "'");
+        out.push_back(v);
+        p = end;
+    }
+    return out;
+}
+
+// ---- flat JSON object: {"key": number | "string" | [numbers], ...}
+void parse_json_config(const std::string& path, Options& o);
+
+void set_option(Options& o, const std::string& key, const std::string& val) {
+    if (key == "grid") o.grid = val;
+    else if (key == "grid-name" || key == "gridName") o.grid_name = val;
+    else if (key == "algo" || key == "algorithm") o.algo = val;
+    else if (key == "ppm") o.ppm = val;
+    else if (key == "pfm") o.pfm = val;
+    else if (key == "snapshot-in" || key == "snapshotIn") o.snap_in = val;
+    else if (key == "snapshot-out" || key == "snapshotOut") o.snap_out = val;
+    else if (key == "cpu-test" || key == "cpuTest") o.cpu_test = val;
+    else if (key == "save-nvdb" || key == "saveNvdb") o.save_nvdb = val;
+    else if (key == "frames") o.frames = (uint32_t)parse_numbers(val).at(0);
+    else if (key == "device") o.device = (int)parse_numbers(val).at(0);
+    else if (key == "width") o.width = (uint32_t)parse_numbers(val).at(0);
+    else if (key == "height") o.height = (uint32_t)parse_numbers(val).at(0);
+    else if (key == "march-cache" || key == "marchCache") o.march_cache = (int)parse_numbers(val).at(0);
+    else if (key == "size") {
+        auto v = parse_numbers(val);
+        if (v.size() != 2) die("--size takes WxH");
+        o.width = (uint32_t)v[0], o.height = (uint32_t)v[1];
+    } else if (key == "lightgen") {
+        auto v = parse_numbers(val);
+        if (v.empty() || v.size() > 3) die("--lightgen takes gx[,gy[,gz]]");
+        o.gx = (uint32_t)v[0], o.gy = v.size() > 1 ? (uint32_t)v[1] : 1, o.gz = v.size() > 2 ? (uint32_t)v[2] : 1;
+    } else if (key == "lightgen-variant" || key == "lightgenVariant") {
+        if (val == "reset" || val == "light_gen") o.keep_origin = 0;
+        else if (val == "keep" || val == "point_light_gen") o.keep_origin = 1;
+        else die("--lightgen-variant takes reset|keep");
+    } else if (key == "config") parse_json_config(val, o);
+    else o.sets[key] = parse_numbers(val);  // a UBO member; validated when applied
+}
+
+void parse_json_config(const std::string& path, Options& o) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) die("cannot read config " + path);
+    std::string s;
+    char buf[4096];
+    size_t n;
+    while ((n = fread(buf, 1, sizeof(buf), f)) > 0) s.append(buf, n);
+    fclose(f);
+    size_t i = s.find('{');
+    if (i == std::string::npos) die(path + ": expected a JSON object");
+    i++;
+    for (;;) {
+        while (i < s.size() && (isspace((unsigned char)s[i]) || s[i] == ',')) i++;
+        if (i >= s.size()) die(path + ": unterminated object");
+        if (s[i] == '}') break;
+        if (s[i] != '"') die(path + ": expected a quoted key");
+        const size_t k1 = s.find('"', i + 1);
+        if (k1 == std::string::npos) die(path + ": unterminated key");
+        const std::string key = s.substr(i + 1, k1 - i - 1);
+        i = s.find(':', k1);
+        if (i == std::string::npos) die(path + ": expected ':' after key " + key);
+        i++;
+        while (i < s.size() && isspace((unsigned char)s[i])) i++;
+        std::string val;
+        if (s[i] == '"') {
+            const size_t e = s.find('"', i + 1);
+            if (e == std::string::npos) die(path + ": unterminated string");
+            val = s.substr(i + 1, e - i - 1);
+            i = e + 1;
+        } else if (s[i] == '[') {
+            const size_t e = s.find(']', i);
+            if (e == std::string::npos) die(path + ": unterminated array");
+            val = s.substr(i, e - i + 1);
+            i = e + 1;
+        } else {
+            size_t e = i;
+            while (e < s.size() && s[e] != ',' && s[e] != '}' && !isspace((unsigned char)s[e])) e++;
+            val = s.substr(i, e - i);
+            if (val == "true") val = "1";
+            if (val == "false") val = "0";
+            i = e;
+        }
+        if (key == "config") die(path + ": nested config files are not supported");
+        set_option(o, key, val);
+    }
+}
+
+vr_algo parse_algo(const std::string& a) {
+    // the combo box order of src/main.cpp:65-68, :652-658
+    if (a == "beam" || a == "Beam") return VR_ALGO_BEAM;
+    if (a == "ray" || a == "Ray") return VR_ALGO_RAY;
+    if (a == "point" || a == "Point") return VR_ALGO_POINT;
+    if (a == "sphere" || a == "Sphere") return VR_ALGO_SPHERE;
+    if (a == "path" || a == "Path") return VR_ALGO_PATH;
+    die("unknown algorithm '" + a + "' (beam|ray|point|sphere|path)");
+}
+
+void load_grid(const Options& o, void** bytes, uint64_t* size) {
+    const double tr[3] = {-32.0, -12.0, -32.0};  // SURVEY 8(d) scene
+    if (o.grid.rfind("cloud:", 0) == 0) {
+        auto v = parse_numbers(o.grid.substr(6));
+        if (v.empty()) die("--grid cloud:N[,seed]");
+        const int n = (int)v[0];
+        check(vr_grid_build_cloud(n, v.size() > 1 ? (uint32_t)v[1] : 1234u, 64.0 / n, tr, 0, bytes, size), nullptr, "vr_grid_build_cloud");
+    } else if (o.grid.rfind("sphere:", 0) == 0) {
+        auto v = parse_numbers(o.grid.substr(7));
+        if (v.empty()) die("--grid sphere:R[,cx,cy,cz]");
+        // default centre: in front of CPU_test's fixed camera (CPU_test/main.cpp:92)
+        const int32_t c[3] = {v.size() > 3 ? (int32_t)v[1] : 0, v.size() > 3 ? (int32_t)v[2] : 250, v.size() > 3 ? (int32_t)v[3] : -200};
+        const double zero[3] = {0, 0, 0};
+        check(vr_grid_build_fog_sphere(v[0], c, 1.0, zero, 0, bytes, size), nullptr, "vr_grid_build_fog_sphere");
+    } else {
+        check(vr_grid_load_nvdb(o.grid.c_str(), o.grid_name.empty() ? nullptr : o.grid_name.c_str(), bytes, size), nullptr, "vr_grid_load_nvdb");
+    }
+}
+
+void usage() {
+    puts("vr_headless: headless driver of libvr (VolumeRenderer's many-light passes on B200)\n"
+         "  --grid cloud:N[,seed] | sphere:R[,cx,cy,cz] | file.nvdb     volume (default cloud:64)\n"
+         "  --grid-name NAME         float grid to pick from a multi-grid .nvdb (default: the first float grid)\n"
+         "  --algo beam|ray|point|sphere|path                            (default point)\n"
+         "  --size WxH | --width W --height H                            (default 1024x1024, the reference window)\n"
+         "  --frames N               progressive frames (new lights every frame)\n"
+         "  --lightgen gx[,gy,gz]    light-generation work-groups of 4x4 photons (reference: 1)\n"
+         "  --lightgen-variant reset|keep   light_gen.comp | {point,ray,sphere}_light_gen.comp\n"
+         "  --set NAME=V[,V,V]       UBO member (cameraPos, fov, photonInitialIntensity, scatteringProbability,\n"
+         "                           absorptionCoefficient, maxLights, rayMaxDistance, rayMarchingStepSize,\n"
+         "                           lightSourceWorldPos, beamRadius, lightRayStepSize); also --NAME V\n"
+         "  --config FILE.json       flat JSON object with any of the options above\n"
+         "  --ppm FILE  --pfm FILE   rgba8 image as binary PPM / float accumulator as PFM\n"
+         "  --snapshot-in FILE --snapshot-out FILE   resume from / save the progressive state\n"
+         "  --cpu-test FILE.ppm      CPU_test's density ray-march (256x256) instead of the many-light passes\n"
+         "  --save-nvdb FILE         write the volume as an uncompressed .nvdb\n"
+         "  --march-cache 0|1  --device D  --quiet");
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    Options o;
+    for (int i = 1; i < argc; i++) {
+        std::string a = argv[i];
+        if (a == "--help" || a == "-h") {
+            usage();
+            return 0;
+        }
+        if (a == "--quiet") {
+            o.quiet = 1;
+            continue;
+        }
+        if (a.rfind("--", 0) != 0) die("unexpected argument '" + a + "' (see --help)");
+        a = a.substr(2);
+        if (i + 1 >= argc) die("--" + a + " needs a value");
+        std::string v = argv[++i];
+        if (a == "set") {
+            const size_t eq = v.find('=');
+            if (eq == std::string::npos) die("--set takes NAME=VALUE");
+            o.sets[v.substr(0, eq)] = parse_numbers(v.substr(eq + 1));
+        } else {
+            set_option(o, a, v);
+        }
+    }
+
+    void* grid = nullptr;
+    uint64_t grid_size = 0;
+    load_grid(o, &grid, &grid_size);
+    if (!o.save_nvdb.empty()) check(vr_grid_save_nvdb(o.save_nvdb.c_str(), grid, grid_size, 0), nullptr, "vr_grid_save_nvdb");
+
+    vr_ctx* ctx = nullptr;
+    check(vr_create(o.device, &ctx), nullptr, "vr_create");
+    check(vr_set_grid(ctx, grid, grid_size), ctx, "vr_set_grid");
+    vr_grid_free(grid);
+    if (!o.quiet) fprintf(stderr, "%s, grid %s: %.2f MB\n", vr_version(), o.grid.c_str(), grid_size / 1e6);
+
+    if (!o.cpu_test.empty()) {
+        const uint32_t w = 256, h = 256;  // CPU_test/main.cpp:90-91
+        std::vector<float> dens((size_t)w * h);
+        check(vr_cpu_test_render(ctx, w, h, dens.data()), ctx, "vr_cpu_test_render");
+        std::vector<uint8_t> img((size_t)w * h * 4, 255);
+        for (size_t p = 0; p < dens.size(); p++) {
+            // unsigned char color = static_cast<unsigned char>(std::min(density * 5.0f, 255.0f));  CPU_test/main.cpp:118
+            const uint8_t c = (uint8_t)fminf(dens[p] * 5.0f, 255.0f);
+            img[4 * p] = img[4 * p + 1] = img[4 * p + 2] = c;
+        }
+        check(vr_image_write_ppm(o.cpu_test.c_str(), img.data(), w, h), nullptr, "vr_image_write_ppm");
+        if (!o.quiet) fprintf(stderr, "CPU_test density image written to %s\n", o.cpu_test.c_str());
+        vr_destroy(ctx);
+        return 0;
+    }
+
+    const vr_algo algo = parse_algo(o.algo);
+    if (!o.snap_in.empty()) {
+        check(vr_snapshot_load(ctx, o.snap_in.c_str()), ctx, "vr_snapshot_load");
+        vr_ubo u;
+        vr_get_params(ctx, &u);
+        o.width = u.framebufferDim[0], o.height = u.framebufferDim[1];
+        if (!o.quiet) fprintf(stderr, "resumed %ux%u at frame %u from %s\n", o.width, o.height, u.frameCount, o.snap_in.c_str());
+    } else {
+        check(vr_resize(ctx, o.width, o.height), ctx, "vr_resize");
+    }
+    vr_ubo u;
+    check(vr_get_params(ctx, &u), ctx, "vr_get_params");
+    if (o.snap_in.empty()) {
+        vr_default_params(&u, o.width, o.height);  // src/main.cpp:546-559
+    }
+    for (auto& kv : o.sets) apply_field(u, kv.first, kv.second, o.quiet != 0);
+    if (u.maxLights > 87500) check(vr_set_max_lights_capacity(ctx, u.maxLights), ctx, "vr_set_max_lights_capacity");
+    check(vr_set_params(ctx, &u), ctx, "vr_set_params");
+    check(vr_set_light_gen_groups(ctx, o.gx, o.gy, o.gz, o.keep_origin ? VR_LG_KEEP_ORIGIN : VR_LG_RESET_ORIGIN), ctx, "vr_set_light_gen_groups");
+    check(vr_set_march_cache(ctx, o.march_cache), ctx, "vr_set_march_cache");
+
+    const auto t0 = std::chrono::steady_clock::now();
+    vr_counters cnt{};
+    for (uint32_t f = 0; f < o.frames; f++) {
+        check(vr_render_frame(ctx, algo, nullptr), ctx, "vr_render_frame");  // the compute section of drawFrame
+        check(vr_get_counters(ctx, &cnt), ctx, "vr_get_counters");
+    }
+    check(vr_sync(ctx), ctx, "vr_sync");
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    vr_timings tsum{};
+    uint64_t nfr = 0;
+    vr_get_timings_sum(ctx, &tsum, &nfr, 0);
+    vr_get_params(ctx, &u);
+    if (!o.quiet)
+        printf("{\"frames\": %u, \"frameCount\": %u, \"ms_per_frame\": %.4f, \"algo\": \"%s\", \"width\": %u, \"height\": %u, "
+               "\"light_count\": %llu, \"eval_lights\": %llu, \"S_ref\": %llu, \"S_eff\": %llu, \"E\": %llu, "
+               "\"eval_ms_per_frame\": %.4f, \"march_ms_per_frame\": %.4f, \"light_gen_ms_per_frame\": %.4f}\n",
+               o.frames, u.frameCount, o.frames ? ms / o.frames : 0.0, o.algo.c_str(), o.width, o.height, (unsigned long long)cnt.light_count,
+               (unsigned long long)cnt.eval_lights, (unsigned long long)cnt.S_ref, (unsigned long long)cnt.S_eff, (unsigned long long)cnt.E,
+               nfr ? tsum.eval_ms / nfr : 0.0, nfr ? tsum.march_ms / nfr : 0.0, nfr ? tsum.light_gen_ms / nfr : 0.0);
+
+    if (!o.ppm.empty()) {
+        std::vector<uint8_t> img((size_t)o.width * o.height * 4);
+        check(vr_read_image_rgba8(ctx, img.data()), ctx, "vr_read_image_rgba8");
+        check(vr_image_write_ppm(o.ppm.c_str(), img.data(), o.width, o.height), nullptr, "vr_image_write_ppm");
+    }
+    if (!o.pfm.empty()) {
+        std::vector<float> acc((size_t)o.width * o.height * 4);
+        check(vr_read_accum_f32(ctx, acc.data()), ctx, "vr_read_accum_f32");
+        check(vr_image_write_pfm(o.pfm.c_str(), acc.data(), o.width, o.height, 4), nullptr, "vr_image_write_pfm");
+    }
+    if (!o.snap_out.empty()) check(vr_snapshot_save(ctx, o.snap_out.c_str()), ctx, "vr_snapshot_save");
+    vr_destroy(ctx);
+    return 0;
+}

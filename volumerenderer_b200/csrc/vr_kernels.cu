@@ -809,8 +809,33 @@ __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const u
 // =====================================================================================================
 // path mode (shaders/path_compute_color.comp), one pixel per thread, exact op order
 // =====================================================================================================
+// The shader's shadow term multiplies `light` by the same factor a = exp(-v1*sigma*step) once per step between the sample
+// and the light source (path_compute_color.comp:17-28; v1 is re-read from ONE voxel next to the light, :20). With
+// rayMarchingStepSize <= 1 that voxel is one of the 27 around the light source, so the whole term is a function of
+// (neighbour, step count): k_path_table runs the shader's multiply chain once per neighbour and k_path looks the value up.
+// Same recurrence, same rounding -> bit-identical to looping per sample; the loop remains as the fallback.
+__global__ void k_path_table(VrGridDev g, vr_ubo u, uint32_t nmax, float* __restrict__ tab) {
+    const uint32_t nb = threadIdx.x;
+    if (nb >= 27) return;
+    const vr_f3 ls = vr_world_to_index(g, vr_make3(u.lightSourceWorldPos[0], u.lightSourceWorldPos[1], u.lightSourceWorldPos[2]));
+    const int32_t i = (int32_t)vr_floor(ls.x) + (int32_t)(nb / 9) - 1, j = (int32_t)vr_floor(ls.y) + (int32_t)((nb / 3) % 3) - 1,
+                  k = (int32_t)vr_floor(ls.z) + (int32_t)(nb % 3) - 1;
+    VrAcc acc;
+    vr_acc_init(acc);
+    const float v1 = vr_lookup(g, acc, i, j, k);
+    const float a = vr_exp(vr_mul(vr_mul(-v1, u.absorptionCoefficient), u.rayMarchingStepSize));
+    float light = vr_div(u.photonInitialIntensity, 10000.0f);
+    float* row = tab + (size_t)nb * (nmax + 1);
+    row[0] = light;
+    for (uint32_t s = 1; s <= nmax; s++) {
+        light = vr_mul(light, a);
+        row[s] = light;
+    }
+}
+
 __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, float* __restrict__ frame_color,
-                                               float4* __restrict__ accum, uchar4* __restrict__ rgba8, VrWorkCounters* wc) {
+                                               float4* __restrict__ accum, uchar4* __restrict__ rgba8, VrWorkCounters* wc,
+                                               const float* __restrict__ tab, uint32_t nmax) {
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -826,6 +851,7 @@ __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_s
         vr_f3 o = r.o, d = r.d;
         vr_f3 cur = vr_add3(o, vr_scale3(d, r.tmin));
         const vr_f3 ls = vr_world_to_index(g, vr_make3(u.lightSourceWorldPos[0], u.lightSourceWorldPos[1], u.lightSourceWorldPos[2]));
+        const int32_t lsi = (int32_t)vr_floor(ls.x), lsj = (int32_t)vr_floor(ls.y), lsk = (int32_t)vr_floor(ls.z);
         const float start = vr_div(u.photonInitialIntensity, 10000.0f);
         float finalColor = 0.0f;
         VrAcc acc, acc2;
@@ -855,7 +881,12 @@ __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_s
                     if (steps > 0) {
                         // the loop body reads the same voxel every iteration (:20): hoist the lookup, keep the multiplies
                         const vr_f3 c2 = vr_add3(ls, vr_scale3(rd, step));
-                        const float v1 = vr_lookup(g, acc2, (int32_t)vr_floor(c2.x), (int32_t)vr_floor(c2.y), (int32_t)vr_floor(c2.z));
+                        const int32_t ci = (int32_t)vr_floor(c2.x), cj = (int32_t)vr_floor(c2.y), ck = (int32_t)vr_floor(c2.z);
+                        const uint32_t di = (uint32_t)(ci - lsi + 1), dj = (uint32_t)(cj - lsj + 1), dk = (uint32_t)(ck - lsk + 1);
+                        if (tab && di < 3u && dj < 3u && dk < 3u && steps <= nmax) {
+                            light = __ldg(tab + (size_t)(di * 9u + dj * 3u + dk) * (nmax + 1) + steps);
+                        } else {
+                        const float v1 = vr_lookup(g, acc2, ci, cj, ck);
                         const float a = vr_exp(vr_mul(vr_mul(-v1, u.absorptionCoefficient), step));
                         if (a == 1.0f) {
                             // x * 1 == x: nothing to do
@@ -864,6 +895,7 @@ __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_s
                                 light = vr_mul(light, a);
                                 if (light == 0.0f) break;  // 0 * a stays 0 (a is finite and non-negative)
                             }
+                        }
                         }
                     }
                     finalColor = vr_add(finalColor, vr_mul(vr_mul(vr_mul(T, val), step), light));
@@ -1153,10 +1185,14 @@ void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t*
     k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8);
 }
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
-              float4* accum, uchar4* rgba8, VrWorkCounters* wc) {
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax) {
     VR_COUNT(1);
+    if (tab) {
+        VR_COUNT(1);
+        k_path_table<<<1, 32, 0, st>>>(g, u, nmax, tab);
+    }
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
-    k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc);
+    k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc, tab, nmax);
 }
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density) {
     VR_COUNT(1);

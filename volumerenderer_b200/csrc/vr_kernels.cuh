@@ -64,8 +64,9 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
 // ---- path mode (shaders/path_compute_color.comp), fully fused per pixel
+// tab (27 * (nmax + 1) floats, may be NULL) receives the shadow-term table: light after n multiplies, per neighbour voxel
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
-              float4* accum, uchar4* rgba8, VrWorkCounters* wc);
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax);
 // ---- CPU_test/main.cpp:25-43, 89-126
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density);
 // ---- traversal test hook

@@ -6,6 +6,7 @@ UBO update, light-counter reset, image clear on the first frame, light-generatio
 follow the `Algorithm` enum (:65-68). All compute runs in libvr's sm_100a kernels; there is no CPU fallback.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -249,6 +250,60 @@ class VolumeRenderer:
         out = np.zeros((height, width), np.float32)
         self._check(self._L.vr_cpu_test_render(self._ctx, width, height, out.ctypes.data_as(C.c_void_p)))
         return out
+
+
+    # ------------------------------------------------------------------ snapshots (progressive state)
+    def save_snapshot(self, path):
+        rc = self._L.vr_snapshot_save(self._ctx, os.fsencode(path))
+        if rc:
+            raise VrError(rc, (self._L.vr_io_last_error() or b"").decode() or self._L.vr_last_error(self._ctx).decode())
+
+    def load_snapshot(self, path):
+        rc = self._L.vr_snapshot_load(self._ctx, os.fsencode(path))
+        if rc:
+            raise VrError(rc, (self._L.vr_io_last_error() or b"").decode() or self._L.vr_last_error(self._ctx).decode())
+        u = VrUbo()
+        self._check(self._L.vr_get_params(self._ctx, C.byref(u)))
+        self.width, self.height = int(u.framebufferDim[0]), int(u.framebufferDim[1])
+
+
+# ---------------------------------------------------------------------- files (host side, no GPU needed)
+def _io_check(L, rc, what):
+    if rc:
+        raise VrError(rc, f"{what}: {(L.vr_io_last_error() or b'').decode()}")
+
+
+def load_nvdb_grid(path, grid_name=None):
+    """First float grid (or the one called grid_name) of an uncompressed .nvdb file / raw grid buffer, as uint8 array."""
+    L = _lib.load()
+    p, sz = C.c_void_p(), C.c_uint64()
+    _io_check(L, L.vr_grid_load_nvdb(os.fsencode(path), grid_name.encode() if grid_name else None, C.byref(p), C.byref(sz)),
+              "vr_grid_load_nvdb")
+    return _take(L, p, sz)
+
+
+def save_nvdb_grid(path, grid, raw=False):
+    L = _lib.load()
+    g = np.ascontiguousarray(grid, np.uint8)
+    _io_check(L, L.vr_grid_save_nvdb(os.fsencode(path), g.ctypes.data_as(C.c_void_p), g.nbytes, int(bool(raw))), "vr_grid_save_nvdb")
+
+
+def write_ppm(path, rgba8):
+    L = _lib.load()
+    a = np.ascontiguousarray(rgba8, np.uint8)
+    assert a.ndim == 3 and a.shape[2] == 4
+    _io_check(L, L.vr_image_write_ppm(os.fsencode(path), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0]), "vr_image_write_ppm")
+
+
+def write_pfm(path, image):
+    L = _lib.load()
+    a = np.ascontiguousarray(image, np.float32)
+    if a.ndim == 2:
+        a = a[..., None]
+    _io_check(L, L.vr_image_write_pfm(os.fsencode(path), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0], a.shape[2]), "vr_image_write_pfm")
+
+
+HEADLESS_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "vr_headless")
 
 
 # ---------------------------------------------------------------------- grid fixtures (host side, no GPU needed)
