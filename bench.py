@@ -11,8 +11,9 @@ samples with non-zero density x lights) divided by the frame time; ms
   python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (N>1: launched by torchrun, NCCL)
   python bench.py --impl reference [...]                          the reference's shader source on the host cores
 
-N>1 partitions the frame into row bands balanced by per-row sample counts (grid and lights replicated, light
-generation repeated on every rank) and exchanges the bands over NCCL inside the timed region: strong scaling.
+N>1 partitions the frame into row bands balanced by a measured per-row cost (grid and lights replicated, light
+generation repeated on every rank) and exchanges the bands' frame colours over NCCL inside the timed region: strong
+scaling.
 """
 import argparse
 import ctypes
@@ -216,17 +217,33 @@ def main():
     r.update_ubo(maxLights=cfg["max_lights"])
     r.set_light_gen_groups(cfg["gx"], 1, 1)
 
-    # row bands balanced by the number of non-zero-density samples per row (identical on every rank)
+    # row bands balanced by a per-row cost measured on one full frame (identical on every rank): the evaluation kernel's
+    # time follows the row's non-zero-density samples, the camera march's the row count (tiles.row_costs)
     bands = [(0, H)]
+    tile = None
+    fc_t = None
+    others = []
     if world > 1:
-        bands = tiles.balanced_row_bands(r.row_sample_counts().astype(np.float64) + 2000.0, world)
-    tile = tiles.band_tile(bands[rank], W) if world > 1 else None
-    accum_t = tiles.accum_as_tensor(r) if world > 1 else None
+        r.draw_frame(algo)
+        r.sync()
+        tm = r.timings()
+        bands = tiles.balanced_row_bands(tiles.row_costs(r.row_sample_counts(), tm["march_ms"], tm["eval_ms"]), world)
+        box = [bands]
+        dist.broadcast_object_list(box, src=0)   # timings differ slightly per rank: everyone uses rank 0's split
+        bands = [tuple(b) for b in box[0]]
+        r.reset_accumulation()
+        tile = tiles.band_tile(bands[rank], W)
+        others = tiles.complement_tiles(bands[rank], W, H)
+        fc_t = tiles.frame_color_as_tensor(r)
 
     def step():
+        # own band: light generation + gather + progressive average; the other ranks' rows arrive as frame colours
+        # (4 B/pixel, one grouped NCCL send/recv on the kernels' stream) and are averaged in locally
         r.draw_frame(algo, tile)
         if world > 1:
-            tiles.exchange_bands(accum_t, bands)
+            tiles.exchange_rows_p2p(fc_t, bands)
+            for t in others:
+                r.accumulate_frame_color(t)
 
     def barrier():
         r.sync()
@@ -364,7 +381,7 @@ def main():
             "metric": "light_pixel_contributions_per_s", "value": value, "unit": "contributions/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": "row bands balanced by S_eff" if world > 1 else "whole frame",
+            "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": "row bands balanced by measured march + evaluation cost, frame colours exchanged by one grouped NCCL send/recv" if world > 1 else "whole frame",
                        "l2": "per-step working set (1.3 GB of samples + 14 MB grid) exceeds the 126 MB L2; no flush needed",
                        "bands": bands if world > 1 else None},
             "clocks": clocks,

@@ -156,6 +156,11 @@ int vr_get_timings(vr_ctx* ctx, vr_timings* out);
 int vr_get_timings_sum(vr_ctx* ctx, vr_timings* sum, uint64_t* frames, int reset);
 /* device pointers for zero-copy interop (NCCL): float4 accumulator, rgba8 image, frame colour; CUDA stream */
 int vr_get_device_buffers(vr_ctx* ctx, void** accum_f32, void** image_rgba8, void** frame_color_f32, void** stream);
+/* multi-GPU image tiling: apply the progressive average (shaders/point_compute_color.comp:99-105, current frameCount) to
+ * the pixels of `tile` from frame colours that are ALREADY in the frame-colour buffer (vr_get_device_buffers) -- rows
+ * another GPU rendered and sent over NVLink. A rank renders its own tile with vr_render_frame(tile), receives the other
+ * ranks' frame colours (4 B per pixel instead of the 16 B accumulator) and calls this for the rest of the image. */
+int vr_accumulate_frame_color(vr_ctx* ctx, const vr_tile* tile_or_null);
 /* per-row count of non-zero-density camera samples for the current params (tile balancing across GPUs) */
 int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
 /* 0: re-march camera rays every frame (default, what the reference does); 1: reuse the camera samples while grid,

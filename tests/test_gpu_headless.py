@@ -38,7 +38,7 @@ def test_headless_matches_host_layer(vr, cloud, tmp_path):
     run = subprocess.run([vr.HEADLESS_PATH, "--config", str(cfg), "--ppm", ppm, "--pfm", pfm], capture_output=True, text=True)
     assert run.returncode == 0, run.stderr
     info = json.loads(run.stdout.strip().splitlines()[-1])
-    assert info["frames"] == 3 and info["frameCount"] == 3 and info["light_count"] == 50
+    assert info["frames"] == 3 and info["frameCount"] == 3 and 0 < info["light_count"] <= 50
     with vr.VolumeRenderer(0) as r:
         r.set_grid(grid)
         r.resize(80, 60)
@@ -49,7 +49,8 @@ def test_headless_matches_host_layer(vr, cloud, tmp_path):
             r.draw_frame("ray")
         assert np.array_equal(_read_ppm(ppm), r.read_image_rgba8()[..., :3])
         assert np.array_equal(_read_pfm(pfm), r.read_accum()[..., :3])
-        assert info["S_eff"] == r.counters()["S_eff"] and info["E"] == r.counters()["E"]
+        c = r.counters()
+        assert (info["S_eff"], info["E"], info["light_count"]) == (c["S_eff"], c["E"], c["light_count"])
 
 
 def test_headless_cpu_test_mode(vr, oracle, tmp_path):

@@ -38,7 +38,7 @@ def _worker(rank, world, port, H, W):
     import torch
     import torch.distributed as dist
     sys.path.insert(0, ROOT)
-    from volumerenderer_b200.tiles import balanced_row_bands, exchange_bands, reduce_progressive_sums
+    from volumerenderer_b200.tiles import balanced_row_bands, exchange_bands, exchange_rows_p2p, reduce_progressive_sums
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -50,6 +50,12 @@ def _worker(rank, world, port, H, W):
     img[y0:y0 + h] = full[y0:y0 + h]          # this rank "rendered" only its band
     exchange_bands(img, bands)
     assert torch.equal(img, full), f"rank {rank}: band exchange did not reassemble the frame"
+    # the grouped send/recv exchange of the 1-channel frame colour gives the same reassembly
+    fc_full = torch.arange(H * W, dtype=torch.float32).reshape(H, W)
+    fc = torch.full((H, W), -1.0)
+    fc[y0:y0 + h] = fc_full[y0:y0 + h]
+    exchange_rows_p2p(fc, bands)
+    assert torch.equal(fc, fc_full), f"rank {rank}: p2p row exchange did not reassemble the frame"
     s = torch.full((H, W, 4), float(rank + 1))
     reduce_progressive_sums(s, dst=0)
     if rank == 0:
@@ -61,3 +67,29 @@ def _worker(rank, world, port, H, W):
 def test_band_exchange_gloo_world2():
     import torch.multiprocessing as mp
     mp.spawn(_worker, args=(2, _free_port(), 37, 16), nprocs=2, join=True)
+
+
+def test_band_exchange_gloo_world3():
+    import torch.multiprocessing as mp
+    mp.spawn(_worker, args=(3, _free_port(), 29, 8), nprocs=3, join=True)
+
+
+def test_complement_tiles_and_row_costs():
+    from volumerenderer_b200.tiles import balanced_row_bands, complement_tiles, row_costs
+    assert complement_tiles((0, 10), 64, 40) == [(0, 10, 64, 30)]
+    assert complement_tiles((10, 5), 64, 40) == [(0, 0, 64, 10), (0, 15, 64, 25)]
+    assert complement_tiles((30, 10), 64, 40) == [(0, 0, 64, 30)]
+    assert complement_tiles((0, 40), 64, 40) == []
+    # rows without samples still cost march time: the split moves towards equal row counts as the march share grows
+    samples = np.zeros(100)
+    samples[40:60] = 1000.0
+    b_eval = balanced_row_bands(row_costs(samples, march_ms=0.0, eval_ms=10.0) + 1e-9, 2)
+    b_mix = balanced_row_bands(row_costs(samples, march_ms=10.0, eval_ms=10.0), 2)
+    assert b_eval[0][1] == 50 and b_mix[0][1] == 50  # symmetric case stays in the middle
+    samples[:] = 0.0
+    samples[80:] = 1000.0
+    heavy_only = balanced_row_bands(row_costs(samples, 0.0, 10.0) + 1e-9, 2)
+    mixed = balanced_row_bands(row_costs(samples, 10.0, 10.0), 2)
+    assert heavy_only[0][1] == 90 and 70 <= mixed[0][1] < 90
+    c = row_costs(samples, 5.0, 10.0)
+    assert abs(c.sum() - samples.sum() * 1.5) < 1e-6 * c.sum()

@@ -891,6 +891,18 @@ int vr_get_timings(vr_ctx* c, vr_timings* out) {
     return VR_OK;
 }
 
+int vr_accumulate_frame_color(vr_ctx* c, const vr_tile* tile_or_null) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (c->ubo.frameCount == 0) return fail(c, VR_E_STATE, "vr_accumulate_frame_color: no frame rendered yet (frameCount == 0)");
+    vr_tile tile;
+    int rc = validate_tile(c, tile_or_null, &tile);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    vrk_accumulate(c->stream, c->ubo, tile, c->frame_color, c->accum, c->rgba8);
+    return check_stream(c);
+}
+
 int vr_get_timings_sum(vr_ctx* c, vr_timings* sum, uint64_t* frames, int reset) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));

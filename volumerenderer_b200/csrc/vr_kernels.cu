@@ -806,6 +806,17 @@ __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const u
     accumulate_pixel(fc, vr_sub(total, 1.0f), total, accum, rgba8, gp);
 }
 
+// running average of an already known frame colour (rows rendered by another GPU and exchanged over NVLink)
+__global__ void __launch_bounds__(256) k_accumulate(vr_ubo u, vr_tile tile, const float* __restrict__ frame_color,
+                                                     float4* __restrict__ accum, uchar4* __restrict__ rgba8) {
+    const uint64_t pix = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= (uint64_t)tile.w * tile.h) return;
+    const uint32_t lx = (uint32_t)(pix % tile.w), ly = (uint32_t)(pix / tile.w);
+    const uint64_t gp = (uint64_t)(tile.y0 + ly) * u.framebufferDim[0] + (tile.x0 + lx);
+    const float total = vr_u2f(u.frameCount);
+    accumulate_pixel(frame_color[gp], vr_sub(total, 1.0f), total, accum, rgba8, gp);
+}
+
 // =====================================================================================================
 // path mode (shaders/path_compute_color.comp), one pixel per thread, exact op order
 // =====================================================================================================
@@ -1183,6 +1194,12 @@ void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t*
     const uint64_t npix = (uint64_t)tile.w * tile.h;
     if (!npix) return;
     k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8);
+}
+void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8) {
+    VR_COUNT(1);
+    const uint64_t npix = (uint64_t)tile.w * tile.h;
+    if (!npix) return;
+    k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, frame_color, accum, rgba8);
 }
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
               float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax) {

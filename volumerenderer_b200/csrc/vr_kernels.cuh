@@ -63,6 +63,8 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
                  const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
+// running average (same arithmetic as vrk_resolve) of frame colours that are already in frame_color for this tile
+void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8);
 // ---- path mode (shaders/path_compute_color.comp), fully fused per pixel
 // tab (27 * (nmax + 1) floats, may be NULL) receives the shadow-term table: light after n multiplies, per neighbour voxel
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,

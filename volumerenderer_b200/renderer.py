@@ -147,6 +147,12 @@ class VolumeRenderer:
         t = C.byref(VrTile(*tile)) if tile is not None else None
         self._check(self._L.vr_render_frame(self._ctx, _algo(algo), t))
 
+    def accumulate_frame_color(self, tile=None):
+        """Progressive average of `tile` from frame colours already in the frame-colour buffer (rows received from
+        another GPU); see include/vr.h."""
+        t = C.byref(VrTile(*tile)) if tile is not None else None
+        self._check(self._L.vr_accumulate_frame_color(self._ctx, t))
+
     def reset_accumulation(self):
         self._check(self._L.vr_reset_accumulation(self._ctx))
 
