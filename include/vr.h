@@ -167,6 +167,12 @@ int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
  * camera, image size and march parameters are unchanged (progressive accumulation) */
 int vr_set_march_cache(vr_ctx* ctx, int enabled);
 
+/* 1 (default): once two consecutive vr_render_frame calls had the same inputs, each call also generates the NEXT frame's
+ * lights (same UBO, frameCount + 1) into a second light buffer on the auxiliary stream, underneath its evaluation kernel;
+ * the next call adopts them if its inputs are what was assumed and regenerates otherwise. Results are identical either
+ * way; 0 switches the prefetch off. */
+int vr_set_light_prefetch(vr_ctx* ctx, int enabled);
+
 /* nearest-voxel grid values at n index coordinates (ijk[3*n]) through the device traversal: what
  * pnanovdb_readaccessor_get_value_address + pnanovdb_read_float return (shaders/PNanoVDB_GLSL.h:2202-2231, :365-368),
  * i.e. leaf values, tile values at lower/upper/root level, and the background outside every root tile. */

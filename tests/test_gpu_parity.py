@@ -133,6 +133,35 @@ def test_progressive_accumulation(renderer, pyoracle, oracle, cloud):
     assert (renderer.read_accum()[..., 3] == 1.0).all() and (renderer.read_image_rgba8()[..., 3] == 255).all()
 
 
+def test_light_prefetch_is_transparent(vr, cloud):
+    """Frames rendered with the next-frame light prefetch (adopted, and discarded after a parameter change, a light-gen
+    dispatch, or a reset) equal frames rendered without it, bit for bit: lights, counters, accumulator."""
+    grid = cloud(64)
+
+    def run(prefetch):
+        out = []
+        with vr.VolumeRenderer(0) as r:
+            r.set_light_prefetch(prefetch)
+            r.set_grid(grid)
+            r.resize(64, 48)
+            r.ubo = r.default_ubo()
+            r.update_ubo(maxLights=60)
+            r.set_light_gen_groups(4, 1, 1)
+            for f in range(1, 12):
+                if f == 5:
+                    r.update_ubo(photonInitialIntensity=70.0)        # prefetched lights for frame 5 are stale
+                if f == 8:
+                    r.set_light_gen_groups(6, 1, 1)
+                if f == 10:
+                    r.reset_accumulation()                           # frameCount restarts at 1
+                r.draw_frame("ray" if f % 2 else "point")
+                lights, count, emitted = r.read_lights()
+                out.append((lights.tobytes(), count, emitted, r.counters()["E"], r.read_accum().tobytes(), r.ubo.frameCount))
+        return out
+
+    assert run(True) == run(False)
+
+
 def test_tiles_equal_full_frame(renderer, pyoracle, oracle, cloud):
     grid = cloud(64)
     W, H = 100, 70  # not a multiple of the 16x8 block

@@ -74,6 +74,22 @@ struct vr_ctx {
     DevBuf<vr_ray_light> lights;
     uint32_t light_capacity = 0;
     VrLightCounter* counter = nullptr;
+    // second light buffer + counter: while a frame is being evaluated, vr_render_frame already generates the NEXT
+    // frame's lights into these (same UBO, frameCount + 1) on the auxiliary stream; the next call adopts them by
+    // swapping the pairs if its inputs are what was assumed (LgSpec), else it regenerates.
+    DevBuf<vr_ray_light> lights_alt;
+    VrLightCounter* counter_alt = nullptr;
+    struct LgSpec {
+        bool valid = false;
+        vr_ubo ubo{};
+        uint64_t grid_gen = 0;
+        uint32_t groups[3] = {0, 0, 0};
+        int variant = 0;
+    } spec;
+    vr_ubo prev_frame_ubo{};       // UBO of the previous vr_render_frame (steady-state detection)
+    uint64_t prev_frame_grid_gen = 0;
+    bool prev_frame_valid = false;
+    bool lg_prefetch = true, prefetch_next = false;
     DevBuf<uint32_t> photon_counts;
     DevBuf<unsigned long long> photon_offsets;
     DevBuf<unsigned long long> lg_scan_tmp;  // light generation runs on the auxiliary stream: own scan scratch
@@ -260,9 +276,9 @@ uint64_t expand_bound(const vr_ctx* c) {
     return (uint64_t)bound;
 }
 
-// light generation on stream `st` (shaders/light_gen.comp), timed into `t`
-int enqueue_light_gen(vr_ctx* c, cudaStream_t st, vr_ctx::TimingSet* t, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz,
-                      vr_lightgen_variant variant) {
+// light generation on stream `st` (shaders/light_gen.comp) with parameters `u` into (lights, counter), timed into `t`
+int enqueue_light_gen(vr_ctx* c, cudaStream_t st, vr_ctx::TimingSet* t, const vr_ubo& u, vr_algo algo, uint32_t gx, uint32_t gy,
+                      uint32_t gz, vr_lightgen_variant variant, vr_ray_light* lights, VrLightCounter* counter) {
     const uint64_t nphot = (uint64_t)gx * 4 * gy * 4 * gz;
     cudaEventRecord(t->ev[0], st);
     t->lg_timed = true;
@@ -273,12 +289,17 @@ int enqueue_light_gen(vr_ctx* c, cudaStream_t st, vr_ctx::TimingSet* t, vr_algo 
         VR_CUDA(c, c->lg_scan_tmp.reserve((nphot + 4095) / 4096 + 1));
         VR_CUDA(c, c->lg_slab.reserve(nphot * vrk_lightgen_local_capacity() * 2));
         const int keep = (variant == VR_LG_KEEP_ORIGIN) ? 1 : 0;
-        vrk_lightgen(st, c->gdev, c->ubo, keep, nx, ny, nz, c->photon_counts.p, c->photon_offsets.p, c->photon_total,
-                     c->lg_scan_tmp.p, c->lg_slab.p, c->lights.p, c->counter);
-        c->lights_external = false;
+        vrk_lightgen(st, c->gdev, u, keep, nx, ny, nz, c->photon_counts.p, c->photon_offsets.p, c->photon_total,
+                     c->lg_scan_tmp.p, c->lg_slab.p, lights, counter);
     }
     cudaEventRecord(t->ev[1], st);
     return VR_OK;
+}
+
+bool same_frame_inputs(const vr_ubo& a, const vr_ubo& b) {  // everything but frameCount
+    vr_ubo x = a, y = b;
+    x.frameCount = y.frameCount = 0;
+    return memcmp(&x, &y, sizeof(vr_ubo)) == 0;
 }
 
 // per-frame scalars -> pinned host memory, without blocking (vr_get_counters waits for ev_scalars)
@@ -352,6 +373,8 @@ int vr_create(int cuda_device, vr_ctx** out) {
     c->launch_base = vrk_launch_count();
     VR_CREATE_CUDA(cudaMalloc(&c->counter, sizeof(VrLightCounter)));
     VR_CREATE_CUDA(cudaMemsetAsync(c->counter, 0, sizeof(VrLightCounter), c->stream));
+    VR_CREATE_CUDA(cudaMalloc(&c->counter_alt, sizeof(VrLightCounter)));
+    VR_CREATE_CUDA(cudaMemsetAsync(c->counter_alt, 0, sizeof(VrLightCounter), c->stream));
     VR_CREATE_CUDA(cudaMalloc(&c->photon_total, sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMalloc(&c->totals, 2 * sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMallocHost(&c->totals_host, 4 * sizeof(unsigned long long)));
@@ -363,7 +386,12 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaMallocHost(&c->scalars_host, sizeof(vr_ctx::Scalars)));
     memset(c->scalars_host, 0, sizeof(vr_ctx::Scalars));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_scalars, cudaEventDisableTiming));
-    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->aux_stream, cudaStreamNonBlocking));
+    {
+        // highest priority: the few light-generation CTAs take the first slots the evaluation kernel frees
+        int prio_lo = 0, prio_hi = 0;
+        VR_CREATE_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->aux_stream, cudaStreamNonBlocking, prio_hi));
+    }
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
@@ -407,6 +435,8 @@ int vr_destroy(vr_ctx* c) {
     c->light_steps.release();
     c->light_offsets.release();
     if (c->counter) cudaFree(c->counter);
+    if (c->counter_alt) cudaFree(c->counter_alt);
+    c->lights_alt.release();
     if (c->photon_total) cudaFree(c->photon_total);
     if (c->totals) cudaFree(c->totals);
     if (c->totals_host) cudaFreeHost(c->totals_host);
@@ -470,7 +500,9 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     const uint32_t tiles = rd<uint32_t>(b, root + 24);
     if (root + 64 + 32ull * tiles > size) return fail(c, VR_E_BADGRID, "root tile table outside the buffer");
     VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the old grid
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->spec.valid = false;
     if (c->grid && c->grid_cap < size) {
         cudaFree(c->grid);
         c->grid = nullptr;
@@ -551,9 +583,14 @@ int vr_set_max_lights_capacity(vr_ctx* c, uint32_t n) {
     if (n == 0 || n > (1u << 28)) return fail(c, VR_E_ARG, "light capacity %u out of range", n);
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));
+    c->spec.valid = false;
     c->lights.release();
+    c->lights_alt.release();
     VR_CUDA(c, c->lights.reserve(n));
+    VR_CUDA(c, c->lights_alt.reserve(n));
     VR_CUDA(c, cudaMemsetAsync(c->lights.p, 0, c->lights.cap * sizeof(vr_ray_light), c->stream));
+    VR_CUDA(c, cudaMemsetAsync(c->lights_alt.p, 0, c->lights_alt.cap * sizeof(vr_ray_light), c->stream));
     c->light_capacity = n;
     if (c->ubo.maxLights > n) c->ubo.maxLights = n;
     return vr_reset_lights(c);
@@ -606,8 +643,13 @@ int vr_dispatch_light_gen(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uin
     vr_ctx::TimingSet* t = nullptr;
     rc = open_timing_set(c, &t);
     if (rc != VR_OK) return rc;
-    rc = enqueue_light_gen(c, c->stream, t, algo, gx, gy, gz, variant);
+    if (c->spec.valid) {  // a prefetched light generation shares the photon scratch buffers: let it drain, then drop it
+        VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_lg_done, 0));
+        c->spec.valid = false;
+    }
+    rc = enqueue_light_gen(c, c->stream, t, c->ubo, algo, gx, gy, gz, variant, c->lights.p, c->counter);
     if (rc != VR_OK) return rc;
+    if (algo != VR_ALGO_PATH) c->lights_external = false;
     return check_stream(c);
 }
 
@@ -743,6 +785,26 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     rc = enqueue_scalars(c, st, !reuse);
     if (rc != VR_OK) return rc;
     if (reuse) c->last_counters.S_ref = c->cached_S[0], c->last_counters.S_eff = c->cached_S[1];
+    if (c->prefetch_next) {
+        // next frame's light generation (frameCount + 1) into the other (lights, counter) pair, on the auxiliary stream,
+        // underneath this frame's evaluation kernel; timed into the next frame's event set
+        vr_ctx::TimingSet* nt = &c->tset[(c->tcur + 1) % vr_ctx::kTimingSets];
+        rc = finalize_set(c, *nt);
+        if (rc != VR_OK) return rc;
+        nt->open = true;
+        vr_ubo nu = c->ubo;
+        nu.frameCount += 1;
+        VR_CUDA(c, cudaEventRecord(c->ev_fork, st));
+        VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+        VR_CUDA(c, cudaMemsetAsync(c->counter_alt, 0, sizeof(VrLightCounter), c->aux_stream));
+        rc = enqueue_light_gen(c, c->aux_stream, nt, nu, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2], c->lg_variant,
+                               c->lights_alt.p, c->counter_alt);
+        if (rc != VR_OK) return rc;
+        VR_CUDA(c, cudaEventRecord(c->ev_lg_done, c->aux_stream));
+        c->spec.valid = true;
+        c->spec.ubo = nu, c->spec.grid_gen = c->grid_gen, c->spec.variant = (int)c->lg_variant;
+        memcpy(c->spec.groups, c->lg_groups, sizeof(c->spec.groups));
+    }
 
     // ---- evaluation (hot) + resolve
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
@@ -775,25 +837,50 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
     c->ubo.frameCount += 1;  // src/main.cpp:712
-    rc = vr_reset_lights(c);  // :722-728
+    vr_ctx::TimingSet* t = nullptr;
+    rc = open_timing_set(c, &t);
     if (rc != VR_OK) return rc;
+    const vr_lightgen_variant variant = c->lg_variant;
+    const uint32_t* gr = c->lg_groups;
+    const bool adopt = c->spec.valid && algo != VR_ALGO_PATH && memcmp(&c->spec.ubo, &c->ubo, sizeof(vr_ubo)) == 0 &&
+                       c->spec.grid_gen == c->grid_gen && memcmp(c->spec.groups, gr, sizeof(c->spec.groups)) == 0 &&
+                       c->spec.variant == (int)variant;
+    if (adopt) {
+        // this frame's lights were generated (or are being generated) on the auxiliary stream while the previous frame
+        // was evaluated: counter reset (:722-728) and light generation (:811-814) already happened, into the other pair
+        std::swap(c->lights, c->lights_alt);
+        std::swap(c->counter, c->counter_alt);
+        c->lights_external = false;
+        c->lg_in_flight = true;  // the gather joins on ev_lg_done
+    } else {
+        if (c->spec.valid) VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_lg_done, 0));  // a stale prefetch must drain first
+        rc = vr_reset_lights(c);  // :722-728
+        if (rc != VR_OK) return rc;
+    }
+    c->spec.valid = false;
     if (c->ubo.frameCount == 1) {  // :731
         rc = vr_clear_image(c);
         if (rc != VR_OK) return rc;
     }
-    // light generation (:811-814) runs on the auxiliary stream, concurrently with the camera march of the gather
-    // (:832-837), which does not read the lights; the gather joins before it builds its light list. The reference's
-    // compute->compute barrier (:817-829) is that join.
-    vr_ctx::TimingSet* t = nullptr;
-    rc = open_timing_set(c, &t);
-    if (rc != VR_OK) return rc;
-    VR_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-    VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
-    rc = enqueue_light_gen(c, c->aux_stream, t, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2], c->lg_variant);
-    if (rc != VR_OK) return rc;
-    VR_CUDA(c, cudaEventRecord(c->ev_lg_done, c->aux_stream));
-    c->lg_in_flight = true;
-    return vr_dispatch_compute_color(c, algo, tile_or_null);
+    if (!adopt) {
+        // light generation (:811-814) runs on the auxiliary stream, concurrently with the camera march of the gather
+        // (:832-837), which does not read the lights; the gather joins before it builds its light list. The
+        // reference's compute->compute barrier (:817-829) is that join.
+        VR_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+        VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
+        rc = enqueue_light_gen(c, c->aux_stream, t, c->ubo, algo, gr[0], gr[1], gr[2], variant, c->lights.p, c->counter);
+        if (rc != VR_OK) return rc;
+        if (algo != VR_ALGO_PATH) c->lights_external = false;
+        VR_CUDA(c, cudaEventRecord(c->ev_lg_done, c->aux_stream));
+        c->lg_in_flight = true;
+    }
+    // steady state (same inputs as the previous frame): prefetch the next frame's lights once this frame's list is built
+    c->prefetch_next = c->lg_prefetch && algo != VR_ALGO_PATH && c->prev_frame_valid && c->prev_frame_grid_gen == c->grid_gen &&
+                       same_frame_inputs(c->prev_frame_ubo, c->ubo) && c->prev_frame_ubo.frameCount + 1 == c->ubo.frameCount;
+    c->prev_frame_ubo = c->ubo, c->prev_frame_grid_gen = c->grid_gen, c->prev_frame_valid = true;
+    rc = vr_dispatch_compute_color(c, algo, tile_or_null);
+    c->prefetch_next = false;
+    return rc;
 }
 
 int vr_reset_accumulation(vr_ctx* c) {
@@ -1052,6 +1139,12 @@ int vr_get_eval_redo_count(vr_ctx* c, uint64_t* ctas) {
     VR_CUDA(c, cudaMemcpyAsync(&h, c->eval_redo, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     *ctas = h;
+    return VR_OK;
+}
+
+int vr_set_light_prefetch(vr_ctx* c, int enabled) {
+    if (!c) return VR_E_ARG;
+    c->lg_prefetch = enabled != 0;
     return VR_OK;
 }
 

@@ -121,6 +121,10 @@ class VolumeRenderer:
         self._check(self._L.vr_get_eval_redo_count(self._ctx, C.byref(n)))
         return int(n.value)
 
+    def set_light_prefetch(self, enabled):
+        """Next-frame light generation underneath the current frame's evaluation kernel (default on); see include/vr.h."""
+        self._check(self._L.vr_set_light_prefetch(self._ctx, int(bool(enabled))))
+
     def set_march_cache(self, enabled):
         self._check(self._L.vr_set_march_cache(self._ctx, int(bool(enabled))))
 
