@@ -223,18 +223,34 @@ def main():
     tile = None
     fc_t = None
     others = []
+    def set_bands(new_bands):
+        nonlocal bands, tile, others
+        box = [new_bands]
+        dist.broadcast_object_list(box, src=0)   # every rank uses rank 0's split
+        bands = [tuple(int(v) for v in b) for b in box[0]]
+        tile = tiles.band_tile(bands[rank], W)
+        others = tiles.complement_tiles(bands[rank], W, H)
+
     if world > 1:
         r.draw_frame(algo)
         r.sync()
         tm = r.timings()
-        bands = tiles.balanced_row_bands(tiles.row_costs(r.row_sample_counts(), tm["march_ms"], tm["eval_ms"]), world)
-        box = [bands]
-        dist.broadcast_object_list(box, src=0)   # timings differ slightly per rank: everyone uses rank 0's split
-        bands = [tuple(b) for b in box[0]]
-        r.reset_accumulation()
-        tile = tiles.band_tile(bands[rank], W)
-        others = tiles.complement_tiles(bands[rank], W, H)
+        cost = tiles.row_costs(r.row_sample_counts(), tm["march_ms"], tm["eval_ms"])
+        set_bands(tiles.balanced_row_bands(cost, world))
         fc_t = tiles.frame_color_as_tensor(r)
+        # measured feedback (untimed): each rank reports the device time of its band, the row costs are rescaled
+        for _ in range(3):
+            r.reset_accumulation()
+            r.timings_sum(reset=True)
+            for _ in range(3):
+                r.draw_frame(algo, tile)
+            ts, nf = r.timings_sum(reset=True)
+            mine = torch.tensor([ts["total_ms"] / max(1, nf)], dtype=torch.float64, device="cuda")
+            allms = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allms, mine)
+            cost = tiles.refine_row_costs(cost, bands, [float(x) for x in allms])
+            set_bands(tiles.balanced_row_bands(cost, world))
+        r.reset_accumulation()
 
     def step():
         # own band: light generation + gather + progressive average; the other ranks' rows arrive as frame colours
@@ -283,6 +299,12 @@ def main():
     launches = r.launch_count() - launches0
     clocks = sampler.stop() if rank == 0 else None
 
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor([pass_ms["march_ms"], pass_ms["eval_ms"], tsum["total_ms"], dev_ms], dtype=torch.float64, device="cuda") / args.steps
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [dict(zip(("march_ms", "eval_ms", "gather_ms", "step_ms"), (round(float(v), 4) for v in x))) for x in allr]
     t = torch.tensor([dev_ms, float(ceff), float(evals), pass_ms["eval_ms"]], dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = t.clone()
@@ -392,6 +414,7 @@ def main():
             "cpu_baseline": cpu_baseline,
             "passes_ms_per_step": {k: v / args.steps for k, v in pass_ms.items()},
             "host_ms_per_step": host_ms / args.steps,
+            "per_rank_ms_per_step": per_rank,
             "contributions_per_frame": ceff_total / args.steps,
         }
         print(json.dumps(line), flush=True)

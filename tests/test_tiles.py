@@ -93,3 +93,20 @@ def test_complement_tiles_and_row_costs():
     assert heavy_only[0][1] == 90 and 70 <= mixed[0][1] < 90
     c = row_costs(samples, 5.0, 10.0)
     assert abs(c.sum() - samples.sum() * 1.5) < 1e-6 * c.sum()
+
+
+def test_refine_row_costs_converges():
+    """feedback balancing against a hidden true cost the model does not know"""
+    from volumerenderer_b200.tiles import balanced_row_bands, refine_row_costs
+    rng = np.random.default_rng(3)
+    H, world = 270, 8
+    true = 1.0 + 40.0 * np.exp(-((np.arange(H) - 150.0) / 40.0) ** 2) + rng.random(H)
+    model = np.ones(H)                      # a poor first guess: all rows equal
+    bands = balanced_row_bands(model, world)
+    for _ in range(4):
+        rank_ms = [true[y0:y0 + h].sum() for y0, h in bands]
+        model = refine_row_costs(model, bands, rank_ms)
+        bands = balanced_row_bands(model, world)
+    rank_ms = np.array([true[y0:y0 + h].sum() for y0, h in bands])
+    assert rank_ms.max() / rank_ms.mean() < 1.08
+    assert sum(h for _, h in bands) == H

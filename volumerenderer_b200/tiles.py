@@ -117,6 +117,24 @@ def row_costs(row_samples, march_ms, eval_ms):
     return s + per_row
 
 
+def refine_row_costs(row_cost, bands, rank_ms):
+    """One step of measured feedback: rank r spent rank_ms[r] on the rows of bands[r], so the cost of those rows is
+    rescaled to make the model's band totals proportional to the measurements. Feed the result to balanced_row_bands;
+    two or three rounds (a couple of untimed frames each) settle the split to within a row or two."""
+    cost = np.asarray(row_cost, np.float64).copy()
+    ms = np.asarray(rank_ms, np.float64)
+    if len(ms) != len(bands) or not np.all(ms > 0):
+        return cost
+    total_model = float(cost.sum())
+    for (y0, h), t in zip(bands, ms):
+        if h <= 0:
+            continue
+        model = float(cost[y0:y0 + h].sum())
+        if model > 0:
+            cost[y0:y0 + h] *= (t / ms.sum()) / (model / total_model)
+    return cost
+
+
 def reduce_progressive_sums(accum_sum, dst=0, group=None):
     """Sample-parallel progressive mode (SURVEY 8e): every rank accumulates a float SUM of the frames it rendered;
     one reduce(sum) to `dst` combines them (divide by the total frame count afterwards). Not available for the
