@@ -175,6 +175,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"], help="N>1 tile exchange")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
     args = ap.parse_args()
@@ -252,7 +253,31 @@ def main():
             set_bands(tiles.balanced_row_bands(cost, world))
         r.reset_accumulation()
 
+    # N>1: the rank's band goes to every GPU straight from the resolve kernel (peer stores over NVLink into torch
+    # symmetric memory) when that is available, else as one grouped NCCL send/recv of the 4 B/pixel frame colours
+    peer_fc = None
+    exchange = "none"
+    if world > 1:
+        exchange = "nccl grouped send/recv of frame colours"
+        if args.exchange in ("auto", "peer"):
+            try:
+                peer_fc = tiles.PeerFrameColor(r, bands)
+                exchange = "peer stores from the resolve kernel (symmetric memory) + device barrier"
+            except Exception as e:  # noqa: BLE001
+                if args.exchange == "peer":
+                    raise
+                log(f"rank {rank}: symmetric memory unavailable ({type(e).__name__}: {e}); using the NCCL exchange")
+        flag = torch.tensor([1 if peer_fc is not None else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag) == 0 and peer_fc is not None:
+            peer_fc.close()
+            peer_fc = None
+            exchange = "nccl grouped send/recv of frame colours"
+
     def step():
+        if peer_fc is not None:
+            peer_fc.draw_frame(algo)
+            return
         # own band: light generation + gather + progressive average; the other ranks' rows arrive as frame colours
         # (4 B/pixel, one grouped NCCL send/recv on the kernels' stream) and are averaged in locally
         r.draw_frame(algo, tile)
@@ -403,7 +428,7 @@ def main():
             "metric": "light_pixel_contributions_per_s", "value": value, "unit": "contributions/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": "row bands balanced by measured march + evaluation cost, frame colours exchanged by one grouped NCCL send/recv" if world > 1 else "whole frame",
+            "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": f"row bands balanced by measured per-rank time; exchange: {exchange}" if world > 1 else "whole frame",
                        "l2": "per-step working set (1.3 GB of samples + 14 MB grid) exceeds the 126 MB L2; no flush needed",
                        "bands": bands if world > 1 else None},
             "clocks": clocks,

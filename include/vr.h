@@ -161,6 +161,14 @@ int vr_get_device_buffers(vr_ctx* ctx, void** accum_f32, void** image_rgba8, voi
  * another GPU rendered and sent over NVLink. A rank renders its own tile with vr_render_frame(tile), receives the other
  * ranks' frame colours (4 B per pixel instead of the 16 B accumulator) and calls this for the rest of the image. */
 int vr_accumulate_frame_color(vr_ctx* ctx, const vr_tile* tile_or_null);
+/* fused tile all-gather: `local` (width*height floats, caller-owned; NULL = the context's private buffer) becomes the
+ * frame-colour buffer, and peers[0..n) are the addresses of the SAME buffer on the GPUs of the group as mapped into this
+ * process (CUDA peer / symmetric memory over NVLink; the entry equal to `local` is skipped). From then on the resolve
+ * and path kernels store every pixel's frame colour to the local buffer and to all peers, so that after a cross-GPU
+ * barrier each GPU holds the whole frame's colours without a separate collective; it then calls
+ * vr_accumulate_frame_color for the rows it did not render. The call does not synchronise: alternate two buffers per
+ * frame so that a fast GPU's stores for frame f+1 never land in a buffer a slow GPU still reads for frame f. */
+int vr_set_frame_color_peers(vr_ctx* ctx, void* local, void* const* peers, uint32_t n);
 /* per-row count of non-zero-density camera samples for the current params (tile balancing across GPUs) */
 int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
 /* 0: re-march camera rays every frame (default, what the reference does); 1: reuse the camera samples while grid,

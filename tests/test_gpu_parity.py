@@ -162,6 +162,49 @@ def test_light_prefetch_is_transparent(vr, cloud):
     assert run(True) == run(False)
 
 
+def test_frame_color_peer_stores(vr, cloud):
+    """vr_set_frame_color_peers: the resolve / path kernels store frame colours to the local buffer and to every peer
+    address (here: further buffers on the same GPU standing in for NVLink-mapped peers), only inside the rendered tile;
+    vr_accumulate_frame_color then completes the progressive average from such a buffer."""
+    import torch
+    grid = cloud(64)
+    W, H = 64, 48
+    with vr.VolumeRenderer(0) as r, vr.VolumeRenderer(0) as full:
+        for q in (r, full):
+            q.set_grid(grid)
+            q.resize(W, H)
+            q.ubo = q.default_ubo()
+            q.update_ubo(maxLights=40)
+            q.set_light_gen_groups(4, 1, 1)
+        bufs = [torch.full((H, W), -1.0, device="cuda") for _ in range(3)]
+        torch.cuda.synchronize()
+        for algo in ("point", "path"):
+            for q in (r, full):
+                q.reset_accumulation()
+            for frame in range(2):
+                full.draw_frame(algo)
+                r.set_frame_color_peers(bufs[0].data_ptr(), [b.data_ptr() for b in bufs])
+                r.draw_frame(algo, (0, 10, W, 20))          # rows 10..29 rendered here
+                r.sync()
+                want = full.read_frame_color()
+                for b in bufs:
+                    got = b.cpu().numpy()
+                    assert np.array_equal(got[10:30], want[10:30])
+                    if frame == 0 and algo == "point":
+                        assert (got[:10] == -1.0).all() and (got[30:] == -1.0).all()
+                # "receive" the other rows (as a peer's stores would have delivered them), then average them in
+                bufs[0][:10] = torch.from_numpy(want[:10]).cuda()
+                bufs[0][30:] = torch.from_numpy(want[30:]).cuda()
+                torch.cuda.synchronize()
+                r.accumulate_frame_color((0, 0, W, 10))
+                r.accumulate_frame_color((0, 30, W, H - 30))
+                assert np.array_equal(r.read_accum(), full.read_accum())
+                assert np.array_equal(r.read_image_rgba8(), full.read_image_rgba8())
+        r.set_frame_color_peers(None, [])
+        r.draw_frame("point")
+        assert r.read_frame_color().max() > 0
+
+
 def test_tiles_equal_full_frame(renderer, pyoracle, oracle, cloud):
     grid = cloud(64)
     W, H = 100, 70  # not a multiple of the 16x8 block

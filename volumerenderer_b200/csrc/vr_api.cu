@@ -107,7 +107,9 @@ struct vr_ctx {
     uint32_t width = 0, height = 0;
     float4* accum = nullptr;
     uchar4* rgba8 = nullptr;
-    float* frame_color = nullptr;
+    float* frame_color = nullptr;        // the buffer in use: own_frame_color or a caller-provided (symmetric) one
+    float* own_frame_color = nullptr;
+    VrFrameColorOut fc_out{};            // frame_color + peer mappings for the kernels
     // gather work buffers
     DevBuf<uint32_t> px_counts;
     DevBuf<unsigned long long> px_offsets;
@@ -450,7 +452,7 @@ int vr_destroy(vr_ctx* c) {
     if (c->eval_redo) cudaFree(c->eval_redo);
     if (c->accum) cudaFree(c->accum);
     if (c->rgba8) cudaFree(c->rgba8);
-    if (c->frame_color) cudaFree(c->frame_color);
+    if (c->own_frame_color) cudaFree(c->own_frame_color);
     for (int k = 0; k < vr_ctx::kTimingSets; k++)
         for (int i = 0; i < 7; i++)
             if (c->tset[k].ev[i]) cudaEventDestroy(c->tset[k].ev[i]);
@@ -544,11 +546,15 @@ int vr_resize(vr_ctx* c, uint32_t w, uint32_t h) {
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->accum) cudaFree(c->accum), c->accum = nullptr;
     if (c->rgba8) cudaFree(c->rgba8), c->rgba8 = nullptr;
-    if (c->frame_color) cudaFree(c->frame_color), c->frame_color = nullptr;
+    if (c->own_frame_color) cudaFree(c->own_frame_color), c->own_frame_color = nullptr;
+    c->frame_color = nullptr;
+    memset(&c->fc_out, 0, sizeof(c->fc_out));
     const uint64_t npix = (uint64_t)w * h;
     VR_CUDA(c, cudaMalloc(&c->accum, npix * sizeof(float4)));
     VR_CUDA(c, cudaMalloc(&c->rgba8, npix * sizeof(uchar4)));
-    VR_CUDA(c, cudaMalloc(&c->frame_color, npix * sizeof(float)));
+    VR_CUDA(c, cudaMalloc(&c->own_frame_color, npix * sizeof(float)));
+    c->frame_color = c->own_frame_color;
+    c->fc_out.local = c->frame_color;
     c->width = w, c->height = h;
     c->ubo.framebufferDim[0] = w, c->ubo.framebufferDim[1] = h;
     c->ubo.frameCount = 0;  // src/main.cpp:937
@@ -702,7 +708,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             if (n < 65536.0) nmax = (uint32_t)n;
         }
         if (nmax) VR_CUDA(c, c->path_tab.reserve((uint64_t)27 * (nmax + 1)));
-        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->frame_color, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax);
+        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->fc_out, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax);
         cudaEventRecord(t->ev[5], st);
         cudaEventRecord(t->ev[6], st);
         t->pending = true, t->open = false;
@@ -815,7 +821,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     else
         vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->contrib.p, c->eval_redo);
     cudaEventRecord(t->ev[5], st);
-    vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->frame_color, c->accum, c->rgba8);
+    vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8);
     cudaEventRecord(t->ev[6], st);
     t->pending = true, t->open = false;
     return check_stream(c);
@@ -975,6 +981,23 @@ int vr_get_timings(vr_ctx* c, vr_timings* out) {
     int rc = finalize_timings(c);
     if (rc != VR_OK) return rc;
     *out = c->timings;
+    return VR_OK;
+}
+
+int vr_set_frame_color_peers(vr_ctx* c, void* local, void* const* peers, uint32_t n) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (n > VR_MAX_PEERS) return fail(c, VR_E_ARG, "at most %d peer buffers", VR_MAX_PEERS);
+    if (n && !peers) return fail(c, VR_E_ARG, "vr_set_frame_color_peers: NULL peer list");
+    // no synchronisation: the switch takes effect for kernels enqueued from now on (callers alternate two buffers)
+    c->frame_color = local ? (float*)local : c->own_frame_color;
+    memset(&c->fc_out, 0, sizeof(c->fc_out));
+    c->fc_out.local = c->frame_color;
+    for (uint32_t q = 0; q < n; q++) {
+        if (!peers[q]) return fail(c, VR_E_ARG, "vr_set_frame_color_peers: NULL peer pointer");
+        if (peers[q] == (void*)c->frame_color) continue;  // this GPU's own entry
+        c->fc_out.peer[c->fc_out.npeers++] = (float*)peers[q];
+    }
     return VR_OK;
 }
 

@@ -786,9 +786,15 @@ __device__ __forceinline__ void accumulate_pixel(float fc, float nm1, float nn, 
     n8.w = 255;
     rgba8[gp] = n8;
 }
+// frame colour of pixel gp to this GPU's buffer and to every peer's (plain stores to peer-mapped memory travel over
+// NVLink; the caller orders them with a cross-GPU barrier before the peers read)
+__device__ __forceinline__ void store_frame_color(const VrFrameColorOut& o, uint64_t gp, float fc) {
+    o.local[gp] = fc;
+    for (uint32_t q = 0; q < o.npeers; q++) o.peer[q][gp] = fc;
+}
 __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const uint32_t* __restrict__ counts,
                                                   const unsigned long long* __restrict__ offsets, const float* __restrict__ contrib,
-                                                  const VrLightCounter* __restrict__ counter, float* __restrict__ frame_color,
+                                                  const VrLightCounter* __restrict__ counter, VrFrameColorOut frame_color,
                                                   float4* __restrict__ accum, uchar4* __restrict__ rgba8) {
     const uint64_t pix = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= (uint64_t)tile.w * tile.h) return;
@@ -801,7 +807,7 @@ __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const u
     float fc = vr_div(finalColor, vr_u2f(counter->lightCount));
     fc = vr_clamp(fc, 0.0f, 1.0f);
     if (fc != fc) fc = 0.0f;  // lightCount == 0 -> 0/0; a NaN stores as 0 (Appendix B)
-    frame_color[gp] = fc;
+    store_frame_color(frame_color, gp, fc);
     const float total = vr_u2f(u.frameCount);  // float totalInvocations = frameCount * 1
     accumulate_pixel(fc, vr_sub(total, 1.0f), total, accum, rgba8, gp);
 }
@@ -844,7 +850,7 @@ __global__ void k_path_table(VrGridDev g, vr_ubo u, uint32_t nmax, float* __rest
     }
 }
 
-__global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, float* __restrict__ frame_color,
+__global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, VrFrameColorOut frame_color,
                                                float4* __restrict__ accum, uchar4* __restrict__ rgba8, VrWorkCounters* wc,
                                                const float* __restrict__ tab, uint32_t nmax) {
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -918,7 +924,7 @@ __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_s
         float fc = vr_clamp(finalColor, 0.0f, 1.0f);
         if (fc != fc) fc = 0.0f;
         const uint64_t gp = (uint64_t)py * u.framebufferDim[0] + px;
-        frame_color[gp] = fc;
+        store_frame_color(frame_color, gp, fc);
         // (previousColor * (contributionCount - 1) + frameColor) / contributionCount with uint contributionCount
         accumulate_pixel(fc, vr_u2f(u.frameCount - 1u), vr_u2f(u.frameCount), accum, rgba8, gp);
     }
@@ -1189,7 +1195,7 @@ void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsa
         k_eval<false, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights_dev, radius, out);
 }
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
-                 const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8) {
+                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8) {
     VR_COUNT(1);
     const uint64_t npix = (uint64_t)tile.w * tile.h;
     if (!npix) return;
@@ -1201,7 +1207,7 @@ void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float*
     if (!npix) return;
     k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, frame_color, accum, rgba8);
 }
-void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
+void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrFrameColorOut& frame_color,
               float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax) {
     VR_COUNT(1);
     if (tab) {

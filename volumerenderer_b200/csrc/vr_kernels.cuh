@@ -22,6 +22,15 @@ struct VrLightCounter {  // binding 4 (shaders/common_bindings.h:14-17) + bookke
     unsigned long long totalEmitted;  // scatter events before the maxLights cap
 };
 
+// where a pixel's frame colour goes: the local buffer and, in image-tiled multi-GPU runs, the same buffer on every
+// other GPU, addressed through peer mappings over NVLink (the all-gather of the tiles is fused into the kernel's stores)
+#define VR_MAX_PEERS 16
+struct VrFrameColorOut {
+    float* local;
+    float* peer[VR_MAX_PEERS];  // other GPUs' buffers as mapped into this process
+    uint32_t npeers;
+};
+
 struct VrWorkCounters {
     unsigned long long S_ref, S_eff;
 };
@@ -62,12 +71,12 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
                             const unsigned long long* nlights_dev, float radius, float* out);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
-                 const float* contrib, const VrLightCounter* counter, float* frame_color, float4* accum, uchar4* rgba8);
+                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8);
 // running average (same arithmetic as vrk_resolve) of frame colours that are already in frame_color for this tile
 void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8);
 // ---- path mode (shaders/path_compute_color.comp), fully fused per pixel
 // tab (27 * (nmax + 1) floats, may be NULL) receives the shadow-term table: light after n multiplies, per neighbour voxel
-void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, float* frame_color,
+void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrFrameColorOut& frame_color,
               float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax);
 // ---- CPU_test/main.cpp:25-43, 89-126
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density);

@@ -157,6 +157,12 @@ class VolumeRenderer:
         t = C.byref(VrTile(*tile)) if tile is not None else None
         self._check(self._L.vr_accumulate_frame_color(self._ctx, t))
 
+    def set_frame_color_peers(self, local_ptr, peer_ptrs):
+        """Fused tile all-gather: resolve stores frame colours to `local_ptr` and every address in `peer_ptrs` (the same
+        buffer on the other GPUs, peer-mapped); (None, []) restores the private buffer. See include/vr.h."""
+        arr = (C.c_void_p * max(1, len(peer_ptrs)))(*[C.c_void_p(int(p)) for p in peer_ptrs])
+        self._check(self._L.vr_set_frame_color_peers(self._ctx, C.c_void_p(int(local_ptr)) if local_ptr else None, arr, len(peer_ptrs)))
+
     def reset_accumulation(self):
         self._check(self._L.vr_reset_accumulation(self._ctx))
 

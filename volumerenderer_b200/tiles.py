@@ -135,6 +135,61 @@ def refine_row_costs(row_cost, bands, rank_ms):
     return cost
 
 
+class PeerFrameColor:
+    """Fused tile all-gather over NVLink peer memory (the "compute + collective in one kernel" form).
+
+    Two (H, W) float32 frame-colour buffers are allocated as torch symmetric memory, i.e. every rank maps every other
+    rank's buffers into its own address space. libvr's resolve kernel then stores each pixel of the rank's band to all
+    ranks' buffers directly (vr_set_frame_color_peers), a device-side barrier on the renderer's stream orders the
+    stores, and each rank averages the rows it did not render from its local copy (vr_accumulate_frame_color). No NCCL
+    call per frame. The two buffers alternate by frame so that a fast rank's stores for the next frame cannot land in
+    memory a slow rank is still reading.
+
+    Raises whatever torch raises if symmetric memory is unavailable; callers fall back to exchange_rows_p2p.
+    """
+
+    def __init__(self, renderer, bands, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.r = renderer
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        dev = torch.device(f"cuda:{renderer.device}")
+        self.bufs, self.hdls, self.ptrs = [], [], []
+        for _ in range(2):
+            t = symm_mem.empty((renderer.height, renderer.width), dtype=torch.float32, device=dev)
+            t.zero_()
+            h = symm_mem.rendezvous(t, self.group)
+            self.bufs.append(t)
+            self.hdls.append(h)
+            self.ptrs.append([int(p) for p in h.buffer_ptrs])
+        self.set_bands(bands)
+        self.parity = 0
+        torch.cuda.synchronize()
+        dist.barrier(self.group)
+
+    def set_bands(self, bands):
+        self.bands = [tuple(b) for b in bands]
+        self.tile = band_tile(self.bands[self.rank], self.r.width)
+        self.others = complement_tiles(self.bands[self.rank], self.r.width, self.r.height)
+
+    def draw_frame(self, algo):
+        """One frame: own band rendered with its frame colours stored to every rank, barrier, rest of the image averaged."""
+        p = self.parity
+        self.r.set_frame_color_peers(self.ptrs[p][self.rank], self.ptrs[p])
+        self.r.draw_frame(algo, self.tile)
+        self.hdls[p].barrier(channel=0)          # device-side, on the current (= renderer's) stream
+        for t in self.others:
+            self.r.accumulate_frame_color(t)
+        self.parity ^= 1
+
+    def close(self):
+        self.r.set_frame_color_peers(None, [])
+
+
 def reduce_progressive_sums(accum_sum, dst=0, group=None):
     """Sample-parallel progressive mode (SURVEY 8e): every rank accumulates a float SUM of the frames it rendered;
     one reduce(sum) to `dst` combines them (divide by the total frame count afterwards). Not available for the
