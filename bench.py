@@ -380,6 +380,28 @@ def main():
         e2e_s, e2e_ceff = float(tmax[0]), float(tsum[1])
     e2e_value = e2e_ceff / e2e_s
 
+    # ---- N>1: the tiled, exchanged result must equal a whole-frame render of the same frames (untimed check)
+    verified = None
+    if world > 1:
+        def render(n_frames, tiled):
+            r.reset_accumulation()
+            for _ in range(n_frames):
+                if tiled:
+                    step()
+                else:
+                    if peer_fc is not None:
+                        r.set_frame_color_peers(None, [])
+                    r.draw_frame(algo)
+            r.sync()
+            return r.read_accum(), r.read_image_rgba8()
+        a_t, i_t = render(3, True)
+        barrier()
+        a_f, i_f = render(3, False)
+        ok = torch.tensor([1 if (np.array_equal(a_t, a_f) and np.array_equal(i_t, i_f)) else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        verified = bool(int(ok))
+        barrier()
+
     if rank == 0:
         # ---- roofline of the dominant kernel (k_eval): FP32-issue bound, measured live with CUDA events
         flop = FLOP_PER_EVAL[algo]
@@ -440,6 +462,7 @@ def main():
             "passes_ms_per_step": {k: v / args.steps for k, v in pass_ms.items()},
             "host_ms_per_step": host_ms / args.steps,
             "per_rank_ms_per_step": per_rank,
+            "multi_gpu_image_equals_single_gpu": verified,
             "contributions_per_frame": ceff_total / args.steps,
         }
         print(json.dumps(line), flush=True)
