@@ -423,7 +423,7 @@ def main():
         except Exception:
             pass
         roofline = {
-            "bound": "fp32", "kernel": f"k_eval<{algo}>", "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s",
+            "bound": "fp32", "kernel": {"point": "k_eval_point3<8,3,2>", "ray": "k_eval_point3<8,3,2>", "sphere": "k_eval_sphere2<8>", "beam": "k_eval_sphere2<8>"}.get(algo, algo), "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s",
             "frac": achieved / peak_fma if peak_fma else None,
             "peak_source": "FFMA microbenchmark measured in this run (vr_ubench kind 0); MEASURED_PEAKS.json has no non-tensor FP32 figure",
             "flop_per_eval": flop, "evals_per_s": evals / eval_s if eval_s > 0 else 0.0,
