@@ -51,7 +51,9 @@ __device__ __forceinline__ void vr_acc_init(VrAcc& a) {
 
 // Nearest-voxel value incl. tile and background values; the value mask is not consulted
 // (pnanovdb_readaccessor_get_value_address + pnanovdb_read_float, shaders/PNanoVDB_GLSL.h:2202-2231, :365-368).
-__device__ __forceinline__ float vr_lookup(const VrGridDev& g, VrAcc& a, int32_t i, int32_t j, int32_t k) {
+// log2dim receives the log2 edge length of the aligned cube that shares this value: 0 = a leaf voxel, 3 = a tile of a
+// lower node (8^3 voxels), 7 = a tile of an upper node (128^3), 12 = a root tile (4096^3), -1 = background (no cube).
+__device__ __forceinline__ float vr_lookup_dim(const VrGridDev& g, VrAcc& a, int32_t i, int32_t j, int32_t k, int& log2dim) {
     const uint8_t* b = g.base;
     const uint32_t dirty = (uint32_t)((i ^ a.kx) | (j ^ a.ky) | (k ^ a.kz));
     uint64_t leaf = (dirty & ~7u) ? 0 : a.leaf;
@@ -70,9 +72,9 @@ __device__ __forceinline__ float vr_lookup(const VrGridDev& g, VrAcc& a, int32_t
                 uint32_t t = 0;
                 for (; t < g.tile_count; t++, tile += VR_TILE_SIZE)
                     if (vr_ld_u64(b + tile) == key) break;
-                if (t == g.tile_count) return vr_ld_f32(b + g.root + VR_ROOT_OFF_BACKGROUND);
+                if (t == g.tile_count) return log2dim = -1, vr_ld_f32(b + g.root + VR_ROOT_OFF_BACKGROUND);
                 const int64_t child = (int64_t)vr_ld_u64(b + tile + VR_TILE_OFF_CHILD);
-                if (child == 0) return vr_ld_f32(b + tile + VR_TILE_OFF_VALUE);
+                if (child == 0) return log2dim = 12, vr_ld_f32(b + tile + VR_TILE_OFF_VALUE);
                 upper = g.root + (uint64_t)child;
                 a.upper = upper;
                 a.kx = i, a.ky = j, a.kz = k;
@@ -80,20 +82,54 @@ __device__ __forceinline__ float vr_lookup(const VrGridDev& g, VrAcc& a, int32_t
             const uint32_t n = ((((uint32_t)i & 4095u) >> 7) << 10) | ((((uint32_t)j & 4095u) >> 7) << 5) |
                                (((uint32_t)k & 4095u) >> 7);
             const uint32_t m = vr_ld_u32(b + upper + VR_UPPER_OFF_CHILD_MASK + 4u * (n >> 5));
-            if (!((m >> (n & 31u)) & 1u)) return vr_ld_f32(b + upper + VR_UPPER_OFF_TABLE + 8u * n);
+            if (!((m >> (n & 31u)) & 1u)) return log2dim = 7, vr_ld_f32(b + upper + VR_UPPER_OFF_TABLE + 8u * n);
             lower = upper + vr_ld_u64(b + upper + VR_UPPER_OFF_TABLE + 8u * n);
             a.lower = lower;
             a.kx = i, a.ky = j, a.kz = k;
         }
         const uint32_t n = ((((uint32_t)i & 127u) >> 3) << 8) | ((((uint32_t)j & 127u) >> 3) << 4) | (((uint32_t)k & 127u) >> 3);
         const uint32_t m = vr_ld_u32(b + lower + VR_LOWER_OFF_CHILD_MASK + 4u * (n >> 5));
-        if (!((m >> (n & 31u)) & 1u)) return vr_ld_f32(b + lower + VR_LOWER_OFF_TABLE + 8u * n);
+        if (!((m >> (n & 31u)) & 1u)) return log2dim = 3, vr_ld_f32(b + lower + VR_LOWER_OFF_TABLE + 8u * n);
         leaf = lower + vr_ld_u64(b + lower + VR_LOWER_OFF_TABLE + 8u * n);
         a.leaf = leaf;
         a.kx = i, a.ky = j, a.kz = k;
     }
     const uint32_t n = (((uint32_t)i & 7u) << 6) | (((uint32_t)j & 7u) << 3) | ((uint32_t)k & 7u);
+    log2dim = 0;
     return vr_ld_f32(b + leaf + VR_LEAF_OFF_TABLE + 4u * n);
+}
+__device__ __forceinline__ float vr_lookup(const VrGridDev& g, VrAcc& a, int32_t i, int32_t j, int32_t k) {
+    int unused;
+    return vr_lookup_dim(g, a, i, j, k, unused);
+}
+
+// Empty-space skipping that keeps the sample lattice. A camera ray at parameter t, position p = o + d*t (as the shader
+// evaluates it in FP32), sits in a constant-value cube of edge 2^log2dim around voxel (i,j,k): a NanoVDB tile. Returns
+// t_lim such that every later lattice point o + d*t', t <= t' < t_lim, floors into that same cube AND into the root
+// bbox, whatever the FP32 rounding of o + d*t' does: the cube (clipped to the bbox) is shrunk by delta on every side,
+// delta being orders of magnitude above the rounding error of a position (two roundings per axis at 1.2e-7 relative)
+// and of t_lim itself. Positions move monotonically along each axis, so "inside the shrunk cube now" + "before the
+// shrunk exit plane" covers the whole stretch. If p is within delta of a face, nothing is skipped (returns -inf).
+// The caller still advances t by repeated `t += step` (the shader's own sequence), so every later sample position stays
+// bit-identical; the skipped points are in-bbox samples of the tile's value.
+__device__ __forceinline__ float vr_tile_exit(const VrGridDev& g, vr_f3 o, vr_f3 d, vr_f3 p, float t, int32_t i, int32_t j,
+                                              int32_t k, int log2dim) {
+    const int32_t mask = ~((1 << log2dim) - 1), dim = 1 << log2dim;
+    const int32_t c[3] = {i, j, k};
+    const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z}, pp[3] = {p.x, p.y, p.z};
+    float t_exit = 3.0e38f;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        int32_t lo = c[a] & mask, hi = lo + dim;
+        lo = lo > g.bmin[a] ? lo : g.bmin[a];
+        hi = hi < g.bmax[a] + 1 ? hi : g.bmax[a] + 1;
+        const float delta = 1.0e-3f + 1.0e-5f * (fabsf(pp[a]) + fabsf(oo[a])) + 2.0e-6f * fabsf(t);
+        const float flo = (float)lo + delta, fhi = (float)hi - delta;
+        if (!(pp[a] > flo && pp[a] < fhi)) return -3.0e38f;
+        if (dd[a] > 0.0f) t_exit = fminf(t_exit, (fhi - oo[a]) / dd[a]);
+        else if (dd[a] < 0.0f) t_exit = fminf(t_exit, (flo - oo[a]) / dd[a]);
+    }
+    return t_exit;
 }
 
 __device__ __forceinline__ bool vr_in_bbox(const VrGridDev& g, int32_t i, int32_t j, int32_t k) {

@@ -309,7 +309,8 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
                 const vr_f3 p = vr_add3(r.o, vr_scale3(r.d, t));
                 const int32_t i = (int32_t)vr_floor(p.x), j = (int32_t)vr_floor(p.y), k = (int32_t)vr_floor(p.z);
                 if (vr_in_bbox(g, i, j, k)) {
-                    const float val = vr_lookup(g, acc, i, j, k);
+                    int log2dim;
+                    const float val = vr_lookup_dim(g, acc, i, j, k, log2dim);
                     sref++;
                     if (val != 0.0f) {
                         if (FILL) {
@@ -318,6 +319,16 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
                         }
                         n++;
                         T = vr_mul(T, vr_exp(vr_mul(vr_mul(-val, u.absorptionCoefficient), step)));
+                    } else if (log2dim > 0) {
+                        // an empty tile: the following lattice points inside it (and inside the bbox) are in-bbox samples
+                        // of density 0 -- counted, nothing else to do. t keeps advancing by single adds (the shader's sequence).
+                        const float t_lim = vr_min(vr_tile_exit(g, r.o, r.d, p, t, i, j, k, log2dim), r.tmax);
+                        float tn = vr_add(t, step);
+                        while (tn < t_lim) {
+                            t = tn;
+                            sref++;
+                            tn = vr_add(t, step);
+                        }
                     }
                 }
                 t = vr_add(t, step);
