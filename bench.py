@@ -176,6 +176,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"], help="N>1 tile exchange")
+    ap.add_argument("--eval-variant", type=int, default=8, choices=[0, 1, 2, 3, 8],
+                    help="evaluation kernel for point/ray lists: 8 = ray-segment kernel (default), 2 = exact packed kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
     args = ap.parse_args()
@@ -207,6 +209,7 @@ def main():
 
     grid = vr.build_cloud_grid(cfg["n"])
     r = vr.VolumeRenderer(local_rank)
+    r.set_eval_variant(args.eval_variant)
     if world > 1:
         shared = torch.cuda.Stream()
         torch.cuda.set_stream(shared)
@@ -422,12 +425,19 @@ def main():
                 traffic = json.load(f).get(args.workload)
         except Exception:
             pass
+        point_kernels = {0: "k_eval<point,8>", 1: "k_eval_point2<8>", 2: "k_eval_point3<8,3,2>", 3: "k_eval_point3<6,4,2>",
+                         8: "k_eval_seg<2> (+ k_eval_point3x<8,3> on leftovers and near-light segments)"}
+        kernel_name = point_kernels[args.eval_variant] if algo in ("point", "ray") else ("k_eval<sphere,8>" if args.eval_variant == 0 else "k_eval_sphere2<8>")
+        # MUFU.RCP per evaluation: the exact kernels need one (plus a rsqrt for sphere lists); the ray-segment kernel shares
+        # one reciprocal between two lights
+        mufu_per_eval = (0.5 if args.eval_variant == 8 else 1.0) if algo in ("point", "ray") else 2.0
         roofline = {
-            "bound": "fp32", "kernel": {"point": "k_eval_point3<8,3,2>", "ray": "k_eval_point3<8,3,2>", "sphere": "k_eval_sphere2<8>", "beam": "k_eval_sphere2<8>"}.get(algo, algo), "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s",
+            "bound": "fp32", "kernel": kernel_name, "achieved": achieved, "peak": peak_fma, "unit": "TFLOP/s",
             "frac": achieved / peak_fma if peak_fma else None,
             "peak_source": "FFMA microbenchmark measured in this run (vr_ubench kind 0); MEASURED_PEAKS.json has no non-tensor FP32 figure",
             "flop_per_eval": flop, "evals_per_s": evals / eval_s if eval_s > 0 else 0.0,
-            "mufu_rcp_peak_per_s": peak_rcp * 1e12, "mufu_frac": (evals / eval_s) / (peak_rcp * 1e12) if peak_rcp and eval_s > 0 else None,
+            "mufu_rcp_peak_per_s": peak_rcp * 1e12, "mufu_per_eval": mufu_per_eval,
+            "mufu_frac": (evals / eval_s) * mufu_per_eval / (peak_rcp * 1e12) if peak_rcp and eval_s > 0 else None,
             "traffic": traffic,
             "hbm": {"bound": "hbm", "achieved": alg_bytes / (eval_s / args.steps) / 1e9 if eval_s > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "frac": (alg_bytes / (eval_s / args.steps) / 1e9) / hbm_peak if eval_s > 0 else None,
@@ -452,7 +462,7 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": cfg["desc"], "light_gen_groups": [cfg["gx"], 1, 1], "partition": f"row bands balanced by measured per-rank time; exchange: {exchange}" if world > 1 else "whole frame",
                        "l2": "per-step working set (1.3 GB of samples + 14 MB grid) exceeds the 126 MB L2; no flush needed",
-                       "bands": bands if world > 1 else None},
+                       "bands": bands if world > 1 else None, "eval_variant": args.eval_variant},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "contributions/s", "ms_per_step": e2e_s * 1e3 / args.steps,
                     "h2d_bytes_per_step": int(grid.nbytes + 96) * world, "d2h_bytes_per_step": int(W * H * 16)},

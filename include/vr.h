@@ -188,9 +188,19 @@ int vr_lookup_values(vr_ctx* ctx, const int32_t* ijk, uint64_t n, float* values_
 
 /* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
  * with the d2 < 1e-4 guard in the loop, 2 = packed kernel that runs the loop unguarded and repeats a thread block with the
- * guard when one of its threads saw d2 < 1e-4 (same results as 1; default), 3 = as 2 with 6 samples per thread. All follow
+ * guard when one of its threads saw d2 < 1e-4 (same results as 1), 3 = as 2 with 6 samples per thread, 8 = below. All follow
  * shaders/common_functions.h:186-194; results differ by rounding only. */
 int vr_set_eval_variant(vr_ctx* ctx, int variant);
+/* variant 8 = ray-segment kernel: the samples of one pixel lie on the camera ray, so eight consecutive samples share the
+ * per-light geometry (distance of the light from the ray, foot point) and two lights share one reciprocal. The line
+ * model drops the FP32 rounding of the sample positions (~1e-5 world units), a relative error of 2e-5/d on the term of a
+ * light at distance d; every thread that came closer than `distance` (default 0.25, raised per segment when its samples
+ * deviate more from their line) to any light hands its samples to variant 2's exact kernel, as are the samples that do
+ * not fill a segment. Measured pixel error against the exact variants: see tests/test_gpu_parity.py. */
+int vr_set_eval_near_distance(vr_ctx* ctx, float distance);
+/* bookkeeping of the last variant-8 evaluation: out[0] = full segments, out[1] = leftover samples, out[2] = samples the
+ * exact kernel evaluated (leftovers + flagged) */
+int vr_get_eval_segment_counts(vr_ctx* ctx, uint64_t out[3]);
 /* the camera samples of the last vr_dispatch_compute_color (point/sphere/ray/beam) that reached the light loop, in pixel-major
  * march order: world x, y, z and weight T*val*step per sample (shaders/point_compute_color.comp:72-89). *count receives
  * the total; at most `capacity` samples (4 floats each) are copied. Diagnostic / test hook. */

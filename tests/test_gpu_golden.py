@@ -61,7 +61,7 @@ def test_light_gen_golden(r, name):
 
 
 @pytest.mark.parametrize("algo", ["point", "sphere", "ray", "beam"])
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 8])
 def test_gather_golden(r, algo, variant):
     r.ubo = r.default_ubo()
     r.update_ubo(frameCount=1, maxLights=100)
@@ -71,7 +71,7 @@ def test_gather_golden(r, algo, variant):
     r.dispatch_compute_color(algo)
     want = np.load(os.path.join(GOLD, f"frame_{algo}.npy"))
     rel, rmse = rel_err(r.read_frame_color(), want)
-    r.set_eval_variant(1)
+    r.set_eval_variant(8)
     assert rel <= REL_TOL and rmse <= RMSE_TOL, (rel, rmse)
 
 

@@ -275,7 +275,7 @@ def test_edge_cases(renderer, vr, pyoracle, oracle, cloud):
 @pytest.mark.parametrize("algo", ["point", "ray"])
 def test_near_light_guard_all_eval_variants(renderer, pyoracle, oracle, cloud, algo):
     """Lights placed ON camera samples (d2 = 0), inside the guard radius (d2 < 1e-4, contributes 0) and just outside it
-    (huge but finite): every evaluation kernel must agree with the oracle, and the speculative kernels (2, 3) must
+    (huge but finite): every evaluation kernel must agree with the oracle, and the speculative kernels (2, 3, 8) must
     take their guarded repeat path and still equal the guarded packed kernel (1) bit for bit."""
     grid = cloud(64)
     W, H = 96, 64
@@ -301,7 +301,7 @@ def test_near_light_guard_all_eval_variants(renderer, pyoracle, oracle, cloud, a
     lights = np.concatenate([base[:20], near, base[20:40]])
     ofc, _ = oracle.gather(grid, ou, algo, lights, skip_zero=True)
     out = {}
-    for variant in (0, 1, 2, 3):
+    for variant in (0, 1, 2, 3, 8):
         renderer.set_eval_variant(variant)
         redo0 = renderer.eval_redo_count()
         renderer.write_lights(lights)
@@ -313,8 +313,74 @@ def test_near_light_guard_all_eval_variants(renderer, pyoracle, oracle, cloud, a
         assert np.isfinite(out[variant]).all()
         if variant >= 2:
             assert renderer.eval_redo_count() > redo0, "the guarded repeat path was not exercised"
-    renderer.set_eval_variant(2)
+    renderer.set_eval_variant(8)
     assert np.array_equal(out[1], out[2]) and np.array_equal(out[1], out[3])
+    # the ray-segment kernel leaves every near-light sample to the exact kernel: same pixels up to the far-field model
+    rel, rmse = rel_err(out[8], out[2])
+    assert rel <= 1e-4, (rel, rmse)
+
+
+@pytest.mark.parametrize("algo", ["point", "ray"])
+def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo):
+    """The ray-segment kernel (variant 8) models a pixel's samples as points on the camera ray; whatever comes closer than
+    the near distance to a light must reach the exact kernel. 300 lights are dropped 0.02 .. 0.6 world units away from
+    randomly picked camera samples (all directions): the frame must match the exact kernel far inside the tolerance and
+    the oracle within it, whole-frame and as two tiles, and a light next to the camera plane must switch every segment
+    to the exact kernel (then the results are the exact kernel's, bit for bit)."""
+    grid = cloud(64)
+    W, H = 160, 96
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=400)
+    base, _, _, _ = oracle.light_gen(grid, ou, (4, 1, 1), 0)
+    _setup(renderer, grid, W, H, maxLights=400, frameCount=1)
+    renderer.set_eval_variant(2)
+    renderer.write_lights(base[:40])
+    renderer.clear_image()
+    renderer.dispatch_compute_color("point")
+    smp = renderer.read_samples()
+    rng = np.random.default_rng(7)
+    picks = smp[rng.integers(0, len(smp), 300), :3]
+    dirs = rng.normal(size=(300, 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    pos = (picks + dirs * rng.uniform(0.02, 0.6, (300, 1))).astype(np.float32)
+    near = np.zeros(300, pyoracle.LIGHT_DTYPE)
+    near["intensity"] = 0.05
+    if algo == "ray":
+        near["from"], near["to"] = pos, pos + np.float32([0.5, 0.3, 0.2])
+    else:
+        near["to"], near["from"] = pos, pos - np.float32([0.5, 0.3, 0.2])
+    lights = np.concatenate([base[:40], near])
+    res = {}
+    for variant in (2, 8):
+        renderer.set_eval_variant(variant)
+        renderer.write_lights(lights)
+        renderer.clear_image()
+        renderer.dispatch_compute_color(algo)
+        res[variant] = renderer.read_frame_color()
+    seg = renderer.eval_segment_counts()
+    assert seg["segments"] > 1000 and seg["exact"] > seg["leftovers"], seg
+    rel, rmse = rel_err(res[8], res[2])
+    assert rel <= 1e-4 and rmse <= 1e-6, (rel, rmse)
+    ofc, _ = oracle.gather(grid, ou, algo, lights, skip_zero=True)
+    rel, rmse = rel_err(res[8], ofc)
+    assert rel <= REL_TOL and rmse <= RMSE_TOL, (rel, rmse)
+    renderer.clear_image()
+    renderer.dispatch_compute_color(algo, (0, 0, W, 40))
+    renderer.dispatch_compute_color(algo, (0, 40, W, H - 40))
+    assert np.array_equal(renderer.read_frame_color(), res[8])
+    # a light within the near distance of the camera plane: no bounded pixel footprint, everything goes the exact way
+    cam = np.zeros(1, pyoracle.LIGHT_DTYPE)
+    cam["to"] = cam["from"] = np.float32(renderer.ubo.cameraPos[:]) + np.float32([0.3, -0.2, 0.1])
+    cam["intensity"] = 1.0
+    lights2 = np.concatenate([lights[:50], cam])
+    for variant in (2, 8):
+        renderer.set_eval_variant(variant)
+        renderer.write_lights(lights2)
+        renderer.clear_image()
+        renderer.dispatch_compute_color("point")
+        res[variant] = renderer.read_frame_color()
+    seg = renderer.eval_segment_counts()
+    assert seg["exact"] == seg["segments"] * 8 + seg["leftovers"], seg
+    assert np.array_equal(res[8], res[2])
 
 
 def test_argument_errors(renderer, vr, cloud):

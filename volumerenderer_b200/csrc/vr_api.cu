@@ -116,10 +116,16 @@ struct vr_ctx {
     DevBuf<unsigned long long> scan_tmp;
     DevBuf<VrSample> samples;
     DevBuf<float> contrib;
+    // ray-segment evaluation (eval_variant 8): segment table + index list of the exact kernel, rebuilt with the march
+    DevBuf<uint32_t> seg_first, seg_pix, seg_list, seg_base;
+    DevBuf<uint8_t> seg_flags;
+    unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
+    bool seg_valid = false;                    // tables match the cached march
+    float eval_near = 0.25f;                   // distance below which a (sample, light) term is left to the exact kernel
     DevBuf<VrEvalLight> eval_lights;
     DevBuf<float4> eval_lights2;
     DevBuf<float> path_tab;  // path mode: shadow-term table (k_path_table)
-    int eval_variant = 2;  // 0: scalar kernel, 1: packed FP32x2 kernel, 2/3: packed speculative kernel (point/ray lists)
+    int eval_variant = 8;  // 0: scalar kernel, 1: packed FP32x2 kernel, 2/3: packed speculative kernel, 8: ray-segment kernel (point/ray lists)
     DevBuf<uint32_t> light_steps;
     DevBuf<unsigned long long> light_offsets;
     unsigned long long* totals = nullptr;       // [0] samples, [1] expanded lights (device)
@@ -397,6 +403,8 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
+    VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 4 * sizeof(unsigned long long)));  // [3]: the flag_all word
+    VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 4 * sizeof(unsigned long long), c->stream));
     VR_CREATE_CUDA(cudaMemsetAsync(c->eval_redo, 0, sizeof(unsigned long long), c->stream));
     for (int k = 0; k < vr_ctx::kTimingSets; k++)
         for (int i = 0; i < 7; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tset[k].ev[i]));
@@ -450,6 +458,12 @@ int vr_destroy(vr_ctx* c) {
     if (c->ev_lg_done) cudaEventDestroy(c->ev_lg_done);
     if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     if (c->eval_redo) cudaFree(c->eval_redo);
+    if (c->seg_counts) cudaFree(c->seg_counts);
+    c->seg_first.release();
+    c->seg_pix.release();
+    c->seg_list.release();
+    c->seg_base.release();
+    c->seg_flags.release();
     if (c->accum) cudaFree(c->accum);
     if (c->rgba8) cudaFree(c->rgba8);
     if (c->own_frame_color) cudaFree(c->own_frame_color);
@@ -749,6 +763,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
         c->cached_samples = nsamples;
         c->march_key = key;
+        c->seg_valid = false;
     }
     VR_CUDA(c, c->contrib.reserve(nsamples + 1));
     c->nsamples_used = nsamples;
@@ -764,6 +779,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     uint32_t nl_launch = c->lights_external ? c->external_count : c->ubo.maxLights;
     if (nl_launch > c->light_capacity) nl_launch = c->light_capacity;
     VR_CUDA(c, cudaMemsetAsync(c->expand_overflow, 0, sizeof(uint32_t), st));
+    uint64_t eval_list_cap = nl_launch;  // upper bound of the evaluation list's length (the length itself lives on the device)
     if (expand) {
         VR_CUDA(c, c->light_steps.reserve(nl_launch + 1));
         VR_CUDA(c, c->light_offsets.reserve(nl_launch + 1));
@@ -777,6 +793,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             cap = c->totals_host[1];
             if (cap > (1ull << 32)) return fail(c, VR_E_ARG, "expanded light list of %llu entries is too large (lightRayStepSize too small?)", (unsigned long long)cap);
         }
+        eval_list_cap = cap;
         VR_CUDA(c, c->eval_lights.reserve(cap + 1));
         VR_CUDA(c, c->eval_lights2.reserve(2 * cap + 2));
         vrk_prepare_expand(st, c->lights.p, c->counter, c->ubo.lightRayStepSize, c->light_offsets.p, c->eval_lights.p,
@@ -818,8 +835,27 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
     else if (sphere)
         vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
-    else
-        vrk_eval_point_packed(st, c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->contrib.p, c->eval_redo);
+    else if (c->eval_variant == 8 && nsamples < 0xffffffffull) {
+        VrSegLists sl;
+        if (!c->seg_valid) {
+            VR_CUDA(c, c->seg_first.reserve(nsamples / 8 + 1));
+            VR_CUDA(c, c->seg_pix.reserve(nsamples / 8 + 1));
+            VR_CUDA(c, c->seg_flags.reserve(nsamples / 8 + 1));
+            VR_CUDA(c, c->seg_list.reserve(nsamples + 1));
+            VR_CUDA(c, c->seg_base.reserve(npix + 1));
+        }
+        sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.list = c->seg_list.p, sl.counts = c->seg_counts;
+        sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
+        sl.list_capacity = (uint32_t)nsamples;
+        if (!c->seg_valid) {
+            vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl);
+            c->seg_valid = true;
+        }
+        vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, c->px_counts.p, c->px_offsets.p, sl,
+                           c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, c->eval_near, c->contrib.p, c->eval_redo);
+    } else
+        vrk_eval_point_packed(st, c->eval_variant == 8 ? 2 : c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1,
+                              c->contrib.p, c->eval_redo);
     cudaEventRecord(t->ev[5], st);
     vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8);
     cudaEventRecord(t->ev[6], st);
@@ -1087,7 +1123,7 @@ int vr_timer_stop(vr_ctx* c, float* ms) {
     return VR_OK;
 }
 int vr_ubench(vr_ctx* c, int kind, double* result) {
-    if (!c || !result || kind < 0 || kind > 4) return VR_E_ARG;
+    if (!c || !result || kind < 0 || kind > 9) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
     float* sink = nullptr;
     VR_CUDA(c, cudaMalloc(&sink, 64));
@@ -1104,7 +1140,7 @@ int vr_ubench(vr_ctx* c, int kind, double* result) {
         }
         float ms = 0;
         cudaEventElapsedTime(&ms, c->tev[0], c->tev[1]);
-        const double rate = ops / (ms * 1e-3) * (kind == 0 ? 2.0 : (kind == 3 ? 4.0 : 1.0)) / 1e12;
+        const double rate = ops / (ms * 1e-3) * (kind == 0 ? 2.0 : (kind == 3 || kind >= 7) ? 4.0 : kind == 5 ? 6.0 : kind == 6 ? 5.0 : 1.0) / 1e12;
         if (rate > best) best = rate;
     }
     cudaFree(sink);
@@ -1135,9 +1171,25 @@ int vr_lookup_values(vr_ctx* c, const int32_t* ijk, uint64_t n, float* values_ou
 }
 
 int vr_set_eval_variant(vr_ctx* c, int variant) {
-    if (!c || variant < 0 || variant > 3) return VR_E_ARG;
+    if (!c || variant < 0 || (variant > 3 && variant != 8)) return VR_E_ARG;
     c->eval_variant = variant;
     return VR_OK;
+}
+
+int vr_set_eval_near_distance(vr_ctx* c, float distance) {
+    if (!c || !(distance >= 0.01f) || !(distance < 1.0e6f)) return VR_E_ARG;  // at least the 0.01 of the shader's own guard
+    c->eval_near = distance;
+    return VR_OK;
+}
+
+int vr_get_eval_segment_counts(vr_ctx* c, uint64_t out[3]) {
+    if (!c || !out) return VR_E_ARG;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    unsigned long long h[3] = {0, 0, 0};
+    VR_CUDA(c, cudaMemcpyAsync(h, c->seg_counts, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    out[0] = h[0], out[1] = h[1], out[2] = h[2];
+    return check_stream(c);
 }
 
 int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {

@@ -771,6 +771,318 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
     }
 }
 
+// ---- ray-segment variant: eight samples of one camera ray share the per-light geometry ----------------------------------
+// The samples of one pixel lie on a line: p_k = A + s_k * D + eps_k, A = the segment's first sample, D = the unit world
+// direction of the camera ray, |eps_k| = the FP32 rounding of the sample position (~1e-5 world units on the bench scene).
+// For a light at L, with M = L - A, b = M.D and h2 = |M - b D|^2 (the squared distance of the light from the ray),
+//     |L - p_k|^2 = (s_k - b)^2 + h2                                   (exact for eps_k = 0)
+// so once b and h2 are known (12 operations per segment and light) every further sample of the segment costs one add and
+// one fma instead of the six operations of the direct form: 3.5 FMA-pipe cycles per evaluation instead of 7. With the
+// distance this cheap the MUFU.RCP rate would bind alone (8 XU cycles per warp-evaluation), so two lights share one
+// reciprocal, W0/a + W1/b = (W0*b + W1*a) * rcp(a*b): FMA pipe 5.5 cycles, XU pipe 4.
+// Error: the model drops eps_k, a relative error of 2*|eps_k|/d on the term of a light at distance d. Segments that come
+// closer than rho to any light are therefore found beforehand (k_flag_near_segments, a geometric test from the light's
+// side: no per-evaluation bookkeeping in the hot loop) and handed to the exact kernel (k_eval_point3x, which also applies
+// the d2 < 1e-4 guard of common_functions.h:190), as is every segment whose measured residual
+// err = max_k |p_k - A - s_k D| + 3e-7 * max_k |s_k| exceeds rho / 5e3. Every term that is kept then has a relative
+// error below 2*err/rho <= 4e-4, typically 1e-5 (measured in tests/test_gpu_parity.py).
+// Samples that do not fill a segment (count mod 8 per pixel) go to the exact kernel as well.
+__global__ void __launch_bounds__(256) k_build_segments(const uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
+                                                        uint64_t npix, VrSegLists sl) {
+    const uint64_t p = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t c = p < npix ? counts[p] : 0u;
+    const uint32_t off = p < npix ? (uint32_t)offsets[p] : 0u;
+    const uint32_t q = c >> 3, r = c & 7u;
+    uint32_t qs = q, rs = r;  // inclusive warp scans
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, qs, o), b = __shfl_up_sync(0xffffffffu, rs, o);
+        if (lane >= (uint32_t)o) qs += a, rs += b;
+    }
+    unsigned long long qbase = 0, rbase = 0;
+    if (lane == 31) {
+        if (qs) qbase = atomicAdd(&sl.counts[0], (unsigned long long)qs);
+        if (rs) rbase = atomicAdd(&sl.counts[1], (unsigned long long)rs);
+    }
+    qbase = __shfl_sync(0xffffffffu, qbase, 31) + (qs - q);
+    rbase = __shfl_sync(0xffffffffu, rbase, 31) + (rs - r);
+    if (p < npix) sl.seg_base[p] = (uint32_t)qbase;
+    for (uint32_t i = 0; i < q; i++) {
+        sl.seg_first[qbase + i] = off + 8u * i;
+        sl.seg_pix[qbase + i] = (uint32_t)p;
+    }
+    for (uint32_t j = 0; j < r; j++) sl.list[rbase + j] = off + 8u * q + j;
+}
+
+// Which segments come closer than rho to a light? Decided geometrically, from the light's side, before the evaluation:
+// one thread block per entry of the light list. A camera ray t*D (D.z > 0, the reference camera looks down +z without
+// rotation, point_compute_color.comp:23-33) that passes within rho of v = L - camera has a point q with |q - v| <= rho,
+// so its image-plane coordinates x = q.x/q.z, y = q.y/q.z lie in the box spanned by (v.x -+ rho)/(v.z -+ rho); the pixels
+// of that box are tested exactly (distance of the light from the ray, position of the foot point against the span of
+// each of the pixel's segments). rho already carries a safety margin; if a light's ball reaches the camera plane the
+// kernel gives up and flags everything (flag_all). Flags are what k_eval_seg reads to hand a segment to the exact kernel.
+__global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __restrict__ lights, const unsigned long long* __restrict__ nlights_dev,
+                                                            vr_ubo u, float tan_scale, vr_tile tile, const uint32_t* __restrict__ counts,
+                                                            const unsigned long long* __restrict__ offsets,
+                                                            const VrSample* __restrict__ samples, VrSegLists sl, float rho) {
+    const uint64_t nl = *nlights_dev;
+    for (uint64_t li = blockIdx.x; li < nl; li += gridDim.x) {
+    const VrEvalLight L = lights[li];
+    const float cx = u.cameraPos[0], cy = u.cameraPos[1], cz = u.cameraPos[2];
+    const float vx = L.x - cx, vy = L.y - cy, vz = L.z - cz;
+    if (vz + rho < 0.0f) continue;  // behind the camera plane by more than rho: no forward ray comes near
+    if (vz - rho <= 1.0e-3f * rho) {
+        if (threadIdx.x == 0) *sl.flag_all = 1u;
+        continue;
+    }
+    const float W = (float)u.framebufferDim[0], H = (float)u.framebufferDim[1], aspect = W / H;
+    const float zn = vz - rho, zf = vz + rho;
+    const float xa = (vx - rho) / ((vx - rho) < 0.0f ? zn : zf), xb = (vx + rho) / ((vx + rho) < 0.0f ? zf : zn);
+    const float ya = (vy - rho) / ((vy - rho) < 0.0f ? zn : zf), yb = (vy + rho) / ((vy + rho) < 0.0f ? zf : zn);
+    // x = ((2 (px + 0.5) / W) - 1) * aspect * tan  <=>  px = (x / (aspect * tan) + 1) * W / 2 - 0.5 ; y decreases with py
+    const float fx0 = (xa / (aspect * tan_scale) + 1.0f) * 0.5f * W - 0.5f, fx1 = (xb / (aspect * tan_scale) + 1.0f) * 0.5f * W - 0.5f;
+    const float fy0 = (1.0f - yb / tan_scale) * 0.5f * H - 0.5f, fy1 = (1.0f - ya / tan_scale) * 0.5f * H - 0.5f;
+    const float lox = (float)tile.x0, hix = (float)(tile.x0 + tile.w) - 1.0f, loy = (float)tile.y0, hiy = (float)(tile.y0 + tile.h) - 1.0f;
+    if (fx1 < lox - 1.0f || fx0 > hix + 1.0f || fy1 < loy - 1.0f || fy0 > hiy + 1.0f) continue;
+    const int32_t px0 = (int32_t)fmaxf(floorf(fx0) - 1.0f, lox), px1 = (int32_t)fminf(ceilf(fx1) + 1.0f, hix);
+    const int32_t py0 = (int32_t)fmaxf(floorf(fy0) - 1.0f, loy), py1 = (int32_t)fminf(ceilf(fy1) + 1.0f, hiy);
+    const int32_t bw = px1 - px0 + 1, bh = py1 - py0 + 1;
+    if (bw <= 0 || bh <= 0) continue;
+    const float rho2 = rho * rho;
+    for (int64_t i = threadIdx.x; i < (int64_t)bw * bh; i += blockDim.x) {
+        const int32_t px = px0 + (int32_t)(i % bw), py = py0 + (int32_t)(i / bw);
+        const float x = ((2.0f * ((float)px + 0.5f)) / W - 1.0f) * aspect * tan_scale;
+        const float y = (1.0f - (2.0f * ((float)py + 0.5f)) / H) * tan_scale;
+        const float inv = rsqrtf(x * x + y * y + 1.0f);
+        const float dx = x * inv, dy = y * inv, dz = inv;
+        const float b = vx * dx + vy * dy + vz * dz;
+        const float ex = vx - b * dx, ey = vy - b * dy, ez = vz - b * dz;
+        if (ex * ex + ey * ey + ez * ez >= rho2) continue;
+        const uint64_t pix = (uint64_t)(py - (int32_t)tile.y0) * tile.w + (uint32_t)(px - (int32_t)tile.x0);
+        const uint32_t nseg = counts[pix] >> 3;
+        if (!nseg) continue;
+        const uint32_t off = (uint32_t)offsets[pix], sb = sl.seg_base[pix];
+        for (uint32_t k = 0; k < nseg; k++) {
+            const float4 p0 = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k);
+            const float4 p1 = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k + 7u);
+            const float s0 = (p0.x - cx) * dx + (p0.y - cy) * dy + (p0.z - cz) * dz;
+            const float s1 = (p1.x - cx) * dx + (p1.y - cy) * dy + (p1.z - cz) * dz;
+            if (b > s0 - rho && b < s1 + rho) sl.flags[sb + k] = 1;
+        }
+    }
+    }
+}
+
+__device__ __forceinline__ float2 neg2(const float2 v) { return make_float2(-v.x, -v.y); }  // folds into the operand modifier
+
+// b = (L - A).D and h2 = |(L - A) - b D|^2 for the two segments of the thread (x and y halves) against one light
+__device__ __forceinline__ void seg_light_geometry(const float4 qa, const float4 qb, const float2 (&A)[3], const float2 (&D)[3],
+                                                   float2& nb, float2& h2) {
+    const float2 Mx = __fadd2_rn(make_float2(qa.x, qa.y), neg2(A[0]));
+    const float2 My = __fadd2_rn(make_float2(qa.z, qa.w), neg2(A[1]));
+    const float2 Mz = __fadd2_rn(make_float2(qb.x, qb.y), neg2(A[2]));
+    float2 b = __fmul2_rn(Mx, D[0]);
+    b = __ffma2_rn(My, D[1], b);
+    b = __ffma2_rn(Mz, D[2], b);
+    nb = neg2(b);
+    const float2 px = __ffma2_rn(nb, D[0], Mx), py = __ffma2_rn(nb, D[1], My), pz = __ffma2_rn(nb, D[2], Mz);
+    h2 = __fmul2_rn(px, px);
+    h2 = __ffma2_rn(py, py, h2);
+    h2 = __ffma2_rn(pz, pz, h2);
+}
+
+constexpr int SEG_LEN = 8;                        // samples per segment
+constexpr int SEG_PER_CTA = 2 * EVAL_THREADS;     // two segments per thread: the x and y halves of every FP32x2 register
+
+template <int MINB>
+__global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
+                                                                  const VrSample* __restrict__ samples, VrSegLists sl,
+                                                                  const float4* __restrict__ lights2,
+                                                                  const unsigned long long* __restrict__ nlights_dev, float rho,
+                                                                  float* __restrict__ out) {
+    const uint64_t nseg = sl.counts[0];
+    const uint64_t seg_base = (uint64_t)blockIdx.x * SEG_PER_CTA;
+    if (seg_base >= nseg) return;  // the launch is sized by the capacity, the segment count lives on the device
+    const uint64_t nlights = *nlights_dev;
+    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
+    if (tid == 0 && ntiles > 0) {
+        const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
+        mbar_expect_tx(&bar[0], cnt * 32u);
+        tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
+    }
+
+    float2 s[SEG_LEN], acc[SEG_LEN], A[3], D[3];
+    float sw[2][SEG_LEN];
+    uint32_t first[2];
+    const bool redo_all = *sl.flag_all != 0u;
+    bool redo[2] = {false, false};  // per segment, so that what the exact kernel evaluates does not depend on the pairing
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
+        float a[3] = {1.0e6f, 1.0e6f, 1.0e6f}, d[3] = {1.0f, 0.0f, 0.0f}, sv[SEG_LEN];
+        first[h] = 0xffffffffu;
+#pragma unroll
+        for (int k = 0; k < SEG_LEN; k++) sv[k] = 0.0f, sw[h][k] = 0.0f;
+        if (seg < nseg) {
+            first[h] = sl.seg_first[seg];
+            const uint32_t pix = sl.seg_pix[seg];
+            const VrCamRay r = vr_camera_ray(g, u, tan_scale, tile.x0 + pix % tile.w, tile.y0 + pix / tile.w);
+            // world direction of the ray: the linear part of the index->world map applied to the index-space direction
+            const float vx = r.d.x * g.mat[0] + r.d.y * g.mat[1] + r.d.z * g.mat[2];
+            const float vy = r.d.x * g.mat[3] + r.d.y * g.mat[4] + r.d.z * g.mat[5];
+            const float vz = r.d.x * g.mat[6] + r.d.y * g.mat[7] + r.d.z * g.mat[8];
+            const float inv = 1.0f / sqrtf(vx * vx + vy * vy + vz * vz);
+            d[0] = vx * inv, d[1] = vy * inv, d[2] = vz * inv;
+            const float4* sp = reinterpret_cast<const float4*>(samples) + first[h];
+            float res2 = 0.0f, smax = 0.0f;
+#pragma unroll
+            for (int k = 0; k < SEG_LEN; k++) {
+                const float4 q = __ldg(sp + k);
+                if (k == 0) a[0] = q.x, a[1] = q.y, a[2] = q.z;
+                const float ex = q.x - a[0], ey = q.y - a[1], ez = q.z - a[2];
+                const float sk = ex * d[0] + ey * d[1] + ez * d[2];
+                const float rx = ex - sk * d[0], ry = ey - sk * d[1], rz = ez - sk * d[2];
+                res2 = fmaxf(res2, rx * rx + ry * ry + rz * rz);
+                smax = fmaxf(smax, fabsf(sk));
+                sv[k] = sk, sw[h][k] = q.w;
+            }
+            // near a light (decided by k_flag_near_segments), or samples too far off their line for the bound to hold
+            redo[h] = redo_all || sl.flags[seg] != 0 || !(5.0e3f * (sqrtf(res2) + 3.0e-7f * smax) <= rho);
+        }
+#pragma unroll
+        for (int k = 0; k < SEG_LEN; k++) {
+            if (h == 0) s[k].x = sv[k], acc[k] = make_float2(0.f, 0.f);
+            else s[k].y = sv[k];
+        }
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            if (h == 0) A[c].x = a[c], D[c].x = d[c];
+            else A[c].y = a[c], D[c].y = d[c];
+        }
+    }
+
+    for (uint64_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = (uint32_t)(tl & 1);
+        if (tid == 0 && tl + 1 < ntiles) {
+            const uint64_t nxt = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (uint32_t)((nlights - nxt) < EVAL2_TILE ? (nlights - nxt) : EVAL2_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
+        const uint64_t lo = tl * EVAL2_TILE;
+        const int cnt = (int)((nlights - lo) < EVAL2_TILE ? (nlights - lo) : EVAL2_TILE);
+        const float4* __restrict__ L = stage[buf];
+        int l = 0;
+#pragma unroll 1
+        for (; l + 2 <= cnt; l += 2) {
+            const float4 qa = L[2 * l], qb = L[2 * l + 1], ra = L[2 * l + 2], rb = L[2 * l + 3];
+            float2 nb0, h0, nb1, h1;
+            seg_light_geometry(qa, qb, A, D, nb0, h0);
+            seg_light_geometry(ra, rb, A, D, nb1, h1);
+            const float2 W0 = make_float2(qb.z, qb.w), W1 = make_float2(rb.z, rb.w);
+#pragma unroll
+            for (int k = 0; k < SEG_LEN; k++) {
+                const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
+                const float2 a = __ffma2_rn(u0, u0, h0), b = __ffma2_rn(u1, u1, h1);
+                const float2 ab = __fmul2_rn(a, b);
+                const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
+                acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
+            }
+        }
+        if (l < cnt) {  // odd tail of the list
+            const float4 qa = L[2 * l], qb = L[2 * l + 1];
+            float2 nb0, h0;
+            seg_light_geometry(qa, qb, A, D, nb0, h0);
+            const float2 W0 = make_float2(qb.z, qb.w);
+#pragma unroll
+            for (int k = 0; k < SEG_LEN; k++) {
+                const float2 u0 = __fadd2_rn(s[k], nb0);
+                const float2 a = __ffma2_rn(u0, u0, h0);
+                acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
+            }
+        }
+        __syncthreads();
+    }
+
+    const uint32_t npush = (redo[0] ? SEG_LEN : 0) + (redo[1] ? SEG_LEN : 0);
+    unsigned long long slot = 0;
+    if (npush) slot = atomicAdd(&sl.counts[2], (unsigned long long)npush);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        if (first[h] == 0xffffffffu) continue;
+#pragma unroll
+        for (int k = 0; k < SEG_LEN; k++) {
+            out[first[h] + k] = sw[h][k] * (h == 0 ? acc[k].x : acc[k].y);
+            if (redo[h] && slot + k < sl.list_capacity) sl.list[slot + k] = first[h] + k;
+        }
+        if (redo[h]) slot += SEG_LEN;
+    }
+}
+
+// The exact kernel (k_eval_point3's two passes) over an index list: leftovers of the segmentation and the samples
+// k_eval_seg flagged. Persistent CTAs walk the list in chunks; the list length lives on the device.
+template <int S, int MINB>
+__global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3x(const VrSample* __restrict__ samples,
+                                                                       const uint32_t* __restrict__ list,
+                                                                       const unsigned long long* __restrict__ nlist_dev,
+                                                                       const float4* __restrict__ lights2,
+                                                                       const unsigned long long* __restrict__ nlights_dev,
+                                                                       float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
+    constexpr int P = S / 2;
+    const uint64_t nlights = *nlights_dev, nlist = *nlist_dev;
+    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
+    __shared__ __align__(8) uint64_t bar[2];
+    const uint32_t tid = threadIdx.x;
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t it = 0;
+    for (uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S); base < nlist; base += (uint64_t)gridDim.x * (EVAL_THREADS * S)) {
+        float2 nsx[P], nsy[P], nsz[P], acc[P];
+        float sw[S];
+        uint32_t idx[S];
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+            float4 a = make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.f), b = a;
+            const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
+            idx[2 * p] = i0 < nlist ? list[i0] : 0xffffffffu;
+            idx[2 * p + 1] = i1 < nlist ? list[i1] : 0xffffffffu;
+            if (idx[2 * p] != 0xffffffffu) a = __ldg(reinterpret_cast<const float4*>(samples) + idx[2 * p]);
+            if (idx[2 * p + 1] != 0xffffffffu) b = __ldg(reinterpret_cast<const float4*>(samples) + idx[2 * p + 1]);
+            nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
+            sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
+            acc[p] = make_float2(0.f, 0.f);
+        }
+        float dmin = 3.0e38f;
+        eval_pass_packed<P, false, 2>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
+        if (__syncthreads_or(!(dmin >= 0.0001f))) {
+            if (tid == 0 && redo_count) atomicAdd(redo_count, 1ull);
+#pragma unroll
+            for (int p = 0; p < P; p++) acc[p] = make_float2(0.f, 0.f);
+            eval_pass_packed<P, true, 2>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
+        }
+#pragma unroll
+        for (int p = 0; p < P; p++) {
+            if (idx[2 * p] != 0xffffffffu) out[idx[2 * p]] = sw[2 * p] * acc[p].x;
+            if (idx[2 * p + 1] != 0xffffffffu) out[idx[2 * p + 1]] = sw[2 * p + 1] * acc[p].y;
+        }
+    }
+}
+
 // =====================================================================================================
 // resolve
 // =====================================================================================================
@@ -1049,6 +1361,43 @@ __global__ void __launch_bounds__(256) k_ubench(float* sink, int iters) {
         }
 #pragma unroll
         for (int j = 0; j < 8; j++) a[j] = b[j].x + b[j].y;
+    } else if (KIND == 5 || KIND == 6) {
+        // FFMA2 and scalar FFMA interleaved (KIND 5: 8 + 8 per round, KIND 6: 8 + 4): do the two FMA sub-pipes take them
+        // concurrently? counted as 32 "ops" per iteration like the others; the caller scales by the real flop count
+        float2 b[8];
+        const float2 s2 = make_float2(s, s), c2 = make_float2(c, c);
+#pragma unroll
+        for (int j = 0; j < 8; j++) b[j] = make_float2(a[j], a[j] + 0.5f);
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    b[j] = __ffma2_rn(b[j], s2, c2);
+                    if (KIND == 5 || (j & 1)) a[j] = fmaf(a[j], s, c);
+                }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) a[j] += b[j].x + b[j].y;
+    } else if (KIND >= 7 && KIND <= 9) {
+        // 8 FFMA2 per round plus 2 MUFU.RCP (7), 2 FMNMX3 (8) or both (9): what the neighbours cost the FMA pipe
+        float2 b[8];
+        const float2 s2 = make_float2(s, s), c2 = make_float2(c, c);
+        float m = 3.0e38f, q0 = s, q1 = c;
+#pragma unroll
+        for (int j = 0; j < 8; j++) b[j] = make_float2(a[j], a[j] + 0.5f);
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) b[j] = __ffma2_rn(b[j], s2, c2);
+                if (KIND != 8) q0 = rcp_approx(q0), q1 = rcp_approx(q1);
+                if (KIND != 7) m = fmin3(m, b[0].x, b[1].y), m = fmin3(m, b[2].x, b[3].y);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; j++) a[j] += b[j].x + b[j].y;
+        a[0] += m + q0 + q1;
     } else if (KIND == 4) {
         float2 X = make_float2(s, s), Y = make_float2(c, c), Z = make_float2(s + c, s + c);
         const float li = 1.0f;
@@ -1115,6 +1464,11 @@ double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters) {
     else if (kind == 1) k_ubench<1><<<blocks, threads, 0, st>>>(sink, iters);
     else if (kind == 3) k_ubench<3><<<blocks, threads, 0, st>>>(sink, iters);
     else if (kind == 4) k_ubench<4><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 5) k_ubench<5><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 6) k_ubench<6><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 7) k_ubench<7><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 8) k_ubench<8><<<blocks, threads, 0, st>>>(sink, iters);
+    else if (kind == 9) k_ubench<9><<<blocks, threads, 0, st>>>(sink, iters);
     else k_ubench<2><<<blocks, threads, 0, st>>>(sink, iters);
     return (double)blocks * threads * (double)iters * 32.0;  // 4 x 8 ops per iteration per thread
 }
@@ -1184,6 +1538,36 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
         case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out, redo_count); break;
         default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out); break;
     }
+}
+void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl) {
+    cudaMemsetAsync(sl.counts, 0, 3 * sizeof(unsigned long long), st);
+    if (!npix) return;
+    VR_COUNT(1);
+    k_build_segments<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, npix, sl);
+}
+void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
+                        uint64_t nsamples, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
+                        const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
+                        const unsigned long long* nlights_dev, float rho, float* out, unsigned long long* redo_count) {
+    if (nsamples == 0) return;
+    // the exact kernel's list restarts from the leftovers every frame; k_eval_seg appends the segments flagged below
+    cudaMemcpyAsync(sl.counts + 2, sl.counts + 1, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
+    const uint64_t seg_cap = nsamples / SEG_LEN;
+    if (seg_cap) {
+        cudaMemsetAsync(sl.flags, 0, seg_cap, st);
+        cudaMemsetAsync(sl.flag_all, 0, sizeof(uint32_t), st);
+        VR_COUNT(2);
+        const float margin = 1.02f * rho + 1.0e-3f;
+        if (nlights_capacity)
+            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples,
+                                                                          sl, margin);
+        k_eval_seg<2><<<(unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA), EVAL_THREADS, 0, st>>>(
+            g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, out);
+    }
+    VR_COUNT(1);
+    const uint64_t chunks = (nsamples + (uint64_t)EVAL_THREADS * 8 - 1) / ((uint64_t)EVAL_THREADS * 8);
+    const unsigned grid = (unsigned)(chunks < 148u * 3u ? chunks : 148u * 3u);
+    k_eval_point3x<8, 3><<<grid, EVAL_THREADS, 0, st>>>(samples, sl.list, sl.counts + 2, lights2, nlights_dev, out, redo_count);
 }
 void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                             const unsigned long long* nlights_dev, float radius, float* out) {

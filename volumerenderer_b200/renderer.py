@@ -104,8 +104,19 @@ class VolumeRenderer:
 
     def set_eval_variant(self, variant):
         """0: scalar FP32 evaluation kernel, 1: packed FP32x2 kernel with the guard in the loop, 2: packed speculative
-        kernel (unguarded loop, guarded repeat when needed; same results as 1; default), 3: as 2, 6 samples per thread."""
+        kernel (unguarded loop, guarded repeat when needed; same results as 1; default), 3: as 2, 6 samples per thread,
+        8: ray-segment kernel (include/vr.h)."""
         self._check(self._L.vr_set_eval_variant(self._ctx, int(variant)))
+
+    def set_eval_near_distance(self, distance):
+        """Variant 8: lights closer than this to any sample of a thread send its samples to the exact kernel."""
+        self._check(self._L.vr_set_eval_near_distance(self._ctx, float(distance)))
+
+    def eval_segment_counts(self):
+        """Variant 8 bookkeeping: dict(segments, leftovers, exact) of the last evaluation."""
+        a = (C.c_uint64 * 3)()
+        self._check(self._L.vr_get_eval_segment_counts(self._ctx, a))
+        return dict(segments=int(a[0]), leftovers=int(a[1]), exact=int(a[2]))
 
     def read_samples(self):
         """(n, 4) float32: world x, y, z, weight of the last gather's camera samples (pixel-major, march order)."""
