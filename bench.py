@@ -54,6 +54,25 @@ class ClockSampler:
         self.proc = None
 
     def start(self):
+        # NVML in a thread (a sample every 5 ms: the timed region of the default run is ~0.3 s); nvidia-smi as the fallback
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.gpu
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [v.strip() for v in vis.split(",") if v.strip()]
+            if ids and all(v.isdigit() for v in ids) and self.gpu < len(ids):
+                idx = int(ids[self.gpu])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.nvml = pynvml
+            self.samples = []
+            self.running = True
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.QUERY}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -63,11 +82,35 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        n = self.nvml
+        while self.running:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                mx = n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)
+                get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+                self.samples.append((sm, mx, int(get(self.handle))))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def _stop_nvml(self):
+        self.running = False
+        self.thread.join(timeout=1)
+        bits = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
+        sm = [a for a, _, _ in self.samples]
+        mx = [b for _, b, _ in self.samples]
+        reasons = sorted(k for k, bit in bits.items() if any(r & bit for _, _, r in self.samples))
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None,
+                "reasons": reasons, "samples": len(sm), "source": "nvml"}
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
     def stop(self):
+        if getattr(self, "nvml", None):
+            return self._stop_nvml()
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.12)

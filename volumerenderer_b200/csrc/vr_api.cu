@@ -833,8 +833,6 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
     if (c->eval_variant == 0)
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
-    else if (sphere)
-        vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
     else if (c->eval_variant == 8 && nsamples < 0xffffffffull) {
         VrSegLists sl;
         if (!c->seg_valid) {
@@ -852,8 +850,11 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             c->seg_valid = true;
         }
         vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, c->px_counts.p, c->px_offsets.p, sl,
-                           c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, c->eval_near, c->contrib.p, c->eval_redo);
-    } else
+                           c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, c->eval_near, sphere, c->ubo.beamRadius,
+                           c->contrib.p, c->eval_redo);
+    } else if (sphere)
+        vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
+    else
         vrk_eval_point_packed(st, c->eval_variant == 8 ? 2 : c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1,
                               c->contrib.p, c->eval_redo);
     cudaEventRecord(t->ev[5], st);

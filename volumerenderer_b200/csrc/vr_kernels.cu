@@ -570,12 +570,20 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
 // (ulp(50) = 4e-6, amplified by 1/|cur - p| near the sphere surface), so the kernel tracks the reference's own
 // arithmetic noise instead of the ideal (|v| - R)^2. 16 packed + 4 MUFU + 4 guard/accumulate slots per pair of
 // evaluations: FMA pipe 17 cycles, XU pipe 16 cycles per evaluation.
-template <int S>
+// LIST: the kernel evaluates samples[list[i]], i < *nlist_dev (the leftovers and near-light segments of the ray-segment
+// kernel); the launch is sized by an upper bound of the list length and CTAs beyond it leave at once.
+template <int S, bool LIST>
 __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                                   const uint32_t* __restrict__ list,
+                                                                   const unsigned long long* __restrict__ nlist_dev,
                                                                    const float4* __restrict__ lights2,
                                                                    const unsigned long long* __restrict__ nlights_dev, float radius,
                                                                    float* __restrict__ out) {
     constexpr int P = S / 2;
+    if (LIST) {
+        nsamples = *nlist_dev;
+        if ((uint64_t)blockIdx.x * (EVAL_THREADS * S) >= nsamples) return;
+    }
     const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
@@ -599,8 +607,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
     for (int p = 0; p < P; p++) {
         float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
         const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
-        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + i0);
-        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + i1);
+        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + (LIST ? (uint64_t)list[i0] : i0));
+        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + (LIST ? (uint64_t)list[i1] : i1));
         nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
         sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
         acc[p] = make_float2(0.f, 0.f);
@@ -648,8 +656,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
 #pragma unroll
     for (int p = 0; p < P; p++) {
         const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
-        if (i0 < nsamples) out[i0] = sw[2 * p] * acc[p].x;
-        if (i1 < nsamples) out[i1] = sw[2 * p + 1] * acc[p].y;
+        if (i0 < nsamples) out[LIST ? (uint64_t)list[i0] : i0] = sw[2 * p] * acc[p].x;
+        if (i1 < nsamples) out[LIST ? (uint64_t)list[i1] : i1] = sw[2 * p + 1] * acc[p].y;
     }
 }
 
@@ -724,12 +732,19 @@ __device__ __forceinline__ void eval_pass_packed(float4 (&stage)[2][2 * EVAL2_TI
     }
 }
 
-template <int S, int MINB, int UNROLL>  // S samples per thread (even), MINB resident CTAs per SM
+// LIST: samples[list[i]], i < *nlist_dev, as in k_eval_sphere2
+template <int S, int MINB, int UNROLL, bool LIST = false>  // S samples per thread (even), MINB resident CTAs per SM
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSample* __restrict__ samples, uint64_t nsamples,
+                                                              const uint32_t* __restrict__ list,
+                                                              const unsigned long long* __restrict__ nlist_dev,
                                                               const float4* __restrict__ lights2,
                                                               const unsigned long long* __restrict__ nlights_dev,
                                                               float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
     constexpr int P = S / 2;
+    if (LIST) {
+        nsamples = *nlist_dev;
+        if ((uint64_t)blockIdx.x * (EVAL_THREADS * S) >= nsamples) return;
+    }
     const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
@@ -748,8 +763,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
         // samples beyond the end sit far away (d2 ~ 3e12): they never trip the d2 check and are never stored
         float4 a = make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.f), b = a;
         const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
-        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + i0);
-        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + i1);
+        if (i0 < nsamples) a = __ldg(reinterpret_cast<const float4*>(samples) + (LIST ? (uint64_t)list[i0] : i0));
+        if (i1 < nsamples) b = __ldg(reinterpret_cast<const float4*>(samples) + (LIST ? (uint64_t)list[i1] : i1));
         nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
         sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
         acc[p] = make_float2(0.f, 0.f);
@@ -766,8 +781,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
 #pragma unroll
     for (int p = 0; p < P; p++) {
         const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
-        if (i0 < nsamples) out[i0] = sw[2 * p] * acc[p].x;
-        if (i1 < nsamples) out[i1] = sw[2 * p + 1] * acc[p].y;
+        if (i0 < nsamples) out[LIST ? (uint64_t)list[i0] : i0] = sw[2 * p] * acc[p].x;
+        if (i1 < nsamples) out[LIST ? (uint64_t)list[i1] : i1] = sw[2 * p + 1] * acc[p].y;
     }
 }
 
@@ -782,7 +797,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
 // reciprocal, W0/a + W1/b = (W0*b + W1*a) * rcp(a*b): FMA pipe 5.5 cycles, XU pipe 4.
 // Error: the model drops eps_k, a relative error of 2*|eps_k|/d on the term of a light at distance d. Segments that come
 // closer than rho to any light are therefore found beforehand (k_flag_near_segments, a geometric test from the light's
-// side: no per-evaluation bookkeeping in the hot loop) and handed to the exact kernel (k_eval_point3x, which also applies
+// side: no per-evaluation bookkeeping in the hot loop) and handed to the exact kernel (k_eval_point3<LIST>, which also applies
 // the d2 < 1e-4 guard of common_functions.h:190), as is every segment whose measured residual
 // err = max_k |p_k - A - s_k D| + 3e-7 * max_k |s_k| exceeds rho / 5e3. Every term that is kept then has a relative
 // error below 2*err/rho <= 4e-4, typically 1e-5 (measured in tests/test_gpu_parity.py).
@@ -895,12 +910,25 @@ __device__ __forceinline__ void seg_light_geometry(const float4 qa, const float4
 constexpr int SEG_LEN = 8;                        // samples per segment
 constexpr int SEG_PER_CTA = 2 * EVAL_THREADS;     // two segments per thread: the x and y halves of every FP32x2 register
 
-template <int MINB>
+// squared distance that enters the reciprocal. Point-type lists: the distance to the light itself. Sphere-type lists
+// (sphere lights, beam sub-points; common_functions.h:182-201): the light acts from the nearest point of its sphere of
+// radius R, which is |p - O| - R away from the sample; k_flag_near_segments is run with rho + R for these lists, so the
+// near-surface samples, where the shader's own rounding of that point matters, are the exact kernel's.
+template <bool SPHERE>
+__device__ __forceinline__ float2 seg_dist2(const float2 l2, const float2 nR) {
+    if (!SPHERE) return l2;
+    const float2 len = __fmul2_rn(l2, make_float2(rsqrt_approx(l2.x), rsqrt_approx(l2.y)));
+    const float2 d = __fadd2_rn(len, nR);
+    return __fmul2_rn(d, d);
+}
+
+template <int MINB, bool SPHERE>
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                                   const VrSample* __restrict__ samples, VrSegLists sl,
                                                                   const float4* __restrict__ lights2,
                                                                   const unsigned long long* __restrict__ nlights_dev, float rho,
-                                                                  float* __restrict__ out) {
+                                                                  float radius, float* __restrict__ out) {
+    const float2 nR = make_float2(-radius, -radius);
     const uint64_t nseg = sl.counts[0];
     const uint64_t seg_base = (uint64_t)blockIdx.x * SEG_PER_CTA;
     if (seg_base >= nseg) return;  // the launch is sized by the capacity, the segment count lives on the device
@@ -994,7 +1022,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
 #pragma unroll
             for (int k = 0; k < SEG_LEN; k++) {
                 const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
-                const float2 a = __ffma2_rn(u0, u0, h0), b = __ffma2_rn(u1, u1, h1);
+                const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
                 const float2 ab = __fmul2_rn(a, b);
                 const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
                 acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
@@ -1008,7 +1036,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
 #pragma unroll
             for (int k = 0; k < SEG_LEN; k++) {
                 const float2 u0 = __fadd2_rn(s[k], nb0);
-                const float2 a = __ffma2_rn(u0, u0, h0);
+                const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR);
                 acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
             }
         }
@@ -1027,59 +1055,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             if (redo[h] && slot + k < sl.list_capacity) sl.list[slot + k] = first[h] + k;
         }
         if (redo[h]) slot += SEG_LEN;
-    }
-}
-
-// The exact kernel (k_eval_point3's two passes) over an index list: leftovers of the segmentation and the samples
-// k_eval_seg flagged. Persistent CTAs walk the list in chunks; the list length lives on the device.
-template <int S, int MINB>
-__global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3x(const VrSample* __restrict__ samples,
-                                                                       const uint32_t* __restrict__ list,
-                                                                       const unsigned long long* __restrict__ nlist_dev,
-                                                                       const float4* __restrict__ lights2,
-                                                                       const unsigned long long* __restrict__ nlights_dev,
-                                                                       float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
-    constexpr int P = S / 2;
-    const uint64_t nlights = *nlights_dev, nlist = *nlist_dev;
-    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
-    __shared__ __align__(8) uint64_t bar[2];
-    const uint32_t tid = threadIdx.x;
-    if (tid == 0) {
-        mbar_init(&bar[0], 1);
-        mbar_init(&bar[1], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    uint32_t it = 0;
-    for (uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S); base < nlist; base += (uint64_t)gridDim.x * (EVAL_THREADS * S)) {
-        float2 nsx[P], nsy[P], nsz[P], acc[P];
-        float sw[S];
-        uint32_t idx[S];
-#pragma unroll
-        for (int p = 0; p < P; p++) {
-            float4 a = make_float4(1.0e6f, 1.0e6f, 1.0e6f, 0.f), b = a;
-            const uint64_t i0 = base + (uint64_t)(2 * p) * EVAL_THREADS + tid, i1 = i0 + EVAL_THREADS;
-            idx[2 * p] = i0 < nlist ? list[i0] : 0xffffffffu;
-            idx[2 * p + 1] = i1 < nlist ? list[i1] : 0xffffffffu;
-            if (idx[2 * p] != 0xffffffffu) a = __ldg(reinterpret_cast<const float4*>(samples) + idx[2 * p]);
-            if (idx[2 * p + 1] != 0xffffffffu) b = __ldg(reinterpret_cast<const float4*>(samples) + idx[2 * p + 1]);
-            nsx[p] = make_float2(-a.x, -b.x), nsy[p] = make_float2(-a.y, -b.y), nsz[p] = make_float2(-a.z, -b.z);
-            sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
-            acc[p] = make_float2(0.f, 0.f);
-        }
-        float dmin = 3.0e38f;
-        eval_pass_packed<P, false, 2>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
-        if (__syncthreads_or(!(dmin >= 0.0001f))) {
-            if (tid == 0 && redo_count) atomicAdd(redo_count, 1ull);
-#pragma unroll
-            for (int p = 0; p < P; p++) acc[p] = make_float2(0.f, 0.f);
-            eval_pass_packed<P, true, 2>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
-        }
-#pragma unroll
-        for (int p = 0; p < P; p++) {
-            if (idx[2 * p] != 0xffffffffu) out[idx[2 * p]] = sw[2 * p] * acc[p].x;
-            if (idx[2 * p + 1] != 0xffffffffu) out[idx[2 * p + 1]] = sw[2 * p + 1] * acc[p].y;
-        }
     }
 }
 
@@ -1534,8 +1509,8 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
     VR_COUNT(1);
     auto grid = [&](int S) { return (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S)); };
     switch (variant) {
-        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out, redo_count); break;
-        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out, redo_count); break;
+        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
+        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
         default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out); break;
     }
 }
@@ -1548,7 +1523,8 @@ void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned 
 void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
-                        const unsigned long long* nlights_dev, float rho, float* out, unsigned long long* redo_count) {
+                        const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
+                        unsigned long long* redo_count) {
     if (nsamples == 0) return;
     // the exact kernel's list restarts from the leftovers every frame; k_eval_seg appends the segments flagged below
     cudaMemcpyAsync(sl.counts + 2, sl.counts + 1, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
@@ -1557,17 +1533,25 @@ void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, fl
         cudaMemsetAsync(sl.flags, 0, seg_cap, st);
         cudaMemsetAsync(sl.flag_all, 0, sizeof(uint32_t), st);
         VR_COUNT(2);
-        const float margin = 1.02f * rho + 1.0e-3f;
+        // sphere-type lists: distances are measured from the sphere's surface, the flags from its centre
+        const float margin = 1.02f * (rho + (sphere ? radius : 0.0f)) + 1.0e-3f;
         if (nlights_capacity)
             k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples,
                                                                           sl, margin);
-        k_eval_seg<2><<<(unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA), EVAL_THREADS, 0, st>>>(
-            g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, out);
+        const unsigned seg_grid = (unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA);
+        if (sphere)
+            k_eval_seg<2, true><<<seg_grid, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+        else
+            k_eval_seg<2, false><<<seg_grid, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
     }
+    // exact kernel over the list: launched over the list's upper bound (every sample), CTAs beyond its length leave at once
     VR_COUNT(1);
-    const uint64_t chunks = (nsamples + (uint64_t)EVAL_THREADS * 8 - 1) / ((uint64_t)EVAL_THREADS * 8);
-    const unsigned grid = (unsigned)(chunks < 148u * 3u ? chunks : 148u * 3u);
-    k_eval_point3x<8, 3><<<grid, EVAL_THREADS, 0, st>>>(samples, sl.list, sl.counts + 2, lights2, nlights_dev, out, redo_count);
+    const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * 8 - 1) / ((uint64_t)EVAL_THREADS * 8));
+    if (sphere)
+        k_eval_sphere2<8, true><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, sl.list, sl.counts + 2, lights2, nlights_dev, radius, out);
+    else
+        k_eval_point3<8, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, sl.list, sl.counts + 2, lights2, nlights_dev, out,
+                                                                     redo_count);
 }
 void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                             const unsigned long long* nlights_dev, float radius, float* out) {
@@ -1575,7 +1559,7 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
     VR_COUNT(1);
     constexpr int S = 8;
     const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S));
-    k_eval_sphere2<S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, radius, out);
+    k_eval_sphere2<S, false><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, radius, out);
 }
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               const unsigned long long* nlights_dev, float radius, float* out) {

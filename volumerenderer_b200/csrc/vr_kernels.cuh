@@ -66,9 +66,9 @@ void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsa
 // k_eval_point3 with 8 / 6 samples per thread; redo_count (device, may be NULL) counts CTAs that repeated with the guard
 void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                            const unsigned long long* nlights_dev, float* out, unsigned long long* redo_count);
-// ray-segment kernel for point-type lists (variant 8): eight consecutive samples of one camera ray share the per-light
+// ray-segment kernel (variant 8; point-type lists, and sphere-type lists with sphere = 1): eight consecutive samples of one camera ray share the per-light
 // geometry (k_eval_seg); what does not fill a segment, and every sample whose thread came closer than the segment's
-// rho to a light (k_flag_near_segments), is evaluated by the exact kernel over an index list (k_eval_point3x).
+// rho to a light (k_flag_near_segments), is evaluated by the exact kernel over an index list (k_eval_point3 / k_eval_sphere2 in LIST mode).
 struct VrSegLists {
     uint32_t* seg_first;          // first sample of every full segment (index into the sample array)
     uint32_t* seg_pix;            // its pixel (tile-local, row-major)
@@ -85,7 +85,8 @@ void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned 
 void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
-                        const unsigned long long* nlights_dev, float rho, float* out, unsigned long long* redo_count);
+                        const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
+                        unsigned long long* redo_count);
 // packed FP32x2 kernel for sphere lights / beam sub-points (common_functions.h:182-201)
 void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                             const unsigned long long* nlights_dev, float radius, float* out);
