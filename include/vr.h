@@ -194,9 +194,10 @@ int vr_set_eval_variant(vr_ctx* ctx, int variant);
 /* variant 8 = ray-segment kernel: the samples of one pixel lie on the camera ray, so eight consecutive samples share the
  * per-light geometry (distance of the light from the ray, foot point) and two lights share one reciprocal. The line
  * model drops the FP32 rounding of the sample positions (~1e-5 world units), a relative error of 2e-5/d on the term of a
- * light at distance d; every thread that came closer than `distance` (default 0.25, raised per segment when its samples
- * deviate more from their line) to any light hands its samples to variant 2's exact kernel, as are the samples that do
- * not fill a segment. Measured pixel error against the exact variants: see tests/test_gpu_parity.py. */
+ * light at distance d; every segment that comes closer than `distance` to a light (found geometrically before the
+ * evaluation; default 0.25, scaled by sqrt(1000 / list length) down to at most 0.1 for long ray/beam sub-point lists) or
+ * whose samples deviate from their line by more than distance / 5e3 goes to variant 2's exact kernel, as do the samples
+ * that do not fill a segment. Measured pixel error against the exact variants: see tests/test_gpu_parity.py. */
 int vr_set_eval_near_distance(vr_ctx* ctx, float distance);
 /* bookkeeping of the last variant-8 evaluation: out[0] = full segments, out[1] = leftover samples, out[2] = samples the
  * exact kernel evaluated (leftovers + flagged) */

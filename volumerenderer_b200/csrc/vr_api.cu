@@ -849,8 +849,15 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl);
             c->seg_valid = true;
         }
+        // near/far boundary: the share of flagged segments grows with the list length times rho^2, so long lists (ray and
+        // beam sub-points) get a smaller rho, down to 0.1 (the kernel's own residual check keeps 2*err/rho <= 4e-4)
+        float rho = c->eval_near;
+        if (eval_list_cap > 1000 && rho > 0.1f) {
+            rho *= sqrtf(1000.0f / (float)eval_list_cap);
+            if (rho < 0.1f) rho = 0.1f;
+        }
         vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, c->px_counts.p, c->px_offsets.p, sl,
-                           c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, c->eval_near, sphere, c->ubo.beamRadius,
+                           c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)
         vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
