@@ -320,8 +320,11 @@ def test_near_light_guard_all_eval_variants(renderer, pyoracle, oracle, cloud, a
     assert rel <= 1e-4, (rel, rmse)
 
 
-@pytest.mark.parametrize("algo", ["point", "ray"])
-def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo):
+@pytest.mark.parametrize("algo,cam", [("point", None), ("ray", None), ("sphere", None), ("beam", None),
+                                      ("point", dict(cameraPos=(14.0, 31.0, -58.0), fov=70.0)),
+                                      ("sphere", dict(cameraPos=(-9.0, 8.0, -40.0), fov=28.0)),
+                                      ("point", dict(cameraPos=(3.0, 22.0, -6.0), fov=60.0))])   # camera inside the cloud
+def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo, cam):
     """The ray-segment kernel (variant 8) models a pixel's samples as points on the camera ray; whatever comes closer than
     the near distance to a light must reach the exact kernel. 300 lights are dropped 0.02 .. 0.6 world units away from
     randomly picked camera samples (all directions): the frame must match the exact kernel far inside the tolerance and
@@ -329,9 +332,10 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo):
     to the exact kernel (then the results are the exact kernel's, bit for bit)."""
     grid = cloud(64)
     W, H = 160, 96
-    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=400)
+    cam = cam or {}
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=400, **cam)
     base, _, _, _ = oracle.light_gen(grid, ou, (4, 1, 1), 0)
-    _setup(renderer, grid, W, H, maxLights=400, frameCount=1)
+    _setup(renderer, grid, W, H, maxLights=400, frameCount=1, **cam)
     renderer.set_eval_variant(2)
     renderer.write_lights(base[:40])
     renderer.clear_image()
@@ -344,7 +348,7 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo):
     pos = (picks + dirs * rng.uniform(0.02, 0.6, (300, 1))).astype(np.float32)
     near = np.zeros(300, pyoracle.LIGHT_DTYPE)
     near["intensity"] = 0.05
-    if algo == "ray":
+    if algo in ("ray", "beam", "sphere"):   # sub-points start at `from`; sphere lights sit at `from` (sphere_compute_color.comp:12)
         near["from"], near["to"] = pos, pos + np.float32([0.5, 0.3, 0.2])
     else:
         near["to"], near["from"] = pos, pos - np.float32([0.5, 0.3, 0.2])
@@ -357,7 +361,7 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo):
         renderer.dispatch_compute_color(algo)
         res[variant] = renderer.read_frame_color()
     seg = renderer.eval_segment_counts()
-    assert seg["segments"] > 1000 and seg["exact"] > seg["leftovers"], seg
+    assert seg["segments"] > 200 and seg["exact"] > seg["leftovers"], seg
     rel, rmse = rel_err(res[8], res[2])
     assert rel <= 1e-4 and rmse <= 1e-6, (rel, rmse)
     ofc, _ = oracle.gather(grid, ou, algo, lights, skip_zero=True)
