@@ -117,10 +117,11 @@ struct vr_ctx {
     DevBuf<VrSample> samples;
     DevBuf<float> contrib;
     // ray-segment evaluation (eval_variant 8): segment table + index list of the exact kernel, rebuilt with the march
-    DevBuf<uint32_t> seg_first, seg_pix, seg_list, seg_base;
+    DevBuf<uint32_t> seg_first, seg_pix, seg_flag, seg16_first, seg16_pix, seg16_flag, seg_list, seg_base;
     DevBuf<uint8_t> seg_flags;
     unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
     bool seg_valid = false;                    // tables match the cached march
+    int seg_pairs = -1;                        // ... and were built for point-type (1) / sphere-type (0) lists
     float eval_near = 0.25f;                   // distance below which a (sample, light) term is left to the exact kernel
     DevBuf<VrEvalLight> eval_lights;
     DevBuf<float4> eval_lights2;
@@ -403,8 +404,8 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
-    VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 4 * sizeof(unsigned long long)));  // [3]: the flag_all word
-    VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 4 * sizeof(unsigned long long), c->stream));
+    VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 6 * sizeof(unsigned long long)));  // layout: VrSegLists::counts
+    VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 6 * sizeof(unsigned long long), c->stream));
     VR_CREATE_CUDA(cudaMemsetAsync(c->eval_redo, 0, sizeof(unsigned long long), c->stream));
     for (int k = 0; k < vr_ctx::kTimingSets; k++)
         for (int i = 0; i < 7; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tset[k].ev[i]));
@@ -463,6 +464,10 @@ int vr_destroy(vr_ctx* c) {
     c->seg_pix.release();
     c->seg_list.release();
     c->seg_base.release();
+    c->seg_flag.release();
+    c->seg16_first.release();
+    c->seg16_pix.release();
+    c->seg16_flag.release();
     c->seg_flags.release();
     if (c->accum) cudaFree(c->accum);
     if (c->rgba8) cudaFree(c->rgba8);
@@ -835,19 +840,28 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
     else if (c->eval_variant == 8 && nsamples < 0xffffffffull) {
         VrSegLists sl;
+        if (c->seg_pairs != (sphere ? 0 : 1)) c->seg_valid = false;
         if (!c->seg_valid) {
-            VR_CUDA(c, c->seg_first.reserve(nsamples / 8 + 1));
-            VR_CUDA(c, c->seg_pix.reserve(nsamples / 8 + 1));
-            VR_CUDA(c, c->seg_flags.reserve(nsamples / 8 + 1));
+            const uint64_t n8 = nsamples / 8 + 1;
+            VR_CUDA(c, c->seg_first.reserve(n8));
+            VR_CUDA(c, c->seg_pix.reserve(n8));
+            VR_CUDA(c, c->seg_flag.reserve(n8));
+            VR_CUDA(c, c->seg16_first.reserve(nsamples / 16 + 1));
+            VR_CUDA(c, c->seg16_pix.reserve(nsamples / 16 + 1));
+            VR_CUDA(c, c->seg16_flag.reserve(nsamples / 16 + 1));
+            VR_CUDA(c, c->seg_flags.reserve(nsamples / 8 + 2));
             VR_CUDA(c, c->seg_list.reserve(nsamples + 1));
             VR_CUDA(c, c->seg_base.reserve(npix + 1));
         }
-        sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.list = c->seg_list.p, sl.counts = c->seg_counts;
+        sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
+        sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
+        sl.list = c->seg_list.p, sl.counts = c->seg_counts;
         sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
         sl.list_capacity = (uint32_t)nsamples;
         if (!c->seg_valid) {
-            vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl);
+            vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl, sphere ? 0 : 1);
             c->seg_valid = true;
+            c->seg_pairs = sphere ? 0 : 1;
         }
         // near/far boundary: the share of flagged segments grows with the list length times rho^2, so long lists (ray and
         // beam sub-points) get a smaller rho, down to 0.1 (the kernel's own residual check keeps 2*err/rho <= 4e-4)
@@ -856,7 +870,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             rho *= sqrtf(1000.0f / (float)eval_list_cap);
             if (rho < 0.1f) rho = 0.1f;
         }
-        vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, c->px_counts.p, c->px_offsets.p, sl,
+        vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, npix, c->px_counts.p, c->px_offsets.p, sl,
                            c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)
@@ -1193,10 +1207,10 @@ int vr_set_eval_near_distance(vr_ctx* c, float distance) {
 int vr_get_eval_segment_counts(vr_ctx* c, uint64_t out[3]) {
     if (!c || !out) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
-    unsigned long long h[3] = {0, 0, 0};
+    unsigned long long h[6] = {0, 0, 0, 0, 0, 0};
     VR_CUDA(c, cudaMemcpyAsync(h, c->seg_counts, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    out[0] = h[0], out[1] = h[1], out[2] = h[2];
+    out[0] = h[5], out[1] = h[1], out[2] = h[2];  // h[5] = 2 * (16-sample entries) + (8-sample entries)
     return check_stream(c);
 }
 

@@ -803,31 +803,47 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
 // error below 2*err/rho <= 4e-4, typically 1e-5 (measured in tests/test_gpu_parity.py).
 // Samples that do not fill a segment (count mod 8 per pixel) go to the exact kernel as well.
 __global__ void __launch_bounds__(256) k_build_segments(const uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
-                                                        uint64_t npix, VrSegLists sl) {
+                                                        uint64_t npix, VrSegLists sl, int pairs) {
     const uint64_t p = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t c = p < npix ? counts[p] : 0u;
     const uint32_t off = p < npix ? (uint32_t)offsets[p] : 0u;
-    const uint32_t q = c >> 3, r = c & 7u;
-    uint32_t qs = q, rs = r;  // inclusive warp scans
+    // q full segments of 8; r leftovers. pairs: q/2 pairs go to the 16-sample table and an odd last one to the 8-sample
+    // table (point-type lists: the FMA-bound kernel gains from sharing the geometry between 16 samples); else all q go
+    // to the 8-sample table (sphere-type lists: MUFU-bound, nothing to gain, and the flags stay finer)
+    const uint32_t q = c >> 3, r = c & 7u, q16 = pairs ? q >> 1 : 0u, q8 = q - 2u * q16;
+    uint32_t v[4] = {q, q16, q8, r};  // inclusive warp scans
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t a = __shfl_up_sync(0xffffffffu, qs, o), b = __shfl_up_sync(0xffffffffu, rs, o);
-        if (lane >= (uint32_t)o) qs += a, rs += b;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, v[i], o);
+            if (lane >= (uint32_t)o) v[i] += a;
+        }
     }
-    unsigned long long qbase = 0, rbase = 0;
+    unsigned long long base[4] = {0, 0, 0, 0};
     if (lane == 31) {
-        if (qs) qbase = atomicAdd(&sl.counts[0], (unsigned long long)qs);
-        if (rs) rbase = atomicAdd(&sl.counts[1], (unsigned long long)rs);
+        unsigned long long* ctr[4] = {&sl.counts[5], &sl.counts[4], &sl.counts[0], &sl.counts[1]};
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            if (v[i]) base[i] = atomicAdd(ctr[i], (unsigned long long)v[i]);
     }
-    qbase = __shfl_sync(0xffffffffu, qbase, 31) + (qs - q);
-    rbase = __shfl_sync(0xffffffffu, rbase, 31) + (rs - r);
-    if (p < npix) sl.seg_base[p] = (uint32_t)qbase;
-    for (uint32_t i = 0; i < q; i++) {
-        sl.seg_first[qbase + i] = off + 8u * i;
-        sl.seg_pix[qbase + i] = (uint32_t)p;
+    const uint32_t mine[4] = {q, q16, q8, r};
+#pragma unroll
+    for (int i = 0; i < 4; i++) base[i] = __shfl_sync(0xffffffffu, base[i], 31) + (v[i] - mine[i]);
+    const uint32_t fb = (uint32_t)base[0];  // the pixel's segments are numbered fb .. fb + q - 1 for the near-light flags
+    if (p < npix) sl.seg_base[p] = fb;
+    for (uint32_t i = 0; i < q16; i++) {
+        sl.seg16_first[base[1] + i] = off + 16u * i;
+        sl.seg16_pix[base[1] + i] = (uint32_t)p;
+        sl.seg16_flag[base[1] + i] = fb + 2u * i;
     }
-    for (uint32_t j = 0; j < r; j++) sl.list[rbase + j] = off + 8u * q + j;
+    for (uint32_t i = 0; i < q8; i++) {
+        sl.seg_first[base[2] + i] = off + 16u * q16 + 8u * i;
+        sl.seg_pix[base[2] + i] = (uint32_t)p;
+        sl.seg_flag[base[2] + i] = fb + 2u * q16 + i;
+    }
+    for (uint32_t j = 0; j < r; j++) sl.list[base[3] + j] = off + 8u * q + j;
 }
 
 // Which segments come closer than rho to a light? Decided geometrically, from the light's side, before the evaluation:
@@ -907,7 +923,7 @@ __device__ __forceinline__ void seg_light_geometry(const float4 qa, const float4
     h2 = __ffma2_rn(pz, pz, h2);
 }
 
-constexpr int SEG_LEN = 8;                        // samples per segment
+constexpr int SEG_LEN = 8;                        // samples per segment (the unit of the tables and flags)
 constexpr int SEG_PER_CTA = 2 * EVAL_THREADS;     // two segments per thread: the x and y halves of every FP32x2 register
 
 // squared distance that enters the reciprocal. Point-type lists: the distance to the light itself. Sphere-type lists
@@ -922,14 +938,20 @@ __device__ __forceinline__ float2 seg_dist2(const float2 l2, const float2 nR) {
     return __fmul2_rn(d, d);
 }
 
-template <int MINB, bool SPHERE>
+// LEN = 8: one segment per half; LEN = 16: two consecutive segments of the same pixel per half (table sl.seg16_*), so the
+// per-light geometry is shared by 16 samples; their weights are read again at the end instead of held in registers.
+template <int MINB, bool SPHERE, int LEN>
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                                   const VrSample* __restrict__ samples, VrSegLists sl,
                                                                   const float4* __restrict__ lights2,
                                                                   const unsigned long long* __restrict__ nlights_dev, float rho,
                                                                   float radius, float* __restrict__ out) {
     const float2 nR = make_float2(-radius, -radius);
-    const uint64_t nseg = sl.counts[0];
+    constexpr bool KEEP_W = LEN <= 8;
+    const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
+    const uint32_t* __restrict__ tab_first = LEN == 16 ? sl.seg16_first : sl.seg_first;
+    const uint32_t* __restrict__ tab_pix = LEN == 16 ? sl.seg16_pix : sl.seg_pix;
+    const uint32_t* __restrict__ tab_flag = LEN == 16 ? sl.seg16_flag : sl.seg_flag;
     const uint64_t seg_base = (uint64_t)blockIdx.x * SEG_PER_CTA;
     if (seg_base >= nseg) return;  // the launch is sized by the capacity, the segment count lives on the device
     const uint64_t nlights = *nlights_dev;
@@ -949,21 +971,24 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
     }
 
-    float2 s[SEG_LEN], acc[SEG_LEN], A[3], D[3];
-    float sw[2][SEG_LEN];
+    float2 s[LEN], acc[LEN], A[3], D[3];
+    float sw[2][KEEP_W ? LEN : 1];
     uint32_t first[2];
     const bool redo_all = *sl.flag_all != 0u;
     bool redo[2] = {false, false};  // per segment, so that what the exact kernel evaluates does not depend on the pairing
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
-        float a[3] = {1.0e6f, 1.0e6f, 1.0e6f}, d[3] = {1.0f, 0.0f, 0.0f}, sv[SEG_LEN];
+        float a[3] = {1.0e6f, 1.0e6f, 1.0e6f}, d[3] = {1.0f, 0.0f, 0.0f}, sv[LEN];
         first[h] = 0xffffffffu;
 #pragma unroll
-        for (int k = 0; k < SEG_LEN; k++) sv[k] = 0.0f, sw[h][k] = 0.0f;
+        for (int k = 0; k < LEN; k++) {
+            sv[k] = 0.0f;
+            if (KEEP_W) sw[h][k] = 0.0f;
+        }
         if (seg < nseg) {
-            first[h] = sl.seg_first[seg];
-            const uint32_t pix = sl.seg_pix[seg];
+            first[h] = tab_first[seg];
+            const uint32_t pix = tab_pix[seg];
             const VrCamRay r = vr_camera_ray(g, u, tan_scale, tile.x0 + pix % tile.w, tile.y0 + pix / tile.w);
             // world direction of the ray: the linear part of the index->world map applied to the index-space direction
             const float vx = r.d.x * g.mat[0] + r.d.y * g.mat[1] + r.d.z * g.mat[2];
@@ -974,7 +999,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             const float4* sp = reinterpret_cast<const float4*>(samples) + first[h];
             float res2 = 0.0f, smax = 0.0f;
 #pragma unroll
-            for (int k = 0; k < SEG_LEN; k++) {
+            for (int k = 0; k < LEN; k++) {
                 const float4 q = __ldg(sp + k);
                 if (k == 0) a[0] = q.x, a[1] = q.y, a[2] = q.z;
                 const float ex = q.x - a[0], ey = q.y - a[1], ez = q.z - a[2];
@@ -982,13 +1007,15 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 const float rx = ex - sk * d[0], ry = ey - sk * d[1], rz = ez - sk * d[2];
                 res2 = fmaxf(res2, rx * rx + ry * ry + rz * rz);
                 smax = fmaxf(smax, fabsf(sk));
-                sv[k] = sk, sw[h][k] = q.w;
+                sv[k] = sk;
+                if (KEEP_W) sw[h][k] = q.w;
             }
             // near a light (decided by k_flag_near_segments), or samples too far off their line for the bound to hold
-            redo[h] = redo_all || sl.flags[seg] != 0 || !(5.0e3f * (sqrtf(res2) + 3.0e-7f * smax) <= rho);
+            const uint32_t fi = tab_flag[seg];  // the pixel's segments are numbered consecutively for the flags
+            redo[h] = redo_all || sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0) || !(5.0e3f * (sqrtf(res2) + 3.0e-7f * smax) <= rho);
         }
 #pragma unroll
-        for (int k = 0; k < SEG_LEN; k++) {
+        for (int k = 0; k < LEN; k++) {
             if (h == 0) s[k].x = sv[k], acc[k] = make_float2(0.f, 0.f);
             else s[k].y = sv[k];
         }
@@ -1020,7 +1047,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             seg_light_geometry(ra, rb, A, D, nb1, h1);
             const float2 W0 = make_float2(qb.z, qb.w), W1 = make_float2(rb.z, rb.w);
 #pragma unroll
-            for (int k = 0; k < SEG_LEN; k++) {
+            for (int k = 0; k < LEN; k++) {
                 const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
                 const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
                 const float2 ab = __fmul2_rn(a, b);
@@ -1034,7 +1061,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             seg_light_geometry(qa, qb, A, D, nb0, h0);
             const float2 W0 = make_float2(qb.z, qb.w);
 #pragma unroll
-            for (int k = 0; k < SEG_LEN; k++) {
+            for (int k = 0; k < LEN; k++) {
                 const float2 u0 = __fadd2_rn(s[k], nb0);
                 const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR);
                 acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
@@ -1043,18 +1070,19 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         __syncthreads();
     }
 
-    const uint32_t npush = (redo[0] ? SEG_LEN : 0) + (redo[1] ? SEG_LEN : 0);
+    const uint32_t npush = (redo[0] ? LEN : 0) + (redo[1] ? LEN : 0);
     unsigned long long slot = 0;
     if (npush) slot = atomicAdd(&sl.counts[2], (unsigned long long)npush);
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         if (first[h] == 0xffffffffu) continue;
 #pragma unroll
-        for (int k = 0; k < SEG_LEN; k++) {
-            out[first[h] + k] = sw[h][k] * (h == 0 ? acc[k].x : acc[k].y);
+        for (int k = 0; k < LEN; k++) {
+            const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
+            out[first[h] + k] = w * (h == 0 ? acc[k].x : acc[k].y);
             if (redo[h] && slot + k < sl.list_capacity) sl.list[slot + k] = first[h] + k;
         }
-        if (redo[h]) slot += SEG_LEN;
+        if (redo[h]) slot += LEN;
     }
 }
 
@@ -1514,14 +1542,15 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
         default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out); break;
     }
 }
-void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl) {
-    cudaMemsetAsync(sl.counts, 0, 3 * sizeof(unsigned long long), st);
+void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
+                        int pairs) {
+    cudaMemsetAsync(sl.counts, 0, 6 * sizeof(unsigned long long), st);
     if (!npix) return;
     VR_COUNT(1);
-    k_build_segments<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, npix, sl);
+    k_build_segments<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, npix, sl, pairs);
 }
 void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
-                        uint64_t nsamples, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
+                        uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
                         const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
                         unsigned long long* redo_count) {
@@ -1538,11 +1567,18 @@ void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, fl
         if (nlights_capacity)
             k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples,
                                                                           sl, margin);
-        const unsigned seg_grid = (unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA);
-        if (sphere)
-            k_eval_seg<2, true><<<seg_grid, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
-        else
-            k_eval_seg<2, false><<<seg_grid, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+        // launches are sized by the tables' upper bounds; CTAs beyond their lengths leave at once. Point-type lists: 16-sample
+        // entries (at most seg_cap / 2), then the odd 8-sample segments (at most one per pixel); sphere-type: 8-sample only
+        const unsigned grid16 = (unsigned)((seg_cap / 2 + SEG_PER_CTA - 1) / SEG_PER_CTA);
+        const unsigned grid8 = (unsigned)(((seg_cap < npix ? seg_cap : npix) + SEG_PER_CTA - 1) / SEG_PER_CTA);
+        const unsigned grid_all = (unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA);
+        VR_COUNT(1);
+        if (sphere) {
+            k_eval_seg<2, true, 8><<<grid_all, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+        } else {
+            k_eval_seg<2, false, 16><<<grid16, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            k_eval_seg<2, false, 8><<<grid8, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+        }
     }
     // exact kernel over the list: launched over the list's upper bound (every sample), CTAs beyond its length leave at once
     VR_COUNT(1);

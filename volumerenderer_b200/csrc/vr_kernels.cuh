@@ -70,20 +70,25 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
 // geometry (k_eval_seg); what does not fill a segment, and every sample whose thread came closer than the segment's
 // rho to a light (k_flag_near_segments), is evaluated by the exact kernel over an index list (k_eval_point3 / k_eval_sphere2 in LIST mode).
 struct VrSegLists {
-    uint32_t* seg_first;          // first sample of every full segment (index into the sample array)
-    uint32_t* seg_pix;            // its pixel (tile-local, row-major)
-    uint32_t* seg_base;           // per pixel: index of its first segment in the two tables above
+    // a pixel's q = count / 8 full segments are numbered consecutively (seg_base[pixel] + k): that number indexes `flags`.
+    // Pairs of them (16 consecutive samples) are the entries of the seg16 table, an odd last one goes to the seg table.
+    uint32_t *seg16_first, *seg16_pix, *seg16_flag;  // first sample / pixel (tile-local, row-major) / flag number
+    uint32_t *seg_first, *seg_pix, *seg_flag;
+    uint32_t* seg_base;           // per pixel: flag number of its first segment
     uint8_t* flags;               // per segment: 1 = comes near a light, evaluate exactly (k_flag_near_segments)
     uint32_t* flag_all;           // 1 = a light sits next to the camera plane: every segment goes to the exact kernel
     uint32_t* list;               // samples for the exact kernel: leftovers, then the fix-ups appended by k_eval_seg
-    unsigned long long* counts;   // [0] segments, [1] leftovers, [2] list length (leftovers + fix-ups)
+    unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + fix-ups), [3] flag_all,
+                                  // [4] seg16 entries, [5] segments (flag numbers)
     uint32_t list_capacity;
 };
 // builds seg_first / seg_pix / the leftover part of list from the per-pixel sample counts and offsets (nsamples < 2^32)
-void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl);
+// pairs != 0: pairs of segments go to the 16-sample table (point-type lists); 0: every segment to the 8-sample table
+void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
+                        int pairs);
 // lights / lights2: the same list in both layouts; nlights_capacity sizes the flagging launch (one block per light)
 void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
-                        uint64_t nsamples, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
+                        uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
                         const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
                         unsigned long long* redo_count);
