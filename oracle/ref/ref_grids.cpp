@@ -11,6 +11,7 @@
 #include <nanovdb/tools/CreatePrimitives.h>
 #include <nanovdb/tools/GridBuilder.h>
 #include <nanovdb/io/IO.h>
+#include <nanovdb/math/SampleFromVoxels.h>
 
 #include <atomic>
 #include <cmath>
@@ -78,6 +79,17 @@ int vrr_get_values(const void* grid_bytes, const int32_t* ijk, uint64_t n, int m
         auto acc = grid->getAccessor();
         for (uint64_t q = 0; q < n; q++) out[q] = acc.getValue(nanovdb::Coord(ijk[3 * q], ijk[3 * q + 1], ijk[3 * q + 2]));
     }
+    return 0;
+}
+
+// nanovdb::math::createSampler<1>(accessor)(xyz): the vendored trilinear sampler (math/SampleFromVoxels.h:174-260, :366-375)
+// at n index-space positions -- the CPU model of the opt-in trilinear density
+int vrr_trilinear(const void* grid_bytes, const float* xyz, uint64_t n, float* out) {
+    auto* grid = reinterpret_cast<const nanovdb::NanoGrid<float>*>(grid_bytes);
+    if (!grid->isValid() || grid->gridType() != nanovdb::GridType::Float) return 1;
+    auto acc = grid->getAccessor();
+    auto smp = nanovdb::math::createSampler<1>(acc);
+    for (uint64_t q = 0; q < n; q++) out[q] = smp(nanovdb::Vec3f(xyz[3 * q], xyz[3 * q + 1], xyz[3 * q + 2]));
     return 0;
 }
 

@@ -245,9 +245,88 @@ inline float sphereLight(V3 incomingPos, V3 sphereOrigin, float lightIntensity, 
 inline V3 lfrom(const vro_light& l) { return v3(l.from[0], l.from[1], l.from[2]); }
 inline V3 lto(const vro_light& l) { return v3(l.to[0], l.to[1], l.to[2]); }
 
+// ------------------------------------------------------------------ opt-in physics
+// None of this exists in the reference's shaders; the definitions below are this repository's own,
+// stated here once and implemented identically by the CUDA kernels (csrc/vr_kernels.cu: vr_phys_factor, vr_trilinear).
+//
+// Trilinear density: nanovdb::math::TrilinearSampler (external/openvdb/nanovdb/nanovdb/math/SampleFromVoxels.h:174-260):
+// ijk = floor(xyz), uvw = xyz - ijk, the eight values at ijk + {0,1}^3, interpolated along z, then y, then x with
+// lerp(a, b, w) = a + w * (b - a)  (SampleFromVoxels.h:196-211, TrilinearSampler::sample).
+inline float lerpf(float a, float b, float w) { return a + w * (b - a); }
+float trilinear(const Grid& g, V3 xyz) {
+    const float fx = vr_floor(xyz.x), fy = vr_floor(xyz.y), fz = vr_floor(xyz.z);
+    const int32_t i = (int32_t)fx, j = (int32_t)fy, k = (int32_t)fz;
+    const float u = xyz.x - fx, v = xyz.y - fy, w = xyz.z - fz;
+    float c[2][2][2];
+    for (int a = 0; a < 2; a++)
+        for (int b = 0; b < 2; b++)
+            for (int d = 0; d < 2; d++) c[a][b][d] = lookup(g, i + a, j + b, k + d);
+    return lerpf(lerpf(lerpf(c[0][0][0], c[0][0][1], w), lerpf(c[0][1][0], c[0][1][1], w), v),
+                 lerpf(lerpf(c[1][0][0], c[1][0][1], w), lerpf(c[1][1][0], c[1][1][1], w), v), u);
+}
+// Factor applied to the contribution of a light acting from `lightPos` on the sample at `p` (both world space):
+//   phase:  Henyey-Greenstein relative to isotropic, P(c) = (1 - g^2) / (1 + g^2 - 2 g c)^(3/2), c = cos of the angle
+//           between the light's travel direction (p - lightPos) and the direction to the camera (cam - p); P = 1 at g = 0
+//   light -> sample transmittance: exp(-absorptionCoefficient * step * sum_{k<n} val(L + k*step*dir)) in index space, step =
+//           rayMarchingStepSize, n = uint(distance / step), nearest-voxel values (the convention of the path mode's
+//           shadow term, path_compute_color.comp:17-28)
+float physFactor(const Grid& g, const vro_ubo& u, const vro_options& o, V3 p, V3 lightPos) {
+    float f = 1.0f;
+    if (o.phase_hg) {
+        const V3 wi = normalize(p - lightPos);
+        const V3 wo = normalize(v3(u.cameraPos[0], u.cameraPos[1], u.cameraPos[2]) - p);
+        const float c = dot(wi, wo), gg = o.hg_g;
+        const float den = (1.0f + gg * gg) - (2.0f * gg) * c;
+        f *= (1.0f - gg * gg) / (den * vr_sqrt(den));
+    }
+    if (o.light_transmittance) {
+        const V3 a = world_to_index(g, lightPos), b = world_to_index(g, p);
+        const V3 ab = b - a;
+        const float dist = length(ab);
+        const float step = u.rayMarchingStepSize;
+        const uint32_t n = (uint32_t)(dist / step);
+        float sum = 0.0f;
+        if (n > 0) {
+            const V3 dir = ab * (1.0f / dist);
+            for (uint32_t k = 0; k < n; k++) {
+                const V3 q = a + dir * ((float)(int32_t)k * step);
+                const int32_t i = (int32_t)vr_floor(q.x), j = (int32_t)vr_floor(q.y), kk = (int32_t)vr_floor(q.z);
+                if (in_bbox(g, i, j, kk)) sum += lookup(g, i, j, kk);
+            }
+        }
+        f *= vr_exp(-(u.absorptionCoefficient * step) * sum);
+    }
+    return f;
+}
+
 // {point,sphere,ray,beam}_compute_color.comp:9-26 computeLightContribution
-float lightSum(int algo, const vro_ubo& u, const vro_light* lights, uint32_t lightCount, V3 p, uint64_t& evals) {
+float lightSum(int algo, const vro_ubo& u, const vro_light* lights, uint32_t lightCount, V3 p, uint64_t& evals,
+               const Grid* g = nullptr, const vro_options* o = nullptr) {
     float total = 0.0f;
+    if (o && (o->phase_hg || o->light_transmittance)) {  // same loops with the opt-in factor per evaluation
+        for (uint32_t i = 0; i < lightCount; i++) {
+            if (algo == VRO_POINT) {
+                total += pointLight(p, lto(lights[i]), lights[i].intensity) * physFactor(*g, u, *o, p, lto(lights[i]));
+                evals++;
+            } else if (algo == VRO_SPHERE) {
+                const V3 curr = closestPointOnSphere(lfrom(lights[i]), u.beamRadius, p);
+                total += pointLight(p, curr, lights[i].intensity) * physFactor(*g, u, *o, p, curr);
+                evals++;
+            } else {
+                V3 rayLocal = lto(lights[i]) - lfrom(lights[i]);
+                V3 rayDir = normalize(rayLocal);
+                uint32_t amountOfSteps = (uint32_t)(length(rayLocal) / u.lightRayStepSize);
+                float pointIntensity = lights[i].intensity / (float)amountOfSteps;
+                for (uint32_t s = 0; s < amountOfSteps; s++) {
+                    V3 curr = lfrom(lights[i]) + ((float)(int32_t)s * u.lightRayStepSize) * rayDir;
+                    if (algo == VRO_BEAM) curr = closestPointOnSphere(curr, u.beamRadius, p);
+                    total += pointLight(p, curr, pointIntensity) * physFactor(*g, u, *o, p, curr);
+                }
+                evals += amountOfSteps;
+            }
+        }
+        return total;
+    }
     if (algo == VRO_POINT) {
         for (uint32_t i = 0; i < lightCount; i++) total += pointLight(p, lto(lights[i]), lights[i].intensity);
         evals += lightCount;
@@ -302,7 +381,7 @@ CamRay cameraRay(const Grid& g, const vro_ubo& u, uint32_t px, uint32_t py) {
 
 // point_compute_color.comp:60-97 -> frameColor for one pixel (all four light models)
 float gatherPixel(const Grid& g, const vro_ubo& u, int algo, const vro_light* lights, uint32_t lightCount, uint32_t px,
-                  uint32_t py, int skip_zero, vro_counters& c) {
+                  uint32_t py, int skip_zero, vro_counters& c, const vro_options* o = nullptr) {
     CamRay r = cameraRay(g, u, px, py);
     float finalColor = 0.0f;
     if (r.hit) c.hit_pixels++;
@@ -316,11 +395,11 @@ float gatherPixel(const Grid& g, const vro_ubo& u, int algo, const vro_light* li
             V3 pWorld = index_to_world(g, pLocal);
             int32_t i = (int32_t)vr_floor(pLocal.x), j = (int32_t)vr_floor(pLocal.y), k = (int32_t)vr_floor(pLocal.z);
             if (in_bbox(g, i, j, k)) {
-                float val = lookup(g, i, j, k);
+                float val = (o && o->trilinear) ? trilinear(g, pLocal) : lookup(g, i, j, k);
                 c.S_ref++;
                 if (val != 0.0f) c.S_eff++;
                 if (!(skip_zero && val == 0.0f)) {
-                    float lightIncoming = lightSum(algo, u, lights, lightCount, pWorld, c.E);
+                    float lightIncoming = lightSum(algo, u, lights, lightCount, pWorld, c.E, &g, o);
                     float dC = T * val * stepSize * lightIncoming;
                     finalColor += dC;
                 }
@@ -448,6 +527,10 @@ int vro_grid_info(const void* grid, uint64_t size, int32_t bbox_min[3], int32_t 
     if (root_tiles) *root_tiles = rd_u32(b, g.root + ROOT_OFF_TABLE_SIZE);
     return 0;
 }
+void vro_trilinear(const void* grid, const float* xyz, uint64_t n, float* out) {
+    Grid g = open_grid(grid);
+    for (uint64_t i = 0; i < n; i++) out[i] = trilinear(g, v3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+}
 void vro_lookup(const void* grid, const int32_t* ijk, uint64_t n, float* out) {
     Grid g = open_grid(grid);
     for (uint64_t q = 0; q < n; q++) out[q] = lookup(g, ijk[3 * q], ijk[3 * q + 1], ijk[3 * q + 2]);
@@ -545,6 +628,13 @@ int vro_light_gen(const void* grid, const vro_ubo* ubo, int variant, uint32_t gx
 int vro_gather(const void* grid, const vro_ubo* ubo, int algo, const vro_light* lights, uint32_t light_count,
                uint32_t x0, uint32_t y0, uint32_t w, uint32_t h, uint32_t stride, int skip_zero, int nthreads,
                float* frame_color, vro_counters* counters) {
+    return vro_gather_ex(grid, ubo, algo, lights, light_count, x0, y0, w, h, stride, skip_zero, nthreads, nullptr, frame_color,
+                         counters);
+}
+
+int vro_gather_ex(const void* grid, const vro_ubo* ubo, int algo, const vro_light* lights, uint32_t light_count,
+                  uint32_t x0, uint32_t y0, uint32_t w, uint32_t h, uint32_t stride, int skip_zero, int nthreads,
+                  const vro_options* options, float* frame_color, vro_counters* counters) {
     Grid g = open_grid(grid);
     const vro_ubo u = *ubo;
     if (stride == 0) stride = 1;
@@ -556,7 +646,7 @@ int vro_gather(const void* grid, const vro_ubo* ubo, int algo, const vro_light* 
         vro_counters& c = cs[(size_t)tid];
         for (uint32_t px = x0; px < x0 + w; px += stride) {
             float fc = (algo == VRO_PATH) ? pathPixel(g, u, px, py, c)
-                                          : gatherPixel(g, u, algo, lights, light_count, px, py, skip_zero, c);
+                                          : gatherPixel(g, u, algo, lights, light_count, px, py, skip_zero, c, options);
             frame_color[(size_t)py * W + px] = fc;
             c.pixels++;
         }

@@ -85,6 +85,20 @@ int vro_gather(const void* grid, const vro_ubo* ubo, int algo, const vro_light* 
                uint32_t x0, uint32_t y0, uint32_t w, uint32_t h, uint32_t stride, int skip_zero, int nthreads,
                float* frame_color, vro_counters* counters);
 
+/* opt-in physics the reference's shaders lack; all zero = the reference's arithmetic.
+ * Definitions: oracle/vr_oracle.cpp (trilinear, physFactor). Mirrors vr_options of include/vr.h. */
+typedef struct vro_options {
+    uint32_t trilinear;           /* density at a camera sample: nanovdb TrilinearSampler instead of the nearest voxel */
+    uint32_t phase_hg;            /* Henyey-Greenstein phase factor (relative to isotropic) per light evaluation */
+    float hg_g;                   /* its asymmetry parameter, |g| < 1 */
+    uint32_t light_transmittance; /* exp(-sigma_a * optical depth) between the light and the sample */
+} vro_options;
+int vro_gather_ex(const void* grid, const vro_ubo* ubo, int algo, const vro_light* lights, uint32_t light_count,
+                  uint32_t x0, uint32_t y0, uint32_t w, uint32_t h, uint32_t stride, int skip_zero, int nthreads,
+                  const vro_options* options, float* frame_color, vro_counters* counters);
+/* TrilinearSampler at n index-space positions xyz[3*n] */
+void vro_trilinear(const void* grid, const float* xyz, uint64_t n, float* out);
+
 /* progressive average, float and rgba8 (shaders/point_compute_color.comp:99-105); n = number of pixels.
  * accum: float RGBA; rgba8: 4 bytes per pixel. path_mode selects the integer form of path_compute_color.comp:121-125. */
 void vro_accumulate(const float* frame_color, uint64_t n, uint32_t frame_count, int path_mode, float* accum_rgba,
