@@ -186,6 +186,36 @@ int vr_set_light_prefetch(vr_ctx* ctx, int enabled);
  * i.e. leaf values, tile values at lower/upper/root level, and the background outside every root tile. */
 int vr_lookup_values(vr_ctx* ctx, const int32_t* ijk, uint64_t n, float* values_out);
 
+/* ---- opt-in physics. None of these exist in the reference's shaders (its gather uses the nearest
+ * voxel, no phase function and no light->sample attenuation: shaders/point_compute_color.comp:60-97,
+ * shaders/common_functions.h:186-194); they are what the reference's description of the method mentions, defined here and
+ * restated on the CPU in oracle/vr_oracle.cpp (trilinear, physFactor). Everything zero (the default) = the reference's
+ * arithmetic. Path mode ignores them.
+ *   trilinear            density at a camera sample = nanovdb::math::TrilinearSampler of the index-space position
+ *                        (external/openvdb/nanovdb/nanovdb/math/SampleFromVoxels.h:174-260) instead of the nearest voxel
+ *   phase_hg, hg_g       every light evaluation is multiplied by the Henyey-Greenstein phase function relative to
+ *                        isotropic, (1-g^2)/(1+g^2-2g cos)^(3/2), cos = angle between the light's travel direction at
+ *                        the sample and the direction to the camera; |hg_g| < 1
+ *   light_transmittance  ... and by exp(-absorptionCoefficient * step * sum of the nearest-voxel values) over
+ *                        n = uint(distance/step) index-space steps from the light to the sample (step =
+ *                        rayMarchingStepSize; the convention of the path mode's shadow term, path_compute_color.comp:17-28)
+ * phase_hg / light_transmittance switch the evaluation to a kernel that keeps every rounding of the CPU restatement; the
+ * transmittance term marches the grid once per (sample, light) pair and is orders of magnitude slower than the gather. */
+typedef struct vr_options {
+    uint32_t trilinear;
+    uint32_t phase_hg;
+    float hg_g;
+    uint32_t light_transmittance;
+} vr_options;
+int vr_set_options(vr_ctx* ctx, const vr_options* options);
+int vr_get_options(vr_ctx* ctx, vr_options* options);
+/* test hook: the device trilinear sampler at n index-space positions xyz[3*n] */
+int vr_trilinear_values(vr_ctx* ctx, const float* xyz, uint64_t n, float* values_out);
+/* calculateRadius of the reference (src/main.cpp:609-618; the call in drawFrame, :713, is commented out there): the
+ * progressive radius update r' = sqrt((r^2 * prod_{k=1}^{15} (k + alpha)/k)^(1/16)); a caller that wants the
+ * reference's per-frame radius update sets ubo.beamRadius = vr_progressive_radius(ubo.beamRadius, alpha) before each frame. Host arithmetic. */
+double vr_progressive_radius(double previous_radius, double alpha);
+
 /* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
  * with the d2 < 1e-4 guard in the loop, 2 = packed kernel that runs the loop unguarded and repeats a thread block with the
  * guard when one of its threads saw d2 < 1e-4 (same results as 1), 3 = as 2 with 6 samples per thread, 8 = below. All follow

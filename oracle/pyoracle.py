@@ -33,6 +33,11 @@ LIGHT_DTYPE = np.dtype([("from", "<f4", 3), ("_pad0", "<f4"), ("to", "<f4", 3), 
 assert LIGHT_DTYPE.itemsize == 32
 
 
+class Options(C.Structure):
+    """vro_options: opt-in physics the reference's shaders lack; all zero = the reference."""
+    _fields_ = [("trilinear", C.c_uint32), ("phase_hg", C.c_uint32), ("hg_g", C.c_float), ("light_transmittance", C.c_uint32)]
+
+
 class Counters(C.Structure):
     _fields_ = [("S_ref", C.c_uint64), ("S_eff", C.c_uint64), ("E", C.c_uint64), ("pixels", C.c_uint64),
                 ("hit_pixels", C.c_uint64)]
@@ -88,6 +93,9 @@ class Oracle:
                                     C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.vro_gather.argtypes = [C.c_void_p, C.POINTER(Ubo), C.c_int, C.c_void_p, C.c_uint32] + [C.c_uint32] * 5 + \
                                 [C.c_int, C.c_int, C.c_void_p, C.POINTER(Counters)]
+        L.vro_gather_ex.argtypes = [C.c_void_p, C.POINTER(Ubo), C.c_int, C.c_void_p, C.c_uint32] + [C.c_uint32] * 5 + \
+            [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(Counters)]
+        L.vro_trilinear.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.vro_accumulate.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
         L.vro_cpu_test.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
 
@@ -144,7 +152,13 @@ class Oracle:
                                C.byref(count), C.byref(emitted), C.byref(steps))
         return lights[:min(count.value, int(ubo.maxLights))].copy(), count.value, emitted.value, steps.value
 
-    def gather(self, grid, ubo, algo, lights, rect=None, stride=1, skip_zero=True, nthreads=0, out=None):
+    def trilinear(self, grid, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self.lib.vro_trilinear(_ptr(grid), _ptr(xyz), len(xyz), _ptr(out))
+        return out
+
+    def gather(self, grid, ubo, algo, lights, rect=None, stride=1, skip_zero=True, nthreads=0, out=None, options=None):
         W, H = ubo.framebufferDim[0], ubo.framebufferDim[1]
         if rect is None:
             rect = (0, 0, W, H)
@@ -153,9 +167,9 @@ class Oracle:
         fc = out if out is not None else np.zeros((H, W), np.float32)
         lights = np.ascontiguousarray(lights, LIGHT_DTYPE)
         cnt = Counters()
-        self.lib.vro_gather(_ptr(grid), C.byref(ubo), ALGO[algo] if isinstance(algo, str) else algo, _ptr(lights),
-                            len(lights), rect[0], rect[1], rect[2], rect[3], stride, int(skip_zero), nthreads, _ptr(fc),
-                            C.byref(cnt))
+        self.lib.vro_gather_ex(_ptr(grid), C.byref(ubo), ALGO[algo] if isinstance(algo, str) else algo, _ptr(lights),
+                               len(lights), rect[0], rect[1], rect[2], rect[3], stride, int(skip_zero), nthreads,
+                               C.byref(options) if options is not None else None, _ptr(fc), C.byref(cnt))
         return fc, {k: getattr(cnt, k) for k, _ in Counters._fields_}
 
     def accumulate(self, frame_color, frame_count, accum=None, rgba8=None, path_mode=False):
@@ -193,6 +207,8 @@ class Ref:
         L.vrr_make_cloud.argtypes = [C.c_int32, C.c_uint32, C.c_double, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.vrr_make_dense.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_double, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
         L.vrr_get_values.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+        if hasattr(L, "vrr_trilinear"):
+            L.vrr_trilinear.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.vrr_grid_facts.argtypes = [C.c_void_p] * 5
         L.vrr_cpu_test.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.vrr_write_nvdb.argtypes = [C.c_void_p, C.c_uint64, C.c_char_p]
@@ -224,6 +240,13 @@ class Ref:
         p, sz = C.c_void_p(), C.c_uint64()
         assert self.lib.vrr_make_dense(_ptr(d), _ptr(dims), _ptr(o), background, voxel, _ptr(t), C.byref(p), C.byref(sz)) == 0
         return self._take(p, sz)
+
+    def trilinear(self, grid, xyz):
+        """nanovdb::math::createSampler<1>(accessor)(xyz) of the vendored NanoVDB at index-space positions."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        assert self.lib.vrr_trilinear(_ptr(grid), _ptr(xyz), len(xyz), _ptr(out)) == 0
+        return out
 
     def get_values(self, grid, ijk, accessor=False):
         ijk = np.ascontiguousarray(ijk, np.int32).reshape(-1, 3)

@@ -3,7 +3,7 @@
 The package is a thin host layer over libvr.so (C ABI in include/vr.h, kernels in csrc/). It has no CPU fallback:
 importing works without a GPU (grid fixtures are host code), creating a VolumeRenderer needs a CUDA device.
 """
-from ._lib import ALGO, LG_KEEP_ORIGIN, LG_RESET_ORIGIN, LIGHT_DTYPE, VrTile, VrUbo, VrLibraryMissing, load  # noqa: F401
+from ._lib import ALGO, LG_KEEP_ORIGIN, LG_RESET_ORIGIN, LIGHT_DTYPE, VrOptions, VrTile, VrUbo, VrLibraryMissing, load  # noqa: F401
 from .renderer import (HEADLESS_PATH, VolumeRenderer, VrError, build_cloud_grid, build_dense_grid,  # noqa: F401
                        build_fog_sphere_grid, load_nvdb_grid, save_nvdb_grid, write_pfm, write_ppm)
 

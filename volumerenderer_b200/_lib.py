@@ -35,6 +35,11 @@ class VrTile(C.Structure):
     _fields_ = [("x0", C.c_uint32), ("y0", C.c_uint32), ("w", C.c_uint32), ("h", C.c_uint32)]
 
 
+class VrOptions(C.Structure):
+    """struct vr_options: opt-in physics; all zero = the reference's arithmetic."""
+    _fields_ = [("trilinear", C.c_uint32), ("phase_hg", C.c_uint32), ("hg_g", C.c_float), ("light_transmittance", C.c_uint32)]
+
+
 class VrCounters(C.Structure):
     _fields_ = [("S_ref", C.c_uint64), ("S_eff", C.c_uint64), ("E", C.c_uint64), ("eval_lights", C.c_uint64),
                 ("light_count", C.c_uint64)]
@@ -56,7 +61,7 @@ EXPORTS = [
     "vr_dispatch_light_gen", "vr_dispatch_compute_color", "vr_set_light_gen_groups", "vr_render_frame",
     "vr_reset_accumulation", "vr_sync", "vr_read_lights", "vr_read_light_counter", "vr_read_image_rgba8",
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
-    "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_accumulate_frame_color", "vr_set_frame_color_peers", "vr_set_march_cache", "vr_set_light_prefetch", "vr_set_eval_variant", "vr_set_eval_near_distance", "vr_get_eval_segment_counts", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
+    "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_accumulate_frame_color", "vr_set_frame_color_peers", "vr_set_march_cache", "vr_set_light_prefetch", "vr_set_options", "vr_get_options", "vr_trilinear_values", "vr_progressive_radius", "vr_set_eval_variant", "vr_set_eval_near_distance", "vr_get_eval_segment_counts", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
     "vr_set_stream", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
     "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
     "vr_io_last_error",
@@ -117,6 +122,11 @@ def load():
     L.vr_set_march_cache.argtypes = [P, I]
     L.vr_set_light_prefetch.argtypes = [P, I]
     L.vr_cpu_test_render.argtypes = [P, U32, U32, P]
+    L.vr_set_options.argtypes = [P, C.POINTER(VrOptions)]
+    L.vr_get_options.argtypes = [P, C.POINTER(VrOptions)]
+    L.vr_trilinear_values.argtypes = [P, P, U64, P]
+    L.vr_progressive_radius.argtypes = [C.c_double, C.c_double]
+    L.vr_progressive_radius.restype = C.c_double
     L.vr_set_eval_variant.argtypes = [P, I]
     L.vr_get_eval_redo_count.argtypes = [P, C.POINTER(U64)]
     L.vr_set_eval_near_distance.argtypes = [P, C.c_float]

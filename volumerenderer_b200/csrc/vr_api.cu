@@ -49,11 +49,12 @@ struct MarchKey {
     vr_tile tile = {0, 0, 0, 0};
     uint32_t dim[2] = {0, 0};
     float cam[3] = {0, 0, 0}, fov = 0, maxd = 0, step = 0, absorb = 0;
+    uint32_t trilinear = 0;
     bool valid = false;
     bool operator==(const MarchKey& o) const {
         return valid && o.valid && grid_gen == o.grid_gen && memcmp(&tile, &o.tile, sizeof(tile)) == 0 &&
                memcmp(dim, o.dim, sizeof(dim)) == 0 && memcmp(cam, o.cam, sizeof(cam)) == 0 && fov == o.fov &&
-               maxd == o.maxd && step == o.step && absorb == o.absorb;
+               maxd == o.maxd && step == o.step && absorb == o.absorb && trilinear == o.trilinear;
     }
 };
 }  // namespace
@@ -122,6 +123,7 @@ struct vr_ctx {
     unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
     bool seg_valid = false;                    // tables match the cached march
     int seg_pairs = -1;                        // ... and were built for point-type (1) / sphere-type (0) lists
+    VrPhysics phys = {0, 0, 0, 0.0f};          // opt-in physics (vr_set_options); all zero = the reference's arithmetic
     float eval_near = 0.25f;                   // distance below which a (sample, light) term is left to the exact kernel
     DevBuf<VrEvalLight> eval_lights;
     DevBuf<float4> eval_lights2;
@@ -743,6 +745,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     key.dim[0] = c->width, key.dim[1] = c->height;
     memcpy(key.cam, c->ubo.cameraPos, sizeof(key.cam));
     key.fov = c->ubo.fov, key.maxd = c->ubo.rayMaxDistance, key.step = c->ubo.rayMarchingStepSize, key.absorb = c->ubo.absorptionCoefficient;
+    key.trilinear = c->phys.trilinear;
     key.valid = true;
     const bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
     const bool reuse = c->march_cache && same_key;
@@ -752,7 +755,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         VR_CUDA(c, c->px_offsets.reserve(npix));
         VR_CUDA(c, c->scan_tmp.reserve((npix + 4095) / 4096 + 1));
         VR_CUDA(c, cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), st));
-        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, c->px_counts.p, nullptr, nullptr, c->wc);
+        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, (int)c->phys.trilinear, c->px_counts.p, nullptr, nullptr, c->wc);
         vrk_scan_u32(st, c->px_counts.p, c->px_offsets.p, c->totals + 0, npix, c->scan_tmp.p);
         if (!same_key) {
             // first gather with these rays: the sample total sizes the buffers, one blocking read. Later frames with
@@ -765,7 +768,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             nsamples = c->totals_host[0];
             VR_CUDA(c, c->samples.reserve(nsamples + 1));
         }
-        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
+        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
         c->cached_samples = nsamples;
         c->march_key = key;
         c->seg_valid = false;
@@ -836,7 +839,9 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
 
     // ---- evaluation (hot) + resolve
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
-    if (c->eval_variant == 0)
+    if (c->phys.phase_hg || c->phys.light_transmittance)  // opt-in physics: its own (slow, every-rounding) kernel
+        vrk_eval_phys(st, sphere, c->gdev, c->ubo, c->phys, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->contrib.p);
+    else if (c->eval_variant == 0)
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
     else if (c->eval_variant == 8 && nsamples < 0xffffffffull) {
         VrSegLists sl;
@@ -1106,7 +1111,7 @@ int vr_row_sample_counts(vr_ctx* c, uint64_t* rows_out) {
     VR_CUDA(c, c->px_counts.reserve(npix));
     DevBuf<unsigned long long> rows;
     VR_CUDA(c, rows.reserve(c->height));
-    vrk_march(c->stream, c->gdev, c->ubo, vr_fov_scale(c->ubo.fov), tile, 0, c->px_counts.p, nullptr, nullptr, nullptr);
+    vrk_march(c->stream, c->gdev, c->ubo, vr_fov_scale(c->ubo.fov), tile, 0, (int)c->phys.trilinear, c->px_counts.p, nullptr, nullptr, nullptr);
     vrk_row_sums(c->stream, c->px_counts.p, c->width, c->height, rows.p);
     cudaError_t e = cudaMemcpyAsync(rows_out, rows.p, (size_t)c->height * 8, cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
@@ -1190,6 +1195,54 @@ int vr_lookup_values(vr_ctx* c, const int32_t* ijk, uint64_t n, float* values_ou
     if (d_out) cudaFree(d_out);
     if (e != cudaSuccess) return fail(c, VR_E_CUDA, "vr_lookup_values failed: %s", cudaGetErrorString(e));
     return check_stream(c);
+}
+
+int vr_set_options(vr_ctx* c, const vr_options* o) {
+    if (!c || !o) return VR_E_ARG;
+    if (o->phase_hg && !(fabsf(o->hg_g) < 1.0f)) return fail(c, VR_E_ARG, "vr_set_options: |hg_g| must be below 1 (got %g)", (double)o->hg_g);
+    c->phys.trilinear = o->trilinear ? 1u : 0u;
+    c->phys.phase_hg = o->phase_hg ? 1u : 0u;
+    c->phys.hg_g = o->hg_g;
+    c->phys.light_transmittance = o->light_transmittance ? 1u : 0u;
+    return VR_OK;
+}
+
+int vr_get_options(vr_ctx* c, vr_options* o) {
+    if (!c || !o) return VR_E_ARG;
+    o->trilinear = c->phys.trilinear, o->phase_hg = c->phys.phase_hg, o->hg_g = c->phys.hg_g;
+    o->light_transmittance = c->phys.light_transmittance;
+    return VR_OK;
+}
+
+int vr_trilinear_values(vr_ctx* c, const float* xyz, uint64_t n, float* values_out) {
+    if (!c) return VR_E_ARG;
+    if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
+    if (n == 0) return VR_OK;
+    if (!xyz || !values_out) return fail(c, VR_E_ARG, "vr_trilinear_values: NULL buffer");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    float *d_xyz = nullptr, *d_out = nullptr;
+    VR_CUDA(c, cudaMalloc(&d_xyz, n * 12));
+    cudaError_t e = cudaMalloc(&d_out, n * 4);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_xyz, xyz, n * 12, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        vrk_trilinear(c->stream, c->gdev, d_xyz, n, d_out);
+        e = cudaMemcpyAsync(values_out, d_out, n * 4, cudaMemcpyDeviceToHost, c->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_xyz);
+    if (d_out) cudaFree(d_out);
+    if (e != cudaSuccess) return fail(c, VR_E_CUDA, "vr_trilinear_values failed: %s", cudaGetErrorString(e));
+    return check_stream(c);
+}
+
+/* calculateRadius of the reference (src/main.cpp:609-618; its call at :713 is commented out): the progressive
+ * photon-mapping radius update for 16 photons per pass, in double precision like the reference */
+double vr_progressive_radius(double previous_radius, double alpha) {
+    const int photonCount = 4 * 4;
+    double squaredRadius = previous_radius * previous_radius;
+    for (int k = 1; k < photonCount; ++k) squaredRadius *= static_cast<double>(k + alpha) / k;
+    squaredRadius = pow(squaredRadius, 1.0 / photonCount);
+    return sqrt(squaredRadius);
 }
 
 int vr_set_eval_variant(vr_ctx* c, int variant) {

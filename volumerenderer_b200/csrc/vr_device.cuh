@@ -103,6 +103,26 @@ __device__ __forceinline__ float vr_lookup(const VrGridDev& g, VrAcc& a, int32_t
     return vr_lookup_dim(g, a, i, j, k, unused);
 }
 
+// ---- opt-in physics (not in the reference's shaders: definitions in oracle/vr_oracle.cpp and vr.h)
+struct VrPhysics {
+    uint32_t trilinear, phase_hg, light_transmittance;
+    float hg_g;
+};
+// nanovdb::math::TrilinearSampler (external/openvdb/nanovdb/nanovdb/math/SampleFromVoxels.h:196-247): the eight values
+// at floor(xyz) + {0,1}^3, lerp(a, b, w) = a + w * (b - a) along z, then y, then x
+__device__ __forceinline__ float vr_lerp(float a, float b, float w) { return vr_add(a, vr_mul(w, vr_sub(b, a))); }
+__device__ __forceinline__ float vr_trilinear(const VrGridDev& g, VrAcc& acc, vr_f3 xyz) {
+    const float fx = vr_floor(xyz.x), fy = vr_floor(xyz.y), fz = vr_floor(xyz.z);
+    const int32_t i = (int32_t)fx, j = (int32_t)fy, k = (int32_t)fz;
+    const float u = vr_sub(xyz.x, fx), v = vr_sub(xyz.y, fy), w = vr_sub(xyz.z, fz);
+    const float c000 = vr_lookup(g, acc, i, j, k), c001 = vr_lookup(g, acc, i, j, k + 1);
+    const float c011 = vr_lookup(g, acc, i, j + 1, k + 1), c010 = vr_lookup(g, acc, i, j + 1, k);
+    const float c100 = vr_lookup(g, acc, i + 1, j, k), c101 = vr_lookup(g, acc, i + 1, j, k + 1);
+    const float c111 = vr_lookup(g, acc, i + 1, j + 1, k + 1), c110 = vr_lookup(g, acc, i + 1, j + 1, k);
+    return vr_lerp(vr_lerp(vr_lerp(c000, c001, w), vr_lerp(c010, c011, w), v),
+                   vr_lerp(vr_lerp(c100, c101, w), vr_lerp(c110, c111, w), v), u);
+}
+
 // Empty-space skipping that keeps the sample lattice. A camera ray at parameter t, position p = o + d*t (as the shader
 // evaluates it in FP32), sits in a constant-value cube of edge 2^log2dim around voxel (i,j,k): a NanoVDB tile. Returns
 // t_lim such that every later lattice point o + d*t', t <= t' < t_lim, floors into that same cube AND into the root
@@ -223,3 +243,37 @@ __device__ __forceinline__ VrCamRay vr_camera_ray(const VrGridDev& g, const vr_u
 }
 // tan(fov * 0.5 * M_PI / 180.0), identical on host and device
 VR_HD float vr_fov_scale(float fov) { return vr_tan(vr_div(vr_mul(vr_mul(fov, 0.5f), 3.14159265358979323846f), 180.0f)); }
+
+// Factor on the contribution of a light acting from lightPos on the sample at p (world space), oracle/vr_oracle.cpp
+// physFactor: Henyey-Greenstein relative to isotropic for the angle between the light's travel direction and the
+// direction to the camera, and exp(-sigma_a * step * sum of nearest-voxel values) over n = uint(distance / step) index-space
+// steps from the light towards the sample. Individually rounded operations in the oracle's order.
+__device__ __forceinline__ float vr_phys_factor(const VrGridDev& g, const vr_ubo& u, const VrPhysics& o, VrAcc& acc, vr_f3 p,
+                                                vr_f3 lightPos) {
+    float f = 1.0f;
+    if (o.phase_hg) {
+        const vr_f3 wi = vr_normalize3(vr_sub3(p, lightPos));
+        const vr_f3 wo = vr_normalize3(vr_sub3(vr_make3(u.cameraPos[0], u.cameraPos[1], u.cameraPos[2]), p));
+        const float c = vr_dot3(wi, wo), gg = o.hg_g;
+        const float den = vr_sub(vr_add(1.0f, vr_mul(gg, gg)), vr_mul(vr_mul(2.0f, gg), c));
+        f = vr_mul(f, vr_div(vr_sub(1.0f, vr_mul(gg, gg)), vr_mul(den, vr_sqrt(den))));
+    }
+    if (o.light_transmittance) {
+        const vr_f3 a = vr_world_to_index(g, lightPos), b = vr_world_to_index(g, p);
+        const vr_f3 ab = vr_sub3(b, a);
+        const float dist = vr_length3(ab);
+        const float step = u.rayMarchingStepSize;
+        const uint32_t n = (uint32_t)vr_div(dist, step);
+        float sum = 0.0f;
+        if (n > 0) {
+            const vr_f3 dir = vr_scale3(ab, vr_div(1.0f, dist));
+            for (uint32_t k = 0; k < n; k++) {
+                const vr_f3 q = vr_add3(a, vr_scale3(dir, vr_mul(vr_i2f((int32_t)k), step)));
+                const int32_t i = (int32_t)vr_floor(q.x), j = (int32_t)vr_floor(q.y), kk = (int32_t)vr_floor(q.z);
+                if (vr_in_bbox(g, i, j, kk)) sum = vr_add(sum, vr_lookup(g, acc, i, j, kk));
+            }
+        }
+        f = vr_mul(f, vr_exp(vr_mul(-vr_mul(u.absorptionCoefficient, step), sum)));
+    }
+    return f;
+}

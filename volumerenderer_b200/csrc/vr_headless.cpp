@@ -27,6 +27,9 @@ struct Options {
     uint32_t width = 1024, height = 1024;  // the reference window (src/main.cpp:40-41)
     uint32_t frames = 1, gx = 1, gy = 1, gz = 1;
     int device = 0, keep_origin = 0, quiet = 0, march_cache = 0;
+    // opt-in physics (vr_options) and the reference's commented-out radius update (src/main.cpp:609-618, :713)
+    int trilinear = 0, light_transmittance = 0, phase_hg = 0, radius_shrink = 0;
+    double hg_g = 0.0, radius_alpha = 0.0;
     std::map<std::string, std::vector<double>> sets;  // UBO overrides
 };
 
@@ -113,6 +116,10 @@ void set_option(Options& o, const std::string& key, const std::string& val) {
     else if (key == "width") o.width = (uint32_t)parse_numbers(val).at(0);
     else if (key == "height") o.height = (uint32_t)parse_numbers(val).at(0);
     else if (key == "march-cache" || key == "marchCache") o.march_cache = (int)parse_numbers(val).at(0);
+    else if (key == "trilinear") o.trilinear = (int)parse_numbers(val).at(0);
+    else if (key == "light-transmittance" || key == "lightTransmittance") o.light_transmittance = (int)parse_numbers(val).at(0);
+    else if (key == "phase-hg" || key == "phaseHg") o.phase_hg = 1, o.hg_g = parse_numbers(val).at(0);
+    else if (key == "radius-update" || key == "radiusUpdate") o.radius_shrink = 1, o.radius_alpha = parse_numbers(val).at(0);
     else if (key == "size") {
         auto v = parse_numbers(val);
         if (v.size() != 2) die("--size takes WxH");
@@ -222,6 +229,8 @@ void usage() {
          "  --snapshot-in FILE --snapshot-out FILE   resume from / save the progressive state\n"
          "  --cpu-test FILE.ppm      CPU_test's density ray-march (256x256) instead of the many-light passes\n"
          "  --save-nvdb FILE         write the volume as an uncompressed .nvdb\n"
+         "  --trilinear 0|1  --phase-hg G  --light-transmittance 0|1   opt-in physics the reference lacks (vr_options)\n"
+         "  --radius-update ALPHA    beamRadius = calculateRadius(beamRadius, ALPHA) before every frame (src/main.cpp:609-618)\n"
          "  --march-cache 0|1  --device D  --quiet");
 }
 
@@ -299,10 +308,17 @@ int main(int argc, char** argv) {
     check(vr_set_params(ctx, &u), ctx, "vr_set_params");
     check(vr_set_light_gen_groups(ctx, o.gx, o.gy, o.gz, o.keep_origin ? VR_LG_KEEP_ORIGIN : VR_LG_RESET_ORIGIN), ctx, "vr_set_light_gen_groups");
     check(vr_set_march_cache(ctx, o.march_cache), ctx, "vr_set_march_cache");
+    vr_options phys = {(uint32_t)(o.trilinear != 0), (uint32_t)o.phase_hg, (float)o.hg_g, (uint32_t)(o.light_transmittance != 0)};
+    check(vr_set_options(ctx, &phys), ctx, "vr_set_options");
 
     const auto t0 = std::chrono::steady_clock::now();
     vr_counters cnt{};
     for (uint32_t f = 0; f < o.frames; f++) {
+        if (o.radius_shrink) {  // uboData.beamRadius = calculateRadius(uboData.beamRadius, uboData.radiusFalloff); (:713, commented out there)
+            check(vr_get_params(ctx, &u), ctx, "vr_get_params");
+            u.beamRadius = (float)vr_progressive_radius(u.beamRadius, o.radius_alpha);
+            check(vr_set_params(ctx, &u), ctx, "vr_set_params");
+        }
         check(vr_render_frame(ctx, algo, nullptr), ctx, "vr_render_frame");  // the compute section of drawFrame
         check(vr_get_counters(ctx, &cnt), ctx, "vr_get_counters");
     }

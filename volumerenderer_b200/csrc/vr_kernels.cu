@@ -285,7 +285,9 @@ __global__ void k_prepare_expand(const vr_ray_light* __restrict__ lights, const 
 // =====================================================================================================
 // 128 threads = 16x8 pixels; each warp is an 8x4 pixel packet (neighbouring rays walk the same leaves, so the
 // 4-byte value loads of a warp fall into a handful of 128-byte lines). One thread per pixel.
-template <bool FILL>
+// TRI: the density at a sample is the trilinear interpolation of the eight surrounding voxel values (opt-in, vr_options);
+// a zero tile value then says nothing about the interpolated neighbourhood, so the empty-tile skipping is off.
+template <bool FILL, bool TRI>
 __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                 uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
                                                 VrSample* __restrict__ samples, VrWorkCounters* wc) {
@@ -309,8 +311,8 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
                 const vr_f3 p = vr_add3(r.o, vr_scale3(r.d, t));
                 const int32_t i = (int32_t)vr_floor(p.x), j = (int32_t)vr_floor(p.y), k = (int32_t)vr_floor(p.z);
                 if (vr_in_bbox(g, i, j, k)) {
-                    int log2dim;
-                    const float val = vr_lookup_dim(g, acc, i, j, k, log2dim);
+                    int log2dim = 0;
+                    const float val = TRI ? vr_trilinear(g, acc, p) : vr_lookup_dim(g, acc, i, j, k, log2dim);
                     sref++;
                     if (val != 0.0f) {
                         if (FILL) {
@@ -319,7 +321,7 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
                         }
                         n++;
                         T = vr_mul(T, vr_exp(vr_mul(vr_mul(-val, u.absorptionCoefficient), step)));
-                    } else if (log2dim > 0) {
+                    } else if (!TRI && log2dim > 0) {
                         // an empty tile: the following lattice points inside it (and inside the bbox) are in-bbox samples
                         // of density 0 -- counted, nothing else to do. t keeps advancing by single adds (the shader's sequence).
                         const float t_lim = vr_min(vr_tile_exit(g, r.o, r.d, p, t, i, j, k, log2dim), r.tmax);
@@ -1086,6 +1088,43 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     }
 }
 
+// ---- opt-in physics: Henyey-Greenstein phase factor and light->sample transmittance per evaluation.
+// Not a hot path: one thread per sample walks the evaluation list from global memory (every thread of a warp reads the
+// same entry) and applies oracle/vr_oracle.cpp's physFactor to each term with individually rounded operations; the
+// transmittance term marches the grid from every light to every sample (orders of magnitude more lookups than the
+// reference's gather). Point-type lists: getPointLightContribution; sphere-type: from the nearest point of the sphere.
+template <bool SPHERE>
+__global__ void __launch_bounds__(128) k_eval_phys(VrGridDev g, vr_ubo u, VrPhysics phys, const VrSample* __restrict__ samples,
+                                                    uint64_t nsamples, const VrEvalLight* __restrict__ lights,
+                                                    const unsigned long long* __restrict__ nlights_dev, float* __restrict__ out) {
+    const uint64_t idx = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (idx >= nsamples) return;
+    const uint64_t nlights = *nlights_dev;
+    const float4 sv = __ldg(reinterpret_cast<const float4*>(samples) + idx);
+    const vr_f3 p = vr_make3(sv.x, sv.y, sv.z);
+    VrAcc acc;
+    vr_acc_init(acc);
+    float total = 0.0f;
+    for (uint64_t l = 0; l < nlights; l++) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(lights) + l);
+        vr_f3 lp = vr_make3(q.x, q.y, q.z);
+        if (SPHERE) lp = vr_add3(lp, vr_scale3(vr_normalize3(vr_sub3(p, lp)), u.beamRadius));  // getClosestPointOnSphere
+        const vr_f3 L = vr_sub3(lp, p);
+        const float d2 = vr_dot3(L, L);
+        if (d2 < 0.0001f) continue;
+        total = vr_add(total, vr_mul(vr_div(q.w, d2), vr_phys_factor(g, u, phys, acc, p, lp)));
+    }
+    out[idx] = vr_mul(sv.w, total);
+}
+
+__global__ void __launch_bounds__(128) k_trilinear(VrGridDev g, const float* __restrict__ xyz, uint64_t n, float* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (i >= n) return;
+    VrAcc acc;
+    vr_acc_init(acc);
+    out[i] = vr_trilinear(g, acc, vr_make3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+}
+
 // =====================================================================================================
 // resolve
 // =====================================================================================================
@@ -1522,14 +1561,35 @@ void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLig
     if (!capacity) return;
     k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, out2, capacity, out_capacity, overflow);
 }
-void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill, int trilinear,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
     VR_COUNT(1);
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
-    if (fill)
-        k_march<true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+    if (trilinear) {
+        if (fill)
+            k_march<true, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+        else
+            k_march<false, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+    } else if (fill)
+        k_march<true, false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
     else
-        k_march<false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+        k_march<false, false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+}
+// opt-in phase function / light->sample transmittance: one thread per sample, every rounding of the oracle kept
+void vrk_eval_phys(cudaStream_t st, int sphere, const VrGridDev& g, const vr_ubo& u, const VrPhysics& phys, const VrSample* samples,
+                   uint64_t nsamples, const VrEvalLight* lights, const unsigned long long* nlights_dev, float* out) {
+    if (nsamples == 0) return;
+    VR_COUNT(1);
+    const unsigned grid = (unsigned)((nsamples + 127) / 128);
+    if (sphere)
+        k_eval_phys<true><<<grid, 128, 0, st>>>(g, u, phys, samples, nsamples, lights, nlights_dev, out);
+    else
+        k_eval_phys<false><<<grid, 128, 0, st>>>(g, u, phys, samples, nsamples, lights, nlights_dev, out);
+}
+void vrk_trilinear(cudaStream_t st, const VrGridDev& g, const float* xyz, uint64_t n, float* out) {
+    if (!n) return;
+    VR_COUNT(1);
+    k_trilinear<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(g, xyz, n, out);
 }
 void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                            const unsigned long long* nlights_dev, float* out, unsigned long long* redo_count) {

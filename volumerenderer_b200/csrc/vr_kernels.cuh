@@ -56,8 +56,12 @@ void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLig
                         const unsigned long long* offsets, VrEvalLight* out, float4* out2, uint32_t capacity,
                         uint64_t out_capacity, uint32_t* overflow);
 // ---- camera-ray march (shaders/point_compute_color.comp:60-94 minus the light loop)
-void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill,
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill, int trilinear,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc);
+// ---- opt-in physics (vr_options): evaluation with the phase / transmittance factor, and the trilinear test hook
+void vrk_eval_phys(cudaStream_t st, int sphere, const VrGridDev& g, const vr_ubo& u, const VrPhysics& phys, const VrSample* samples,
+                   uint64_t nsamples, const VrEvalLight* lights, const unsigned long long* nlights_dev, float* out);
+void vrk_trilinear(cudaStream_t st, const VrGridDev& g, const float* xyz, uint64_t n, float* out);
 // ---- the hot kernels: every sample against every entry of the expanded light list (length read from *nlights_dev)
 // scalar FP32 kernels (point / sphere), every rounding of the shader kept
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 from . import _lib
-from ._lib import ALGO, LG_KEEP_ORIGIN, LG_RESET_ORIGIN, LIGHT_DTYPE, VrCounters, VrTile, VrTimings, VrUbo
+from ._lib import ALGO, LG_KEEP_ORIGIN, LG_RESET_ORIGIN, LIGHT_DTYPE, VrCounters, VrOptions, VrTile, VrTimings, VrUbo
 
 
 class VrError(RuntimeError):
@@ -101,6 +101,30 @@ class VolumeRenderer:
 
     def set_light_gen_groups(self, gx=1, gy=1, gz=1, variant=LG_RESET_ORIGIN):
         self._check(self._L.vr_set_light_gen_groups(self._ctx, gx, gy, gz, variant))
+
+    def set_options(self, trilinear=False, phase_hg_g=None, light_transmittance=False):
+        """Opt-in physics the reference's shaders lack (include/vr.h, vr_options): trilinear density at the camera
+        samples, Henyey-Greenstein phase factor with asymmetry `phase_hg_g` (None = off), light->sample transmittance.
+        All off (the default) is the reference's arithmetic."""
+        o = VrOptions(int(bool(trilinear)), int(phase_hg_g is not None), float(phase_hg_g or 0.0), int(bool(light_transmittance)))
+        self._check(self._L.vr_set_options(self._ctx, C.byref(o)))
+
+    def options(self):
+        o = VrOptions()
+        self._check(self._L.vr_get_options(self._ctx, C.byref(o)))
+        return dict(trilinear=bool(o.trilinear), phase_hg_g=o.hg_g if o.phase_hg else None,
+                    light_transmittance=bool(o.light_transmittance))
+
+    def trilinear_values(self, xyz):
+        """Device trilinear sampler (nanovdb TrilinearSampler semantics) at index-space positions; test hook."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros(len(xyz), np.float32)
+        self._check(self._L.vr_trilinear_values(self._ctx, xyz.ctypes.data_as(C.c_void_p), len(xyz), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def update_beam_radius(self, alpha):
+        """ubo.beamRadius = calculateRadius(ubo.beamRadius, alpha) (src/main.cpp:609-618, the call commented out at :713)."""
+        return self.update_ubo(beamRadius=float(self._L.vr_progressive_radius(float(self.ubo.beamRadius), float(alpha))))
 
     def set_eval_variant(self, variant):
         """0: scalar FP32 evaluation kernel, 1: packed FP32x2 kernel with the guard in the loop, 2: packed speculative
