@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -101,6 +102,8 @@ struct vr_ctx {
     // light generation of vr_render_frame overlaps the camera march on this stream
     cudaStream_t aux_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_lg_done = nullptr;
+    cudaStream_t seg_stream = nullptr;  // low priority: the small evaluation kernels that fill the big kernel's tail
+    cudaEvent_t ev_seg_fork = nullptr, ev_seg_join = nullptr;
     bool lg_in_flight = false;
     uint32_t lg_groups[3] = {1, 1, 1};
     vr_lightgen_variant lg_variant = VR_LG_RESET_ORIGIN;
@@ -404,10 +407,17 @@ int vr_create(int cuda_device, vr_ctx** out) {
         VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->aux_stream, cudaStreamNonBlocking, prio_hi));
     }
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);  // lo = the numerically largest = lowest priority
+        VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->seg_stream, cudaStreamNonBlocking, lo));
+    }
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_fork, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
-    VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 6 * sizeof(unsigned long long)));  // layout: VrSegLists::counts
-    VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 6 * sizeof(unsigned long long), c->stream));
+    VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 8 * sizeof(unsigned long long)));  // layout: VrSegLists::counts
+    VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 8 * sizeof(unsigned long long), c->stream));
     VR_CREATE_CUDA(cudaMemsetAsync(c->eval_redo, 0, sizeof(unsigned long long), c->stream));
     for (int k = 0; k < vr_ctx::kTimingSets; k++)
         for (int i = 0; i < 7; i++) VR_CREATE_CUDA(cudaEventCreate(&c->tset[k].ev[i]));
@@ -458,6 +468,9 @@ int vr_destroy(vr_ctx* c) {
     if (c->scalars_host) cudaFreeHost(c->scalars_host);
     if (c->ev_scalars) cudaEventDestroy(c->ev_scalars);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_seg_fork) cudaEventDestroy(c->ev_seg_fork);
+    if (c->ev_seg_join) cudaEventDestroy(c->ev_seg_join);
+    if (c->seg_stream) cudaStreamDestroy(c->seg_stream);
     if (c->ev_lg_done) cudaEventDestroy(c->ev_lg_done);
     if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     if (c->eval_redo) cudaFree(c->eval_redo);
@@ -875,7 +888,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             rho *= sqrtf(1000.0f / (float)eval_list_cap);
             if (rho < 0.1f) rho = 0.1f;
         }
-        vrk_eval_point_seg(st, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, npix, c->px_counts.p, c->px_offsets.p, sl,
+        static const bool seg_side = !(getenv("VR_SEG_SIDE") && atoi(getenv("VR_SEG_SIDE")) == 0);  // experiments: 0 = one stream
+        vrk_eval_point_seg(st, seg_side ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, npix, c->px_counts.p, c->px_offsets.p, sl,
                            c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)

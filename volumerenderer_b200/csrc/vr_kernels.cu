@@ -20,6 +20,7 @@
 // and uses MUFU.RCP; its results are within a few ulp per term (tolerance 1e-3 relative on the pixel, BASELINE.json).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "vr_kernels.cuh"
 
@@ -577,13 +578,16 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
 template <int S, bool LIST>
 __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample* __restrict__ samples, uint64_t nsamples,
                                                                    const uint32_t* __restrict__ list,
+                                                                   const unsigned long long* __restrict__ nlist_begin_dev,
                                                                    const unsigned long long* __restrict__ nlist_dev,
                                                                    const float4* __restrict__ lights2,
                                                                    const unsigned long long* __restrict__ nlights_dev, float radius,
                                                                    float* __restrict__ out) {
     constexpr int P = S / 2;
-    if (LIST) {
-        nsamples = *nlist_dev;
+    if (LIST) {  // entries [*nlist_begin_dev (0 if NULL), *nlist_dev) of the list
+        const uint64_t lbeg = nlist_begin_dev ? *nlist_begin_dev : 0;
+        list += lbeg;
+        nsamples = *nlist_dev - lbeg;
         if ((uint64_t)blockIdx.x * (EVAL_THREADS * S) >= nsamples) return;
     }
     const uint64_t nlights = *nlights_dev;
@@ -738,13 +742,16 @@ __device__ __forceinline__ void eval_pass_packed(float4 (&stage)[2][2 * EVAL2_TI
 template <int S, int MINB, int UNROLL, bool LIST = false>  // S samples per thread (even), MINB resident CTAs per SM
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSample* __restrict__ samples, uint64_t nsamples,
                                                               const uint32_t* __restrict__ list,
+                                                              const unsigned long long* __restrict__ nlist_begin_dev,
                                                               const unsigned long long* __restrict__ nlist_dev,
                                                               const float4* __restrict__ lights2,
                                                               const unsigned long long* __restrict__ nlights_dev,
                                                               float* __restrict__ out, unsigned long long* __restrict__ redo_count) {
     constexpr int P = S / 2;
-    if (LIST) {
-        nsamples = *nlist_dev;
+    if (LIST) {  // entries [*nlist_begin_dev (0 if NULL), *nlist_dev) of the list
+        const uint64_t lbeg = nlist_begin_dev ? *nlist_begin_dev : 0;
+        list += lbeg;
+        nsamples = *nlist_dev - lbeg;
         if ((uint64_t)blockIdx.x * (EVAL_THREADS * S) >= nsamples) return;
     }
     const uint64_t nlights = *nlights_dev;
@@ -907,6 +914,21 @@ __global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __
     }
 }
 
+// the flagged entries of a segment table go onto the exact kernel's list (behind the leftovers), before the evaluation
+// starts: the exact kernel can then run next to the segment kernel instead of after it
+template <int LEN>
+__global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl) {
+    const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
+    const uint64_t e = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (e >= nseg) return;
+    const uint32_t fi = (LEN == 16 ? sl.seg16_flag : sl.seg_flag)[e];
+    if (!(*sl.flag_all != 0u || sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0))) return;
+    const uint32_t first = (LEN == 16 ? sl.seg16_first : sl.seg_first)[e];
+    const unsigned long long slot = atomicAdd(&sl.counts[2], (unsigned long long)LEN);
+    for (int k = 0; k < LEN; k++)
+        if (slot + k < sl.list_capacity) sl.list[slot + k] = first + k;
+}
+
 __device__ __forceinline__ float2 neg2(const float2 v) { return make_float2(-v.x, -v.y); }  // folds into the operand modifier
 
 // b = (L - A).D and h2 = |(L - A) - b D|^2 for the two segments of the thread (x and y halves) against one light
@@ -978,6 +1000,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     uint32_t first[2];
     const bool redo_all = *sl.flag_all != 0u;
     bool redo[2] = {false, false};  // per segment, so that what the exact kernel evaluates does not depend on the pairing
+    bool skip[2] = {false, false};  // on the exact kernel's list already: that kernel (another stream) owns the result
 #pragma unroll
     for (int h = 0; h < 2; h++) {
         const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
@@ -1013,8 +1036,13 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 if (KEEP_W) sw[h][k] = q.w;
             }
             // near a light (decided by k_flag_near_segments), or samples too far off their line for the bound to hold
+            // Segments near a light were put on the exact kernel's list by k_list_flagged already. What is decided here: samples
+            // too far off their line for the bound to hold -> hand the entry over as well (rare: a safety net for grid scales
+            // where FP32 positions are coarse).
             const uint32_t fi = tab_flag[seg];  // the pixel's segments are numbered consecutively for the flags
-            redo[h] = redo_all || sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0) || !(5.0e3f * (sqrtf(res2) + 3.0e-7f * smax) <= rho);
+            const bool listed = redo_all || sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0);
+            skip[h] = listed;
+            redo[h] = !listed && !(5.0e3f * (sqrtf(res2) + 3.0e-7f * smax) <= rho);
         }
 #pragma unroll
         for (int k = 0; k < LEN; k++) {
@@ -1080,8 +1108,10 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         if (first[h] == 0xffffffffu) continue;
 #pragma unroll
         for (int k = 0; k < LEN; k++) {
-            const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
-            out[first[h] + k] = w * (h == 0 ? acc[k].x : acc[k].y);
+            if (!skip[h]) {
+                const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
+                out[first[h] + k] = w * (h == 0 ? acc[k].x : acc[k].y);
+            }
             if (redo[h] && slot + k < sl.list_capacity) sl.list[slot + k] = first[h] + k;
         }
         if (redo[h]) slot += LEN;
@@ -1597,57 +1627,101 @@ void vrk_eval_point_packed(cudaStream_t st, int variant, const VrSample* samples
     VR_COUNT(1);
     auto grid = [&](int S) { return (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S)); };
     switch (variant) {
-        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
-        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
+        case 2: k_eval_point3<8, 3, 2><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
+        case 3: k_eval_point3<6, 4, 2><<<grid(6), EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, nullptr, lights2, nlights_dev, out, redo_count); break;
         default: k_eval_point2<8><<<grid(8), EVAL_THREADS, 0, st>>>(samples, nsamples, lights2, nlights_dev, out); break;
     }
 }
 void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
                         int pairs) {
-    cudaMemsetAsync(sl.counts, 0, 6 * sizeof(unsigned long long), st);
+    cudaMemsetAsync(sl.counts, 0, 8 * sizeof(unsigned long long), st);
     if (!npix) return;
     VR_COUNT(1);
     k_build_segments<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, npix, sl, pairs);
 }
-void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
+// the exact kernels over entries [*begin_dev (0 if NULL), *end_dev) of the list; launched over `bound` entries, CTAs beyond
+// the real length leave at once. Small launches use 4 samples per thread: twice the CTAs at half the duration.
+static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* samples, uint64_t bound, bool small, const VrSegLists& sl,
+                              const unsigned long long* begin_dev, const unsigned long long* end_dev, const float4* lights2,
+                              const unsigned long long* nlights_dev, float radius, float* out, unsigned long long* redo_count) {
+    if (!bound) return;
+    VR_COUNT(1);
+    const uint64_t per_cta = (uint64_t)EVAL_THREADS * (small ? 4 : 8);
+    const unsigned grid = (unsigned)((bound + per_cta - 1) / per_cta);
+    if (sphere) {
+        if (small)
+            k_eval_sphere2<4, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, radius, out);
+        else
+            k_eval_sphere2<8, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, radius, out);
+    } else if (small) {
+        k_eval_point3<4, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, out, redo_count);
+    } else {
+        k_eval_point3<8, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, out, redo_count);
+    }
+}
+
+// Evaluation pass of the ray-segment path. Main stream: near-light flags, the flagged entries onto the exact kernel's list,
+// then the big segment kernel. Side stream (lower priority, forked once the list is complete): the odd 8-sample segments and
+// the exact kernel over the list (leftovers + near-light segments) -- independent work whose CTAs fill the SMs that the big
+// kernel's last wave leaves idle. After the join: the exact kernel on whatever the segment kernels handed over themselves
+// (entries whose samples deviate too much from their line; normally none, then every CTA of that launch leaves at once).
+void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join, const VrGridDev& g,
+                        const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
                         const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
                         unsigned long long* redo_count) {
     if (nsamples == 0) return;
-    // the exact kernel's list restarts from the leftovers every frame; k_eval_seg appends the segments flagged below
+    if (!side) side = st;
+    // the exact kernel's list restarts from the leftovers every frame
     cudaMemcpyAsync(sl.counts + 2, sl.counts + 1, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
     const uint64_t seg_cap = nsamples / SEG_LEN;
+    static const int small_env = getenv("VR_LIST_SMALL") ? atoi(getenv("VR_LIST_SMALL")) : 1;
+    const bool small = small_env && nsamples < 40ull * 1000 * 1000;
+    const unsigned grid16 = (unsigned)((seg_cap / 2 + SEG_PER_CTA - 1) / SEG_PER_CTA);
+    const uint64_t cap8 = sphere ? seg_cap : (seg_cap < npix ? seg_cap : npix);  // point-type: at most one odd segment per pixel
+    const unsigned grid8 = (unsigned)((cap8 + SEG_PER_CTA - 1) / SEG_PER_CTA);
     if (seg_cap) {
         cudaMemsetAsync(sl.flags, 0, seg_cap, st);
         cudaMemsetAsync(sl.flag_all, 0, sizeof(uint32_t), st);
-        VR_COUNT(2);
         // sphere-type lists: distances are measured from the sphere's surface, the flags from its centre
         const float margin = 1.02f * (rho + (sphere ? radius : 0.0f)) + 1.0e-3f;
-        if (nlights_capacity)
-            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples,
-                                                                          sl, margin);
-        // launches are sized by the tables' upper bounds; CTAs beyond their lengths leave at once. Point-type lists: 16-sample
-        // entries (at most seg_cap / 2), then the odd 8-sample segments (at most one per pixel); sphere-type: 8-sample only
-        const unsigned grid16 = (unsigned)((seg_cap / 2 + SEG_PER_CTA - 1) / SEG_PER_CTA);
-        const unsigned grid8 = (unsigned)(((seg_cap < npix ? seg_cap : npix) + SEG_PER_CTA - 1) / SEG_PER_CTA);
-        const unsigned grid_all = (unsigned)((seg_cap + SEG_PER_CTA - 1) / SEG_PER_CTA);
+        if (nlights_capacity) {
+            VR_COUNT(1);
+            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(
+                lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples, sl, margin);
+        }
+        if (!sphere && seg_cap / 2) {
+            VR_COUNT(1);
+            k_list_flagged<16><<<(unsigned)((seg_cap / 2 + 255) / 256), 256, 0, st>>>(sl);
+        }
+        VR_COUNT(1);
+        k_list_flagged<8><<<(unsigned)((cap8 + 255) / 256), 256, 0, st>>>(sl);
+    }
+    // counts[6] = the list length now (leftovers + near-light segments); the segment kernels append behind it
+    cudaMemcpyAsync(sl.counts + 6, sl.counts + 2, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
+    if (side != st) {
+        cudaEventRecord(ev_fork, st);
+        cudaStreamWaitEvent(side, ev_fork, 0);
+    }
+    if (seg_cap) {
+        // launches are sized by the tables' upper bounds; CTAs beyond their lengths leave at once
         VR_COUNT(1);
         if (sphere) {
-            k_eval_seg<2, true, 8><<<grid_all, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+            k_eval_seg<2, true, 8><<<grid8, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
         } else {
             k_eval_seg<2, false, 16><<<grid16, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
-            k_eval_seg<2, false, 8><<<grid8, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            VR_COUNT(1);
+            k_eval_seg<2, false, 8><<<grid8, EVAL_THREADS, 0, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
         }
     }
-    // exact kernel over the list: launched over the list's upper bound (every sample), CTAs beyond its length leave at once
-    VR_COUNT(1);
-    const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * 8 - 1) / ((uint64_t)EVAL_THREADS * 8));
-    if (sphere)
-        k_eval_sphere2<8, true><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, sl.list, sl.counts + 2, lights2, nlights_dev, radius, out);
-    else
-        k_eval_point3<8, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, sl.list, sl.counts + 2, lights2, nlights_dev, out,
-                                                                     redo_count);
+    launch_exact_list(side, sphere, samples, nsamples, small, sl, nullptr, sl.counts + 6, lights2, nlights_dev, radius, out, redo_count);
+    if (side != st) {
+        cudaEventRecord(ev_join, side);
+        cudaStreamWaitEvent(st, ev_join, 0);
+    }
+    launch_exact_list(st, sphere, samples, seg_cap * SEG_LEN, small, sl, sl.counts + 6, sl.counts + 2, lights2, nlights_dev, radius, out,
+                      redo_count);
 }
 void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                             const unsigned long long* nlights_dev, float radius, float* out) {
@@ -1655,7 +1729,7 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
     VR_COUNT(1);
     constexpr int S = 8;
     const unsigned grid = (unsigned)((nsamples + (uint64_t)EVAL_THREADS * S - 1) / ((uint64_t)EVAL_THREADS * S));
-    k_eval_sphere2<S, false><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, lights2, nlights_dev, radius, out);
+    k_eval_sphere2<S, false><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, nullptr, nullptr, nullptr, lights2, nlights_dev, radius, out);
 }
 void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsamples, const VrEvalLight* lights,
               const unsigned long long* nlights_dev, float radius, float* out) {

@@ -83,7 +83,7 @@ struct VrSegLists {
     uint32_t* flag_all;           // 1 = a light sits next to the camera plane: every segment goes to the exact kernel
     uint32_t* list;               // samples for the exact kernel: leftovers, then the fix-ups appended by k_eval_seg
     unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + fix-ups), [3] flag_all,
-                                  // [4] seg16 entries, [5] segments (flag numbers)
+                                  // [4] seg16 entries, [5] segments (flag numbers), [6] list length before the segment kernels
     uint32_t list_capacity;
 };
 // builds seg_first / seg_pix / the leftover part of list from the per-pixel sample counts and offsets (nsamples < 2^32)
@@ -91,7 +91,9 @@ struct VrSegLists {
 void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
                         int pairs);
 // lights / lights2: the same list in both layouts; nlights_capacity sizes the flagging launch (one block per light)
-void vrk_eval_point_seg(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
+// side (may be NULL = st): a second stream for the independent small kernels; ev_fork / ev_join order the two streams
+void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join, const VrGridDev& g,
+                        const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
                         const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
