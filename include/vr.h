@@ -145,6 +145,11 @@ int vr_read_lights(vr_ctx* ctx, vr_ray_light* out, uint32_t capacity, uint32_t* 
 int vr_read_light_counter(vr_ctx* ctx, uint32_t counter[2], uint64_t* total_emitted);
 int vr_read_image_rgba8(vr_ctx* ctx, uint8_t* out);        /* width*height*4 bytes */
 int vr_read_accum_f32(vr_ctx* ctx, float* out);            /* width*height*4 floats (RGBA, linear) */
+/* the same read-back without blocking: the accumulator as it is after the work enqueued so far is snapshotted on the
+ * device and copied to `out` (pinned host memory for a truly asynchronous copy) on a copy stream, underneath whatever is
+ * enqueued next; `out` is valid after vr_read_wait (or the next vr_read_accum_f32_async, which waits for the previous one). */
+int vr_read_accum_f32_async(vr_ctx* ctx, float* out);
+int vr_read_wait(vr_ctx* ctx);
 int vr_read_frame_color_f32(vr_ctx* ctx, float* out);      /* width*height floats: the last frame's clamp()ed colour, R=G=B */
 int vr_write_accum_f32(vr_ctx* ctx, const float* in, uint32_t frame_count); /* restore a snapshot (resume) */
 int vr_write_image_rgba8(vr_ctx* ctx, const uint8_t* in);

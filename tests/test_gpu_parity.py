@@ -387,6 +387,27 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo, cam
     assert np.array_equal(res[8], res[2])
 
 
+def test_async_readback_equals_blocking(renderer, cloud):
+    """vr_read_accum_f32_async snapshots the accumulator at the point of the call: the frames enqueued afterwards (which
+    overwrite it) must not leak into the copy, and a second request waits for the first."""
+    _setup(renderer, cloud(64), 96, 64, maxLights=64)
+    renderer.set_light_gen_groups(4, 1, 1)
+    renderer.reset_accumulation()
+    renderer.draw_frame("point")
+    want1 = renderer.read_accum()
+    renderer.reset_accumulation()
+    renderer.draw_frame("point")
+    a, b = np.zeros((64, 96, 4), np.float32), np.zeros((64, 96, 4), np.float32)
+    renderer.read_accum_async(a)
+    for _ in range(3):
+        renderer.draw_frame("point")        # frames 2..4 change the accumulator while the copy is in flight
+    renderer.read_accum_async(b)
+    renderer.read_wait()
+    assert np.array_equal(a, want1)
+    assert np.array_equal(b, renderer.read_accum()) and not np.array_equal(a, b)
+    renderer.set_light_gen_groups(1, 1, 1)
+
+
 def test_argument_errors(renderer, vr, cloud):
     grid = cloud(64)
     _setup(renderer, grid, 32, 32)

@@ -102,6 +102,15 @@ struct vr_ctx {
     // light generation of vr_render_frame overlaps the camera march on this stream
     cudaStream_t aux_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_lg_done = nullptr;
+    cudaStream_t upload_stream = nullptr;  // vr_set_grid: host->device copy of a new grid next to the frames in flight
+    uint8_t* grid_alt = nullptr;           // the second grid buffer (vr_set_grid alternates)
+    uint64_t grid_alt_cap = 0;
+    bool grid_alt_busy = false;
+    cudaEvent_t ev_grid_alt_free = nullptr;
+    cudaStream_t copy_stream = nullptr;  // asynchronous read-back (vr_read_accum_f32_async): copies overlap the next frame
+    cudaEvent_t ev_copy_ready = nullptr, ev_copy_done = nullptr;
+    DevBuf<float> accum_snapshot;
+    bool copy_pending = false;
     cudaStream_t seg_stream = nullptr;  // low priority: the small evaluation kernels that fill the big kernel's tail
     cudaEvent_t ev_seg_fork = nullptr, ev_seg_join = nullptr;
     bool lg_in_flight = false;
@@ -412,6 +421,11 @@ int vr_create(int cuda_device, vr_ctx** out) {
         cudaDeviceGetStreamPriorityRange(&lo, &hi);  // lo = the numerically largest = lowest priority
         VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->seg_stream, cudaStreamNonBlocking, lo));
     }
+    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->upload_stream, cudaStreamNonBlocking));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_grid_alt_free, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_ready, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_fork, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
@@ -468,6 +482,16 @@ int vr_destroy(vr_ctx* c) {
     if (c->scalars_host) cudaFreeHost(c->scalars_host);
     if (c->ev_scalars) cudaEventDestroy(c->ev_scalars);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->copy_stream) {
+        cudaStreamSynchronize(c->copy_stream);
+        cudaStreamDestroy(c->copy_stream);
+    }
+    if (c->upload_stream) cudaStreamDestroy(c->upload_stream);
+    if (c->ev_grid_alt_free) cudaEventDestroy(c->ev_grid_alt_free);
+    if (c->grid_alt) cudaFree(c->grid_alt);
+    if (c->ev_copy_ready) cudaEventDestroy(c->ev_copy_ready);
+    if (c->ev_copy_done) cudaEventDestroy(c->ev_copy_done);
+    c->accum_snapshot.release();
     if (c->ev_seg_fork) cudaEventDestroy(c->ev_seg_fork);
     if (c->ev_seg_join) cudaEventDestroy(c->ev_seg_join);
     if (c->seg_stream) cudaStreamDestroy(c->seg_stream);
@@ -536,21 +560,35 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     const uint32_t tiles = rd<uint32_t>(b, root + 24);
     if (root + 64 + 32ull * tiles > size) return fail(c, VR_E_BADGRID, "root tile table outside the buffer");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the old grid
-    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
     c->spec.valid = false;
-    if (c->grid && c->grid_cap < size) {
-        cudaFree(c->grid);
-        c->grid = nullptr;
-        c->grid_cap = 0;
+    // Two device buffers: the new grid goes into the one no enqueued work reads, on an upload stream, while the frames
+    // already enqueued keep rendering from the other (kernels take the grid pointer by value at launch). The host waits
+    // for the copy (the caller may reuse `bytes` on return); the GPU does not wait for anything.
+    if (c->grid_alt && c->grid_alt_cap < size) {
+        if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));
+        cudaFree(c->grid_alt);
+        c->grid_alt = nullptr;
+        c->grid_alt_cap = 0;
+    }
+    if (!c->grid_alt) {
+        VR_CUDA(c, cudaMalloc(&c->grid_alt, size));
+        c->grid_alt_cap = size;
+        c->grid_alt_busy = false;
+    }
+    if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));  // its last readers (two grids ago) are done
+    VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, bytes, size, cudaMemcpyHostToDevice, c->upload_stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->upload_stream));
+    // everything enqueued so far reads the old buffer: it is free again once this event has passed
+    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    {
+        uint8_t* t = c->grid;
+        c->grid = c->grid_alt, c->grid_alt = t;
+        const uint64_t tc = c->grid_cap;
+        c->grid_cap = c->grid_alt_cap, c->grid_alt_cap = tc;
+        c->grid_alt_busy = c->grid_alt != nullptr;
     }
     c->have_grid = false;
-    if (!c->grid) {
-        VR_CUDA(c, cudaMalloc(&c->grid, size));
-        c->grid_cap = size;
-    }
-    VR_CUDA(c, cudaMemcpyAsync(c->grid, bytes, size, cudaMemcpyHostToDevice, c->stream));
-    VR_CUDA(c, cudaStreamSynchronize(c->stream));
     VrGridDev g{};
     g.base = c->grid;
     g.root = root;
@@ -578,6 +616,8 @@ int vr_resize(vr_ctx* c, uint32_t w, uint32_t h) {
     if (w == 0 || h == 0 || w > 65536 || h > 65536) return fail(c, VR_E_ARG, "image size %ux%u invalid", w, h);
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->copy_stream) VR_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    c->copy_pending = false;
     if (c->accum) cudaFree(c->accum), c->accum = nullptr;
     if (c->rgba8) cudaFree(c->rgba8), c->rgba8 = nullptr;
     if (c->own_frame_color) cudaFree(c->own_frame_color), c->own_frame_color = nullptr;
@@ -1022,6 +1062,34 @@ int vr_read_lights(vr_ctx* c, vr_ray_light* out, uint32_t capacity, uint32_t* co
 int vr_read_image_rgba8(vr_ctx* c, uint8_t* out) { VR_READ_IMAGE(c, out, c->rgba8, (size_t)c->width * c->height * 4); }
 int vr_read_accum_f32(vr_ctx* c, float* out) { VR_READ_IMAGE(c, out, c->accum, (size_t)c->width * c->height * 16); }
 int vr_read_frame_color_f32(vr_ctx* c, float* out) { VR_READ_IMAGE(c, out, c->frame_color, (size_t)c->width * c->height * 4); }
+
+/* Asynchronous read-back of the float accumulator: the image is snapshotted on the render stream (device-to-device), the
+ * copy to the host runs on a copy stream underneath the frames enqueued afterwards. */
+int vr_read_accum_f32_async(vr_ctx* c, float* out) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (!out) return fail(c, VR_E_ARG, "NULL output buffer");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const size_t bytes = (size_t)c->width * c->height * 16;
+    if (c->copy_pending) VR_CUDA(c, cudaEventSynchronize(c->ev_copy_done));  // one read-back in flight: the snapshot is reused
+    VR_CUDA(c, c->accum_snapshot.reserve(bytes / 4));
+    VR_CUDA(c, cudaMemcpyAsync(c->accum_snapshot.p, c->accum, bytes, cudaMemcpyDeviceToDevice, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_copy_ready, c->stream));
+    VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_copy_ready, 0));
+    VR_CUDA(c, cudaMemcpyAsync(out, c->accum_snapshot.p, bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_copy_done, c->copy_stream));
+    c->copy_pending = true;
+    return VR_OK;
+}
+int vr_read_wait(vr_ctx* c) {
+    if (!c) return VR_E_ARG;
+    if (c->copy_pending) {
+        VR_CUDA(c, cudaSetDevice(c->device));
+        VR_CUDA(c, cudaEventSynchronize(c->ev_copy_done));
+        c->copy_pending = false;
+    }
+    return check_stream(c);
+}
 
 int vr_write_accum_f32(vr_ctx* c, const float* in, uint32_t frame_count) {
     if (!c) return VR_E_ARG;

@@ -224,6 +224,14 @@ class VolumeRenderer:
         self._check(self._L.vr_read_accum_f32(self._ctx, out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def read_accum_async(self, out):
+        """vr_read_accum_f32_async into `out` ((H, W, 4) float32, ideally pinned): valid after read_wait()."""
+        assert out.dtype == np.float32 and out.size == self.width * self.height * 4 and out.flags["C_CONTIGUOUS"]
+        self._check(self._L.vr_read_accum_f32_async(self._ctx, out.ctypes.data_as(C.c_void_p)))
+
+    def read_wait(self):
+        self._check(self._L.vr_read_wait(self._ctx))
+
     def read_image_rgba8(self):
         out = np.zeros((self.height, self.width, 4), np.uint8)
         self._check(self._L.vr_read_image_rgba8(self._ctx, out.ctypes.data_as(C.c_void_p)))
