@@ -1,7 +1,7 @@
 #!/bin/bash
 # GPU-box session for profiles/ (round 1, ray-segment kernels): bench (both arms), ncu launch list, ncu --set full of the
 # kernels of one steady-state frame, and of the sphere-list segment kernel. usage (repo root, on the box): bash tools/gpu_capture3.sh <tag>
-TAG=${1:-r01k}
+TAG=${1:-r01m}
 OUT=gpurun_out
 mkdir -p $OUT
 python bench.py > $OUT/${TAG}_bench_C2.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"
@@ -10,7 +10,7 @@ python bench.py --eval-variant 2 --no-cpu-baseline > $OUT/${TAG}_bench_C2_exact_
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/${TAG}_launches_C2.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:k_eval_seg|k_eval_point3|k_march|k_lightgen<|k_resolve|k_flag_near|k_build_seg' -s 39 -c 13 -f \
+    -k 'regex:k_eval_seg|k_eval_point3|k_march|k_lightgen<|k_resolve|k_flag_near|k_build_seg|k_list_flagged' -s 42 -c 14 -f \
     -o $OUT/${TAG}_full_frame python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $OUT/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 ncu -i $OUT/${TAG}_full_frame.ncu-rep --page raw --csv > $OUT/${TAG}_ncu_full_frame_kernels.csv 2>/dev/null
 python tools/eval_variants.py sphere 1000 32 8 > $OUT/${TAG}_sphere_plain.log 2>&1 && \
