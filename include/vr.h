@@ -100,6 +100,14 @@ const char* vr_last_error(const vr_ctx* ctx); /* ctx may be NULL: error of a fai
  * (src/main.cpp:1191-1212). Copies `size` bytes; validates magic, grid type FLOAT and 32-byte size granularity.
  * Grids >= 4 GiB are accepted (64-bit addressing) but cannot be parity-checked against 32-bit GLSL addressing. */
 int vr_set_grid(vr_ctx* ctx, const void* nanovdb_bytes, uint64_t size);
+/* The same from a buffer that already is in device memory (this GPU's, or a peer's reachable over NVLink): multi-GPU
+ * hosts push the volume over PCIe once and replicate it GPU to GPU (e.g. an NCCL broadcast into `device_bytes`) instead
+ * of uploading it once per GPU. The copy is enqueued on the context's stream (vr_set_stream): it runs behind the work
+ * the caller enqueued there to produce `device_bytes`, and `device_bytes` may be overwritten once later work on that
+ * stream has started. `header` is a HOST copy of the first `header_size` bytes of the grid, at least up to the end of
+ * the root node's fixed part (1024 bytes cover every grid the NanoVDB writers lay out, where the root follows the tree);
+ * it supplies what the host must know: map, bounding box, root offset, tile count. No host synchronisation. */
+int vr_set_grid_device(vr_ctx* ctx, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size);
 
 /* ---- binding 0: rgba8 storage image sized to the swapchain extent, recreated on resize (src/main.cpp:338-378, :950).
  * Allocates the rgba8 image plus a float4 accumulator and resets the progressive state (frameCount = 0, :937). */

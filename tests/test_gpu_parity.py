@@ -431,3 +431,55 @@ def test_argument_errors(renderer, vr, cloud):
         r2.dispatch_light_gen("point")
     assert e.value.code == 5
     r2.close()
+
+
+@pytest.mark.gpu
+def test_set_grid_device_equals_set_grid(vr, cloud):
+    """vr_set_grid_device (grid taken from device memory in stream order, header from the host) renders what vr_set_grid
+    renders, bit for bit; a header that stops before the root node is refused; tiles.ReplicatedGrid (one upload, staging
+    buffers alternating) drives it the same way."""
+    import torch
+    from volumerenderer_b200 import tiles
+
+    grid_a, grid_b = cloud(64), cloud(32)
+    r = vr.VolumeRenderer(0)
+    try:
+        r.resize(96, 64)
+        r.update_ubo(maxLights=64)
+
+        def frames(setter):
+            out = []
+            for g in (grid_a, grid_b, grid_a):
+                setter(g)
+                r.reset_accumulation()
+                r.draw_frame("point")
+                r.draw_frame("point")
+                out.append((r.read_accum(), r.read_lights()[0].tobytes()))
+            return out
+
+        want = frames(r.set_grid)
+
+        def from_device(g):
+            t = torch.from_numpy(g).cuda()
+            torch.cuda.synchronize()  # the renderer runs on its own stream here: the source must be complete
+            r.set_grid_device(t.data_ptr(), g.nbytes, g[:1024])
+            r.sync()  # t goes out of scope: keep it alive until the copy has run
+
+        got = frames(from_device)
+        for (a, la), (b, lb) in zip(want, got):
+            assert np.array_equal(a, b) and la == lb and len(la) > 0
+        with pytest.raises(vr.VrError):
+            r.set_grid_device(torch.from_numpy(grid_a).cuda().data_ptr(), grid_a.nbytes, grid_a[:700])
+        # ReplicatedGrid on one rank: renderer on torch's stream, pinned source, no host synchronisation in between
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            r.set_stream(st.cuda_stream)
+            pinned = {id(g): torch.from_numpy(g).pin_memory() for g in (grid_a, grid_b)}
+            rg = {g.nbytes: tiles.ReplicatedGrid(r, g.nbytes) for g in (grid_a, grid_b)}
+            got2 = frames(lambda g: rg[g.nbytes].set_grid(pinned[id(g)], g[:4096]))
+            r.sync()
+        r.set_stream(None)
+        for (a, la), (b, lb) in zip(want, got2):
+            assert np.array_equal(a, b) and la == lb and len(la) > 0
+    finally:
+        r.close()

@@ -541,11 +541,10 @@ void vr_default_params(vr_ubo* p, uint32_t width, uint32_t height) {
     p->radiusFalloff = 0.0f;
 }
 
-int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
-    if (!c) return VR_E_ARG;
-    if (!bytes) return fail(c, VR_E_ARG, "vr_set_grid: NULL buffer");
-    const uint8_t* b = (const uint8_t*)bytes;
+// header checks shared by vr_set_grid / vr_set_grid_device: b holds the first `have` bytes of a grid of `size` bytes
+static int parse_grid_header(vr_ctx* c, const uint8_t* b, uint64_t have, uint64_t size, uint64_t* root_out, uint32_t* tiles_out) {
     if (size < 672 + 64 + 64) return fail(c, VR_E_BADGRID, "buffer too small for a NanoVDB grid (%llu bytes)", (unsigned long long)size);
+    if (have < 672 + 64) return fail(c, VR_E_ARG, "grid header too short (%llu bytes)", (unsigned long long)have);
     const uint64_t magic = rd<uint64_t>(b, 0);
     // "NanoVDB0" (grid), "NanoVDB1" / "NanoVDB2" are used by newer writers for the same GridData layout
     if (magic != 0x304244566f6e614eULL && magic != 0x314244566f6e614eULL && magic != 0x324244566f6e614eULL)
@@ -557,14 +556,15 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     const uint64_t tree = 672;
     const uint64_t root = tree + rd<uint64_t>(b, tree + 24);
     if (root + 64 > size) return fail(c, VR_E_BADGRID, "root offset outside the buffer");
+    if (root + 64 > have) return fail(c, VR_E_ARG, "grid header too short: the root node ends at byte %llu", (unsigned long long)(root + 64));
     const uint32_t tiles = rd<uint32_t>(b, root + 24);
     if (root + 64 + 32ull * tiles > size) return fail(c, VR_E_BADGRID, "root tile table outside the buffer");
-    VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
-    c->spec.valid = false;
-    // Two device buffers: the new grid goes into the one no enqueued work reads, on an upload stream, while the frames
-    // already enqueued keep rendering from the other (kernels take the grid pointer by value at launch). The host waits
-    // for the copy (the caller may reuse `bytes` on return); the GPU does not wait for anything.
+    *root_out = root, *tiles_out = tiles;
+    return VR_OK;
+}
+
+// the buffer the next grid goes into: the one of the two that no enqueued work reads
+static int grid_alt_prepare(vr_ctx* c, uint64_t size) {
     if (c->grid_alt && c->grid_alt_cap < size) {
         if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));
         cudaFree(c->grid_alt);
@@ -577,18 +577,16 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
         c->grid_alt_busy = false;
     }
     if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));  // its last readers (two grids ago) are done
-    VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, bytes, size, cudaMemcpyHostToDevice, c->upload_stream));
-    VR_CUDA(c, cudaStreamSynchronize(c->upload_stream));
-    // everything enqueued so far reads the old buffer: it is free again once this event has passed
-    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
-    {
-        uint8_t* t = c->grid;
-        c->grid = c->grid_alt, c->grid_alt = t;
-        const uint64_t tc = c->grid_cap;
-        c->grid_cap = c->grid_alt_cap, c->grid_alt_cap = tc;
-        c->grid_alt_busy = c->grid_alt != nullptr;
-    }
-    c->have_grid = false;
+    return VR_OK;
+}
+
+// the filled grid_alt becomes the grid; b = header bytes on the host
+static void grid_alt_install(vr_ctx* c, const uint8_t* b, uint64_t size, uint64_t root, uint32_t tiles) {
+    uint8_t* t = c->grid;
+    c->grid = c->grid_alt, c->grid_alt = t;
+    const uint64_t tc = c->grid_cap;
+    c->grid_cap = c->grid_alt_cap, c->grid_alt_cap = tc;
+    c->grid_alt_busy = c->grid_alt != nullptr;
     VrGridDev g{};
     g.base = c->grid;
     g.root = root;
@@ -608,6 +606,51 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     c->have_grid = true;
     c->march_key.valid = false;
     if (size >= (1ull << 32)) c->err = "note: grid >= 4 GiB, beyond the reference's 32-bit GLSL addressing";
+}
+
+int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
+    if (!c) return VR_E_ARG;
+    if (!bytes) return fail(c, VR_E_ARG, "vr_set_grid: NULL buffer");
+    const uint8_t* b = (const uint8_t*)bytes;
+    uint64_t root = 0;
+    uint32_t tiles = 0;
+    int rc = parse_grid_header(c, b, size, size, &root, &tiles);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
+    c->spec.valid = false;
+    // Two device buffers: the new grid goes into the one no enqueued work reads, on an upload stream, while the frames
+    // already enqueued keep rendering from the other (kernels take the grid pointer by value at launch). The host waits
+    // for the copy (the caller may reuse `bytes` on return); the GPU does not wait for anything.
+    rc = grid_alt_prepare(c, size);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, bytes, size, cudaMemcpyHostToDevice, c->upload_stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->upload_stream));
+    // everything enqueued so far reads the old buffer: it is free again once this event has passed
+    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    c->have_grid = false;
+    grid_alt_install(c, b, size, root, tiles);
+    return VR_OK;
+}
+
+int vr_set_grid_device(vr_ctx* c, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size) {
+    if (!c) return VR_E_ARG;
+    if (!device_bytes || !header) return fail(c, VR_E_ARG, "vr_set_grid_device: NULL buffer");
+    uint64_t root = 0;
+    uint32_t tiles = 0;
+    int rc = parse_grid_header(c, (const uint8_t*)header, header_size < size ? header_size : size, size, &root, &tiles);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
+    c->spec.valid = false;
+    rc = grid_alt_prepare(c, size);
+    if (rc != VR_OK) return rc;
+    // device -> device (or peer -> device over NVLink) in stream order: behind whatever the caller enqueued on this
+    // context's stream to produce device_bytes (e.g. a broadcast), in front of the next frame; no host synchronisation
+    VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, device_bytes, size, cudaMemcpyDefault, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    c->have_grid = false;
+    grid_alt_install(c, (const uint8_t*)header, size, root, tiles);
     return VR_OK;
 }
 

@@ -65,6 +65,12 @@ class VolumeRenderer:
         g = np.ascontiguousarray(np.frombuffer(grid_bytes, np.uint8) if not isinstance(grid_bytes, np.ndarray) else grid_bytes)
         self._check(self._L.vr_set_grid(self._ctx, g.ctypes.data_as(C.c_void_p), g.nbytes))
 
+    def set_grid_device(self, device_ptr, nbytes, header):
+        """vr_set_grid_device: the grid from `nbytes` bytes of device memory at `device_ptr` (int), copied in stream order
+        on the renderer's stream; `header` = host bytes of the grid's first >= 1024 bytes (or the whole grid)."""
+        h = np.ascontiguousarray(np.frombuffer(header, np.uint8) if not isinstance(header, np.ndarray) else header)
+        self._check(self._L.vr_set_grid_device(self._ctx, C.c_void_p(int(device_ptr)), int(nbytes), h.ctypes.data_as(C.c_void_p), h.nbytes))
+
     def resize(self, width, height):
         """binding 0: storage image sized to the framebuffer; resets the progressive state (src/main.cpp:936-982)."""
         self._check(self._L.vr_resize(self._ctx, width, height))

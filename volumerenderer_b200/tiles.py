@@ -223,3 +223,47 @@ def accum_as_tensor(renderer):
     bufs = renderer.device_buffers()
     return torch.as_tensor(DeviceArray(bufs["accum"], (renderer.height, renderer.width, 4), "<f4"),
                            device=f"cuda:{renderer.device}")
+
+
+class ReplicatedGrid:
+    """A new volume every frame on N GPUs with ONE host->device transfer per node: rank `src` uploads the NanoVDB bytes
+    into a device staging buffer (its own stream, two buffers, so the upload of frame k+1 runs under frame k), one NCCL
+    broadcast replicates them over NVLink, and every rank installs them with vr_set_grid_device in stream order. Nothing
+    here blocks the host. The renderer must run on torch's current stream (renderer.set_stream), which is also the
+    stream the broadcast is ordered on."""
+
+    def __init__(self, renderer, nbytes, src=0, group=None):
+        import torch
+
+        self.r, self.src, self.group, self.nbytes = renderer, src, group, int(nbytes)
+        dev = f"cuda:{renderer.device}"
+        self.staging = [torch.empty(self.nbytes, dtype=torch.uint8, device=dev) for _ in range(2)]
+        self.upload = torch.cuda.Stream(device=dev)
+        self.uploaded = [torch.cuda.Event() for _ in range(2)]
+        self.consumed = [None, None]
+        self.k = 0
+
+    def set_grid(self, pinned_grid, header):
+        """pinned_grid: uint8 CPU tensor (pinned) with the grid on rank `src`, ignored elsewhere; header: host bytes of the
+        grid's first >= 1024 bytes, on every rank (they carry the map, the bounding box and the root offset)."""
+        import torch
+        import torch.distributed as dist
+
+        i = self.k & 1
+        main = torch.cuda.current_stream()
+        world = dist.get_world_size(self.group) if dist.is_initialized() else 1
+        rank = dist.get_rank(self.group) if dist.is_initialized() else 0
+        if rank == self.src:
+            if self.consumed[i] is not None:
+                self.upload.wait_event(self.consumed[i])  # the broadcast of two frames ago has read this buffer
+            with torch.cuda.stream(self.upload):
+                self.staging[i].copy_(pinned_grid, non_blocking=True)
+                self.uploaded[i].record(self.upload)
+            main.wait_event(self.uploaded[i])
+        if world > 1:
+            dist.broadcast(self.staging[i], src=self.src, group=self.group)
+        self.r.set_grid_device(self.staging[i].data_ptr(), self.nbytes, header)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.consumed[i] = ev
+        self.k += 1
