@@ -188,6 +188,14 @@ int vr_row_sample_counts(vr_ctx* ctx, uint64_t* rows_out /* height entries */);
  * camera, image size and march parameters are unchanged (progressive accumulation) */
 int vr_set_march_cache(vr_ctx* ctx, int enabled);
 
+/* 1 (default): with the ray-segment evaluation (variant 8) the camera march runs ONCE per frame: every pixel gets a slot
+ * in the sample buffer sized by a lookup-free upper bound of its step count (the march loop's own t sequence), so the
+ * counting pass of the two-pass march (count, scan, fill) is not needed; the sample buffer then has gaps and is about
+ * S_ref/S_eff times larger. 0: always two passes and a compact buffer. Images, counters and vr_read_samples are identical
+ * either way. The exact kernels (variants 0-3), the opt-in physics and frames whose bound total would not fit 32-bit
+ * sample indices use the two-pass march regardless. */
+int vr_set_march_single_pass(vr_ctx* ctx, int enabled);
+
 /* 1 (default): once two consecutive vr_render_frame calls had the same inputs, each call also generates the NEXT frame's
  * lights (same UBO, frameCount + 1) into a second light buffer on the auxiliary stream, underneath its evaluation kernel;
  * the next call adopts them if its inputs are what was assumed and regenerates otherwise. Results are identical either

@@ -483,3 +483,53 @@ def test_set_grid_device_equals_set_grid(vr, cloud):
             assert np.array_equal(a, b) and la == lb and len(la) > 0
     finally:
         r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("algo", ["point", "beam"])
+def test_single_pass_march_equals_two_pass(vr, cloud, algo):
+    """The single-pass march (slots from the lookup-free step bound, sample buffer with gaps) and the two-pass march
+    (count, scan, fill: compact buffer) give the same samples, counters and images bit for bit, on the whole frame, on
+    tiles, with a new grid every frame and with the march cache."""
+    from volumerenderer_b200.tiles import band_tile
+
+    grid, grid2 = cloud(64), cloud(32)
+    r = vr.VolumeRenderer(0)
+    try:
+        W, H = 160, 96
+        r.resize(W, H)
+        r.update_ubo(maxLights=48, beamRadius=0.4)
+
+        def run(single):
+            r.set_march_single_pass(single)
+            out = []
+            for g in (grid, grid2, grid):
+                r.set_grid(g)
+                r.reset_accumulation()
+                for _ in range(3):
+                    r.draw_frame(algo)
+                out.append((r.read_accum(), r.read_image_rgba8(), r.read_samples(), r.counters(), r.row_sample_counts()))
+            # two tiles of one frame, then the march cache on repeated frames
+            r.clear_image()
+            r.dispatch_compute_color(algo, band_tile((0, 40), W))
+            s0 = r.read_samples()
+            r.dispatch_compute_color(algo, band_tile((40, H - 40), W))
+            out.append((r.read_frame_color(), s0, r.read_samples()))
+            r.set_march_cache(True)
+            r.reset_accumulation()
+            for _ in range(3):
+                r.draw_frame(algo)
+            r.set_march_cache(False)
+            out.append((r.read_accum(),))
+            return out
+
+        two, one = run(False), run(True)
+        for a, b in zip(two, one):
+            for x, y in zip(a, b):
+                if isinstance(x, dict):
+                    assert x == y
+                else:
+                    assert np.array_equal(x, y)
+        assert two[0][3]["S_eff"] > 10000 and len(two[0][2]) == two[0][3]["S_eff"]
+    finally:
+        r.close()

@@ -61,7 +61,7 @@ EXPORTS = [
     "vr_dispatch_light_gen", "vr_dispatch_compute_color", "vr_set_light_gen_groups", "vr_render_frame",
     "vr_reset_accumulation", "vr_sync", "vr_read_lights", "vr_read_light_counter", "vr_read_image_rgba8",
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
-    "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_accumulate_frame_color", "vr_set_frame_color_peers", "vr_set_march_cache", "vr_set_light_prefetch", "vr_read_accum_f32_async", "vr_read_wait", "vr_set_options", "vr_get_options", "vr_trilinear_values", "vr_progressive_radius", "vr_set_eval_variant", "vr_set_eval_near_distance", "vr_get_eval_segment_counts", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
+    "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_accumulate_frame_color", "vr_set_frame_color_peers", "vr_set_march_cache", "vr_set_march_single_pass", "vr_set_light_prefetch", "vr_read_accum_f32_async", "vr_read_wait", "vr_set_options", "vr_get_options", "vr_trilinear_values", "vr_progressive_radius", "vr_set_eval_variant", "vr_set_eval_near_distance", "vr_get_eval_segment_counts", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
     "vr_set_stream", "vr_set_grid_device", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
     "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
     "vr_io_last_error",
@@ -123,6 +123,7 @@ def load():
     L.vr_set_frame_color_peers.argtypes = [P, P, C.POINTER(P), U32]
     L.vr_set_march_cache.argtypes = [P, I]
     L.vr_set_light_prefetch.argtypes = [P, I]
+    L.vr_set_march_single_pass.argtypes = [P, I]
     L.vr_cpu_test_render.argtypes = [P, U32, U32, P]
     L.vr_set_options.argtypes = [P, C.POINTER(VrOptions)]
     L.vr_get_options.argtypes = [P, C.POINTER(VrOptions)]

@@ -51,14 +51,31 @@ struct MarchKey {
     uint32_t dim[2] = {0, 0};
     float cam[3] = {0, 0, 0}, fov = 0, maxd = 0, step = 0, absorb = 0;
     uint32_t trilinear = 0;
+    uint32_t gaps = 0;  // layout of the sample buffer: 1 = single-pass march, one slot per pixel sized by its step bound
     bool valid = false;
     bool operator==(const MarchKey& o) const {
         return valid && o.valid && grid_gen == o.grid_gen && memcmp(&tile, &o.tile, sizeof(tile)) == 0 &&
                memcmp(dim, o.dim, sizeof(dim)) == 0 && memcmp(cam, o.cam, sizeof(cam)) == 0 && fov == o.fov &&
-               maxd == o.maxd && step == o.step && absorb == o.absorb && trilinear == o.trilinear;
+               maxd == o.maxd && step == o.step && absorb == o.absorb && trilinear == o.trilinear && gaps == o.gaps;
     }
 };
 }  // namespace
+
+// what the per-pixel step bounds of the single-pass march depend on: the rays and the grid's box and map, not its voxels
+struct BoundKey {
+    vr_tile tile = {0, 0, 0, 0};
+    uint32_t dim[2] = {0, 0};
+    float cam[3] = {0, 0, 0}, fov = 0, maxd = 0, step = 0;
+    int32_t bmin[3] = {0, 0, 0}, bmax[3] = {0, 0, 0};
+    float mat[9] = {0}, inv[9] = {0}, vec[3] = {0};
+    bool valid = false;
+    bool operator==(const BoundKey& o) const {
+        return valid && o.valid && memcmp(&tile, &o.tile, sizeof(tile)) == 0 && memcmp(dim, o.dim, sizeof(dim)) == 0 &&
+               memcmp(cam, o.cam, sizeof(cam)) == 0 && fov == o.fov && maxd == o.maxd && step == o.step &&
+               memcmp(bmin, o.bmin, sizeof(bmin)) == 0 && memcmp(bmax, o.bmax, sizeof(bmax)) == 0 &&
+               memcmp(mat, o.mat, sizeof(mat)) == 0 && memcmp(inv, o.inv, sizeof(inv)) == 0 && memcmp(vec, o.vec, sizeof(vec)) == 0;
+    }
+};
 
 struct vr_ctx {
     int device = 0;
@@ -155,13 +172,19 @@ struct vr_ctx {
     Scalars* scalars_host = nullptr;
     cudaEvent_t ev_scalars = nullptr;
     bool counters_pending = false, counters_have_march = false;
-    uint64_t nsamples_used = 0;
+    uint64_t nsamples_used = 0;  // what totals[0] holds for this gather (sample buffer range)
+    uint64_t nreal_used = 0;     // samples of this gather
     unsigned long long* eval_redo = nullptr;  // CTAs of the speculative eval kernel that repeated with the guard (cumulative)
     vr_counters last_counters{};
     vr_algo last_algo = VR_ALGO_POINT;
     bool march_cache = false;
     MarchKey march_key;
-    uint64_t cached_samples = 0;
+    uint64_t cached_samples = 0;  // length of the sample buffer's address range (= sample count when the buffer is compact)
+    uint64_t cached_real = 0;     // number of samples in it
+    bool march_single = true;     // vr_set_march_single_pass
+    MarchKey gaps_refused;        // rays whose bound total does not fit 32-bit sample indices: two-pass march
+    BoundKey bound_key;           // px_offsets hold the slots of these rays (single-pass layout), bound_extent their total
+    uint64_t bound_extent = 0;
     uint64_t cached_S[2] = {0, 0};  // S_ref, S_eff of the cached march
     // timing: a ring of event sets so that per-pass times can be collected without a host sync per frame
     struct TimingSet {
@@ -358,7 +381,7 @@ int finalize_counters(vr_ctx* c) {
     if (lc > c->light_capacity) lc = c->light_capacity;
     c->last_counters.light_count = lc;
     c->last_counters.eval_lights = h.neval;
-    c->last_counters.E = c->nsamples_used * h.neval;
+    c->last_counters.E = c->nreal_used * h.neval;
     return VR_OK;
 }
 
@@ -843,34 +866,85 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     key.fov = c->ubo.fov, key.maxd = c->ubo.rayMaxDistance, key.step = c->ubo.rayMarchingStepSize, key.absorb = c->ubo.absorptionCoefficient;
     key.trilinear = c->phys.trilinear;
     key.valid = true;
-    const bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
+    // Single-pass march (default with the ray-segment evaluation, which addresses samples through tables): slots sized by
+    // a lookup-free bound of each pixel's step count, so the count pass of the two-pass march (40 % of it) is not needed.
+    // The exact kernels (variants 0-3) and the opt-in physics walk a compact sample array: two passes for them.
+    key.gaps = (c->march_single && c->eval_variant == 8 && !(c->phys.phase_hg || c->phys.light_transmittance)) ? 1u : 0u;
+    if (key.gaps && key == c->gaps_refused) key.gaps = 0;
+    bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
     const bool reuse = c->march_cache && same_key;
-    uint64_t nsamples = c->cached_samples;
+    uint64_t nsamples = c->cached_samples, nreal = c->cached_real;
     if (!reuse) {
         VR_CUDA(c, c->px_counts.reserve(npix));
         VR_CUDA(c, c->px_offsets.reserve(npix));
         VR_CUDA(c, c->scan_tmp.reserve((npix + 4095) / 4096 + 1));
         VR_CUDA(c, cudaMemsetAsync(c->wc, 0, sizeof(VrWorkCounters), st));
-        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, (int)c->phys.trilinear, c->px_counts.p, nullptr, nullptr, c->wc);
-        vrk_scan_u32(st, c->px_counts.p, c->px_offsets.p, c->totals + 0, npix, c->scan_tmp.p);
-        if (!same_key) {
-            // first gather with these rays: the sample total sizes the buffers, one blocking read. Later frames with
-            // the same camera/grid/tile march again (count and fill) but the total is known: no host round trip.
+        BoundKey bk;
+        bk.tile = tile, bk.dim[0] = c->width, bk.dim[1] = c->height;
+        memcpy(bk.cam, c->ubo.cameraPos, sizeof(bk.cam));
+        bk.fov = c->ubo.fov, bk.maxd = c->ubo.rayMaxDistance, bk.step = c->ubo.rayMarchingStepSize;
+        memcpy(bk.bmin, c->gdev.bmin, sizeof(bk.bmin)), memcpy(bk.bmax, c->gdev.bmax, sizeof(bk.bmax));
+        memcpy(bk.mat, c->gdev.mat, sizeof(bk.mat)), memcpy(bk.inv, c->gdev.inv, sizeof(bk.inv)), memcpy(bk.vec, c->gdev.vec, sizeof(bk.vec));
+        bk.valid = true;
+        // the slots depend on the rays and on the grid's box and map only: a new grid of the same shape (an animated
+        // volume) keeps them, and the frame needs neither the bound kernel nor the blocking read of the total
+        const bool same_slots = key.gaps && (bk == c->bound_key);
+        if (!key.gaps) c->bound_key.valid = false;  // the two-pass march overwrites px_offsets
+        if (key.gaps && !same_slots) {
             c->march_key.valid = false;
+            c->bound_key.valid = false;
+            vrk_march_bound(st, c->gdev, c->ubo, tan_scale, tile, c->px_counts.p);
+            vrk_scan_u32(st, c->px_counts.p, c->px_offsets.p, c->totals + 0, npix, c->scan_tmp.p);
             VR_CUDA(c, cudaMemcpyAsync(c->totals_host, c->totals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
             VR_CUDA(c, cudaStreamSynchronize(st));
             rc = check_stream(c);
             if (rc != VR_OK) return rc;
             nsamples = c->totals_host[0];
-            VR_CUDA(c, c->samples.reserve(nsamples + 1));
+            if (nsamples >= (1ull << 32) - 4096) {  // sample indices are 32-bit in the segment tables
+                c->gaps_refused = key;
+                key.gaps = 0;
+            } else {
+                VR_CUDA(c, c->samples.reserve(nsamples + 1));
+                c->bound_key = bk;
+                c->bound_extent = nsamples;
+            }
         }
-        vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
+        if (key.gaps) nsamples = c->bound_extent;
+        if (key.gaps) {
+            // same rays as before: the slots (offsets, total) are still valid, the march alone runs again
+            vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 2, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, c->wc);
+            if (!same_key) {  // the number of samples sizes the segment tables and the evaluation launches: second blocking read
+                VR_CUDA(c, cudaMemcpyAsync(c->totals_host + 2, &c->wc->S_eff, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                VR_CUDA(c, cudaStreamSynchronize(st));
+                rc = check_stream(c);
+                if (rc != VR_OK) return rc;
+                nreal = c->totals_host[2];
+            }
+        } else {
+            vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, (int)c->phys.trilinear, c->px_counts.p, nullptr, nullptr, c->wc);
+            vrk_scan_u32(st, c->px_counts.p, c->px_offsets.p, c->totals + 0, npix, c->scan_tmp.p);
+            if (!same_key) {
+                // first gather with these rays: the sample total sizes the buffers, one blocking read. Later frames with
+                // the same camera/grid/tile march again (count and fill) but the total is known: no host round trip.
+                c->march_key.valid = false;
+                VR_CUDA(c, cudaMemcpyAsync(c->totals_host, c->totals, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+                VR_CUDA(c, cudaStreamSynchronize(st));
+                rc = check_stream(c);
+                if (rc != VR_OK) return rc;
+                nsamples = c->totals_host[0];
+                VR_CUDA(c, c->samples.reserve(nsamples + 1));
+            }
+            nreal = nsamples;
+            vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
+        }
         c->cached_samples = nsamples;
+        c->cached_real = nreal;
         c->march_key = key;
         c->seg_valid = false;
     }
     VR_CUDA(c, c->contrib.reserve(nsamples + 1));
     c->nsamples_used = nsamples;
+    c->nreal_used = nreal;
     cudaEventRecord(t->ev[3], st);
 
     // ---- light list for the evaluation kernels (needs the lights: join the light-generation stream)
@@ -943,22 +1017,22 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         VrSegLists sl;
         if (c->seg_pairs != (sphere ? 0 : 1)) c->seg_valid = false;
         if (!c->seg_valid) {
-            const uint64_t n8 = nsamples / 8 + 1;
+            const uint64_t n8 = nreal / 8 + 1;
             VR_CUDA(c, c->seg_first.reserve(n8));
             VR_CUDA(c, c->seg_pix.reserve(n8));
             VR_CUDA(c, c->seg_flag.reserve(n8));
-            VR_CUDA(c, c->seg16_first.reserve(nsamples / 16 + 1));
-            VR_CUDA(c, c->seg16_pix.reserve(nsamples / 16 + 1));
-            VR_CUDA(c, c->seg16_flag.reserve(nsamples / 16 + 1));
-            VR_CUDA(c, c->seg_flags.reserve(nsamples / 8 + 2));
-            VR_CUDA(c, c->seg_list.reserve(nsamples + 1));
+            VR_CUDA(c, c->seg16_first.reserve(nreal / 16 + 1));
+            VR_CUDA(c, c->seg16_pix.reserve(nreal / 16 + 1));
+            VR_CUDA(c, c->seg16_flag.reserve(nreal / 16 + 1));
+            VR_CUDA(c, c->seg_flags.reserve(nreal / 8 + 2));
+            VR_CUDA(c, c->seg_list.reserve(nreal + 1));
             VR_CUDA(c, c->seg_base.reserve(npix + 1));
         }
         sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
         sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
         sl.list = c->seg_list.p, sl.counts = c->seg_counts;
         sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
-        sl.list_capacity = (uint32_t)nsamples;
+        sl.list_capacity = (uint32_t)nreal;
         if (!c->seg_valid) {
             vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl, sphere ? 0 : 1);
             c->seg_valid = true;
@@ -972,7 +1046,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             if (rho < 0.1f) rho = 0.1f;
         }
         static const bool seg_side = !(getenv("VR_SEG_SIDE") && atoi(getenv("VR_SEG_SIDE")) == 0);  // experiments: 0 = one stream
-        vrk_eval_point_seg(st, seg_side ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nsamples, npix, c->px_counts.p, c->px_offsets.p, sl,
+        vrk_eval_point_seg(st, seg_side ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nreal, npix, c->px_counts.p, c->px_offsets.p, sl,
                            c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)
@@ -1396,14 +1470,43 @@ int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    const uint64_t n = c->cached_samples;
+    const uint64_t n = c->cached_real;
     if (count) *count = n;
     const uint64_t m = n < capacity ? n : capacity;
     if (m && !out) return fail(c, VR_E_ARG, "vr_read_samples: NULL output buffer");
-    if (m) {
+    if (!m) return VR_OK;
+    if (!c->march_key.gaps) {
         VR_CUDA(c, cudaMemcpyAsync(out, c->samples.p, m * sizeof(VrSample), cudaMemcpyDeviceToHost, c->stream));
         VR_CUDA(c, cudaStreamSynchronize(c->stream));
+        return VR_OK;
     }
+    // single-pass march: the sample buffer has gaps; gather the pixels' runs into a compact copy first
+    const vr_tile tile = c->march_key.tile;
+    const uint64_t npix = (uint64_t)tile.w * tile.h;
+    DevBuf<unsigned long long> compact_offsets, total;
+    DevBuf<VrSample> compact;
+    int rc = VR_OK;
+    do {
+        if (compact_offsets.reserve(npix) != cudaSuccess || total.reserve(1) != cudaSuccess || compact.reserve(n + 1) != cudaSuccess ||
+            c->scan_tmp.reserve((npix + 4095) / 4096 + 1) != cudaSuccess) {
+            rc = fail(c, VR_E_CUDA, "vr_read_samples: out of device memory");
+            break;
+        }
+        vrk_scan_u32(c->stream, c->px_counts.p, compact_offsets.p, total.p, npix, c->scan_tmp.p);
+        vrk_compact_samples(c->stream, c->px_counts.p, c->px_offsets.p, compact_offsets.p, npix, c->samples.p, compact.p);
+        if (cudaMemcpyAsync(out, compact.p, m * sizeof(VrSample), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+            cudaStreamSynchronize(c->stream) != cudaSuccess)
+            rc = fail(c, VR_E_CUDA, "vr_read_samples: copy failed");
+    } while (0);
+    compact_offsets.release();
+    total.release();
+    compact.release();
+    return rc;
+}
+
+int vr_set_march_single_pass(vr_ctx* c, int enabled) {
+    if (!c) return VR_E_ARG;
+    c->march_single = enabled != 0;
     return VR_OK;
 }
 

@@ -288,10 +288,31 @@ __global__ void k_prepare_expand(const vr_ray_light* __restrict__ lights, const 
 // 4-byte value loads of a warp fall into a handful of 128-byte lines). One thread per pixel.
 // TRI: the density at a sample is the trilinear interpolation of the eight surrounding voxel values (opt-in, vr_options);
 // a zero tile value then says nothing about the interpolated neighbourhood, so the empty-tile skipping is off.
-template <bool FILL, bool TRI>
+// An upper bound of a pixel's sample count that needs no lookups: the number of steps its march loop can take, from the
+// same FP32 sequence t = max(tmin, 0), t += step while t < tmax (the lookups, the bbox test and the T cut-off only ever
+// remove steps). With it the march runs ONCE (MODE 2 below): a scan of the bounds gives every pixel a private, large
+// enough slot in the sample buffer, which then has gaps; every later kernel addresses samples through (counts, offsets).
+__global__ void __launch_bounds__(128) k_march_bound(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, uint32_t* __restrict__ bound) {
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    if (lx >= tile.w || ly >= tile.h) return;
+    const VrCamRay r = vr_camera_ray(g, u, tan_scale, tile.x0 + lx, tile.y0 + ly);
+    uint32_t n = 0;
+    if (r.hit && r.tmax > 0.0f) {
+        const float step = u.rayMarchingStepSize;
+        for (float t = vr_max(r.tmin, 0.0f); t < r.tmax; t = vr_add(t, step)) n++;
+    }
+    bound[(uint64_t)ly * tile.w + lx] = n;
+}
+
+// MODE 0: count the pixel's samples (counts, work counters); 1: write them at offsets[pix] (after a scan of the counts:
+// compact sample buffer); 2: both in one pass, offsets from a scan of k_march_bound's bounds (sample buffer with gaps)
+template <int MODE, bool TRI>
 __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                 uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
                                                 VrSample* __restrict__ samples, VrWorkCounters* wc) {
+    constexpr bool FILL = MODE != 0, COUNT = MODE != 1;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -337,9 +358,9 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
                 t = vr_add(t, step);
             }
         }
-        if (!FILL) counts[pix] = n;
+        if (COUNT) counts[pix] = n;
     }
-    if (!FILL && wc) {
+    if (COUNT && wc) {
         unsigned long long a = sref, b = n;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -1591,19 +1612,42 @@ void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLig
     if (!capacity) return;
     k_prepare_expand<<<capacity, 64, 0, st>>>(lights, counter, lrs, offsets, out, out2, capacity, out_capacity, overflow);
 }
-void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill, int trilinear,
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int mode, int trilinear,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
     VR_COUNT(1);
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
+#define VR_MARCH(M, T) k_march<M, T><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc)
     if (trilinear) {
-        if (fill)
-            k_march<true, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
-        else
-            k_march<false, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
-    } else if (fill)
-        k_march<true, false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
-    else
-        k_march<false, false><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc);
+        if (mode == 0) VR_MARCH(0, true);
+        else if (mode == 1) VR_MARCH(1, true);
+        else VR_MARCH(2, true);
+    } else {
+        if (mode == 0) VR_MARCH(0, false);
+        else if (mode == 1) VR_MARCH(1, false);
+        else VR_MARCH(2, false);
+    }
+#undef VR_MARCH
+}
+void vrk_march_bound(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, uint32_t* bound) {
+    VR_COUNT(1);
+    dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
+    k_march_bound<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, bound);
+}
+// samples of a buffer with gaps -> compact list in pixel order (test hook vr_read_samples)
+__global__ void __launch_bounds__(256) k_compact_samples(const uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
+                                                         const unsigned long long* __restrict__ compact_offsets, uint64_t npix,
+                                                         const VrSample* __restrict__ samples, VrSample* __restrict__ out) {
+    const uint64_t p = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= npix) return;
+    const float4* src = reinterpret_cast<const float4*>(samples) + offsets[p];
+    float4* dst = reinterpret_cast<float4*>(out) + compact_offsets[p];
+    for (uint32_t i = 0, n = counts[p]; i < n; i++) dst[i] = src[i];
+}
+void vrk_compact_samples(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, const unsigned long long* compact_offsets,
+                         uint64_t npix, const VrSample* samples, VrSample* out) {
+    if (npix == 0) return;
+    VR_COUNT(1);
+    k_compact_samples<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, compact_offsets, npix, samples, out);
 }
 // opt-in phase function / light->sample transmittance: one thread per sample, every rounding of the oracle kept
 void vrk_eval_phys(cudaStream_t st, int sphere, const VrGridDev& g, const vr_ubo& u, const VrPhysics& phys, const VrSample* samples,

@@ -56,8 +56,13 @@ void vrk_prepare_expand(cudaStream_t st, const vr_ray_light* lights, const VrLig
                         const unsigned long long* offsets, VrEvalLight* out, float4* out2, uint32_t capacity,
                         uint64_t out_capacity, uint32_t* overflow);
 // ---- camera-ray march (shaders/point_compute_color.comp:60-94 minus the light loop)
-void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int fill, int trilinear,
+// mode 0: count per pixel (+ work counters); 1: fill at offsets (compact buffer, offsets = scan of the counts);
+// 2: single pass, counts + fill at offsets = scan of vrk_march_bound's per-pixel upper bounds (buffer with gaps)
+void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int mode, int trilinear,
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc);
+void vrk_march_bound(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, uint32_t* bound);
+void vrk_compact_samples(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, const unsigned long long* compact_offsets,
+                         uint64_t npix, const VrSample* samples, VrSample* out);
 // ---- opt-in physics (vr_options): evaluation with the phase / transmittance factor, and the trilinear test hook
 void vrk_eval_phys(cudaStream_t st, int sphere, const VrGridDev& g, const vr_ubo& u, const VrPhysics& phys, const VrSample* samples,
                    uint64_t nsamples, const VrEvalLight* lights, const unsigned long long* nlights_dev, float* out);

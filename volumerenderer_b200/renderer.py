@@ -280,6 +280,10 @@ class VolumeRenderer:
         self._check(self._L.vr_get_device_buffers(self._ctx, C.byref(a), C.byref(i), C.byref(f), C.byref(s)))
         return dict(accum=a.value, rgba8=i.value, frame_color=f.value, stream=s.value)
 
+    def set_march_single_pass(self, enabled):
+        """vr_set_march_single_pass: 1 (default) = one march per frame into a sample buffer with gaps; 0 = count + fill."""
+        self._check(self._L.vr_set_march_single_pass(self._ctx, int(bool(enabled))))
+
     def set_stream(self, cuda_stream):
         """Run on a caller-owned CUDA stream (int handle, e.g. torch.cuda.current_stream().cuda_stream); None = own."""
         self._check(self._L.vr_set_stream(self._ctx, C.c_void_p(cuda_stream) if cuda_stream else None))
