@@ -4,7 +4,7 @@
 //
 //   light generation   k_lightgen<LOCAL> -> scan -> k_lightgen_compact    shaders/light_gen.comp:9-100
 //   light expansion    k_prepare_* (ray/beam sub-points pre-expanded)     shaders/ray_compute_color.comp:13-20
-//   camera march       k_march<COUNT> -> scan -> k_march<FILL>            shaders/point_compute_color.comp:20-94
+//   camera march       k_march_bound -> scan -> k_march<SINGLE> (or <COUNT> -> scan -> <FILL>)   shaders/point_compute_color.comp:20-94
 //   evaluation (HOT)   k_eval<POINT|SPHERE>: samples x lights             shaders/common_functions.h:182-201
 //   resolve            k_resolve: ordered per-pixel sum, clamp, average   shaders/point_compute_color.comp:97-105
 //
