@@ -421,6 +421,11 @@ def test_argument_errors(renderer, vr, cloud):
     with pytest.raises(vr.VrError):
         renderer.dispatch_compute_color("ray")
     renderer.update_ubo(lightRayStepSize=0.3)
+    renderer.update_ubo(rayMarchingStepSize=1.0e-6)  # t += step would stop advancing: refused instead of hanging the GPU
+    with pytest.raises(vr.VrError) as e:
+        renderer.dispatch_compute_color("point")
+    assert e.value.code == 1 and "too small" in str(e.value)
+    renderer.update_ubo(rayMarchingStepSize=1.0)
     with pytest.raises(vr.VrError) as e:
         renderer.set_grid(np.zeros(4096, np.uint8))
     assert e.value.code == 3

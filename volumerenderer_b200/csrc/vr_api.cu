@@ -807,6 +807,21 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     if ((algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM) && !(c->ubo.lightRayStepSize > 0.0f))
         return fail(c, VR_E_ARG, "lightRayStepSize must be > 0 for ray/beam (uint(len/0) is undefined, ray_compute_color.comp:15)");
     if (!(c->ubo.rayMarchingStepSize > 0.0f)) return fail(c, VR_E_ARG, "rayMarchingStepSize must be > 0");
+    {
+        // t += step stops advancing once step < ulp(t)/2, i.e. beyond ~1.6e7 steps per ray: the shader loop (and ours)
+        // would never end. The longest ray inside the grid's box runs from the camera to the box's far corner.
+        const VrGridDev& g = c->gdev;
+        const double sx = c->ubo.cameraPos[0] - g.vec[0], sy = c->ubo.cameraPos[1] - g.vec[1], sz = c->ubo.cameraPos[2] - g.vec[2];
+        double far2 = 0.0;
+        for (int a = 0; a < 3; a++) {
+            const double ci = sx * g.inv[3 * a] + sy * g.inv[3 * a + 1] + sz * g.inv[3 * a + 2];
+            const double lo = fabs(ci - (double)g.bmin[a]), hi = fabs((double)g.bmax[a] + 1.0 - ci);
+            far2 += (lo > hi ? lo : hi) * (lo > hi ? lo : hi);
+        }
+        if (sqrt(far2) / (double)c->ubo.rayMarchingStepSize > 8.0e6)
+            return fail(c, VR_E_ARG, "rayMarchingStepSize %g is too small for this grid and camera: more than 8e6 steps per ray, the FP32 march would stop advancing",
+                        (double)c->ubo.rayMarchingStepSize);
+    }
     vr_tile tile;
     int rc = validate_tile(c, tile_or_null, &tile);
     if (rc != VR_OK) return rc;
