@@ -892,6 +892,10 @@ __global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __
     const VrEvalLight L = lights[li];
     const float cx = u.cameraPos[0], cy = u.cameraPos[1], cz = u.cameraPos[2];
     const float vx = L.x - cx, vy = L.y - cy, vz = L.z - cz;
+    if (!(vx * vx + vy * vy + vz * vz <= 1.0e10f)) {  // absurdly far (or NaN): products of squared distances may leave FP32
+        if (threadIdx.x == 0) *sl.flag_all = 1u;
+        continue;
+    }
     if (vz + rho < 0.0f) continue;  // behind the camera plane by more than rho: no forward ray comes near
     if (vz - rho <= 1.0e-3f * rho) {
         if (threadIdx.x == 0) *sl.flag_all = 1u;
