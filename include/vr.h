@@ -158,6 +158,10 @@ int vr_read_accum_f32(vr_ctx* ctx, float* out);            /* width*height*4 flo
  * enqueued next; `out` is valid after vr_read_wait (or the next vr_read_accum_f32_async, which waits for the previous one). */
 int vr_read_accum_f32_async(vr_ctx* ctx, float* out);
 int vr_read_wait(vr_ctx* ctx);
+/* the same for one tile: in image-tiled multi-GPU runs every GPU returns the rows it rendered over its own PCIe link
+ * instead of one GPU pulling the whole image. `out` addresses the tile's first pixel in the caller's image (pinned memory,
+ * possibly shared between the ranks' processes), rows out_pitch_bytes apart. One read-back in flight per context. */
+int vr_read_accum_f32_tile_async(vr_ctx* ctx, const vr_tile* tile_or_null, float* out, uint64_t out_pitch_bytes);
 int vr_read_frame_color_f32(vr_ctx* ctx, float* out);      /* width*height floats: the last frame's clamp()ed colour, R=G=B */
 int vr_write_accum_f32(vr_ctx* ctx, const float* in, uint32_t frame_count); /* restore a snapshot (resume) */
 int vr_write_image_rgba8(vr_ctx* ctx, const uint8_t* in);
@@ -195,12 +199,37 @@ int vr_set_march_cache(vr_ctx* ctx, int enabled);
  * either way. The exact kernels (variants 0-3), the opt-in physics and frames whose bound total would not fit 32-bit
  * sample indices use the two-pass march regardless. */
 int vr_set_march_single_pass(vr_ctx* ctx, int enabled);
+/* layout of the last gather's sample buffer (diagnostic): out[0] = 1 single-pass layout with gaps / 0 compact two-pass
+ * layout, out[1] = extent of the buffer in samples (slots), out[2] = samples in it */
+int vr_get_march_info(vr_ctx* ctx, uint64_t out[3]);
 
 /* 1 (default): once two consecutive vr_render_frame calls had the same inputs, each call also generates the NEXT frame's
  * lights (same UBO, frameCount + 1) into a second light buffer on the auxiliary stream, underneath its evaluation kernel;
  * the next call adopts them if its inputs are what was assumed and regenerates otherwise. Results are identical either
  * way; 0 switches the prefetch off. */
 int vr_set_light_prefetch(vr_ctx* ctx, int enabled);
+
+/* 1 (default): the small kernels of the ray-segment evaluation (odd 8-sample segments, the exact kernel over leftovers and
+ * near-light segments) run on a second, low-priority stream next to the big segment kernel; 0: everything on the context's
+ * stream, one kernel after the other. Results are identical bit for bit (tests/test_gpu_parity.py). */
+int vr_set_eval_side_stream(vr_ctx* ctx, int enabled);
+
+/* ---- sample-parallel progressive rendering: G GPUs each render every G-th frame of a progressive run and
+ * keep a float SUM of their frame colours; one reduce(sum) and a division replace the sequential running average of
+ * shaders/point_compute_color.comp:99-105 (equal up to float reassociation; the rgba8 running average, re-quantised every
+ * frame, is sequential by construction and is not available in this mode).
+ *   vr_set_frame_step(step)       vr_render_frame advances frameCount by `step` instead of 1 (src/main.cpp:712): rank r
+ *                                 of G sets ubo.frameCount = r with vr_set_params and step = G, and renders frames
+ *                                 r+1, r+1+G, ... with exactly the light lists the sequential run generates for them
+ *   vr_set_accumulate_mode(SUM)   the float accumulator adds each frame colour instead of averaging; rgba8 is not touched;
+ *                                 clear with vr_clear_image (the implicit clear only happens at frameCount == 1)
+ *   vr_finish_sum(total)          after the sums were reduced into this context's accumulator (vr_get_device_buffers +
+ *                                 NCCL, or vr_group_render_progressive): accumulator = sum / total, rgba8 = UNORM8 of
+ *                                 that average, frameCount = total */
+enum { VR_ACCUM_AVERAGE = 0, VR_ACCUM_SUM = 1 };
+int vr_set_frame_step(vr_ctx* ctx, uint32_t step);
+int vr_set_accumulate_mode(vr_ctx* ctx, int mode);
+int vr_finish_sum(vr_ctx* ctx, uint32_t total_frames);
 
 /* nearest-voxel grid values at n index coordinates (ijk[3*n]) through the device traversal: what
  * pnanovdb_readaccessor_get_value_address + pnanovdb_read_float return (shaders/PNanoVDB_GLSL.h:2202-2231, :365-368),

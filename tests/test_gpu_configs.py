@@ -1,0 +1,153 @@
+"""BASELINE.json configurations C3, C4 and C5 as the north star states them, through the C ABI:
+
+  C4-A  Beam lights, 512^3 cloud, 1920x1080, maxLights 256 per frame, progressive accumulation over >= 16 frames
+        (shaders/beam_compute_color.comp:9-26, running average shaders/point_compute_color.comp:97-105): float
+        accumulator against the oracle on a pixel stride, rgba8 image within +-1 LSB, light lists bit-exact every frame
+  C5    Sphere lights + Path mode at 3840x2160 on the 1024^3-extent cloud (shaders/sphere_compute_color.comp:9-15,
+        shaders/path_compute_color.comp:33-128): sphere within tolerance on a stride, path bit-exact on a stride; this is
+        the one frame whose single-pass slot total exceeds 32-bit sample indices and takes the two-pass march
+  C3    Ray lights, 4096 lights, 256^3 cloud, 1080p: an 8-band tiled render equals the whole frame bit for bit
+
+Sizes: VR_TEST_C5_GRID=512 swaps the 1024^3 cloud (about 0.6 GB, tens of seconds to build on the host) for the 512^3 one;
+VR_TEST_C4_FRAMES sets the number of accumulated frames (default 16; the config's 64 takes about four times as long).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+REL_TOL, RMSE_TOL = 1e-3, 1e-4   # BASELINE.json: max relative error / RMSE on linear float radiance
+
+
+@pytest.fixture()
+def fresh(vr):
+    r = vr.VolumeRenderer(0)
+    yield r
+    r.close()
+
+
+def test_c4a_progressive_beam_accumulation(fresh, pyoracle, oracle, cloud):
+    r = fresh
+    W, H, ML, GX, stride = 1920, 1080, 256, 8, 24
+    frames = int(os.environ.get("VR_TEST_C4_FRAMES", "16"))
+    grid = cloud(512)
+    r.set_grid(grid)
+    r.resize(W, H)
+    r.ubo = r.default_ubo()
+    r.update_ubo(maxLights=ML)
+    r.set_light_gen_groups(GX, 1, 1)
+    r.reset_accumulation()
+    acc = np.zeros((H, W, 4), np.float32)
+    acc[..., 3] = 1.0
+    img8 = np.zeros((H, W, 4), np.uint8)
+    img8[..., 3] = 255
+    fc_o = np.zeros((H, W), np.float32)
+    sub = (slice(None, None, stride), slice(None, None, stride))
+    for frame in range(1, frames + 1):
+        r.draw_frame("beam")
+        ou = pyoracle.default_ubo(W, H, frameCount=frame, maxLights=ML)
+        ol, oc, oem, _ = oracle.light_gen(grid, ou, (GX, 1, 1), 0)
+        gl, gc, gem = r.read_lights()
+        assert (gc, gem) == (oc, oem) and gl.tobytes() == ol.tobytes(), f"frame {frame}: light list differs"
+        oracle.gather(grid, ou, "beam", ol, stride=stride, out=fc_o)
+        oracle.accumulate(fc_o, frame, acc, img8)
+        if frame in (1, 2, frames // 2, frames):
+            got = r.read_accum()
+            rel, rmse = rel_err(got[sub][..., 0], acc[sub][..., 0])
+            assert rel <= REL_TOL and rmse <= RMSE_TOL, (frame, rel, rmse)
+            d8 = np.abs(r.read_image_rgba8()[sub].astype(int) - img8[sub].astype(int)).max()
+            assert d8 <= 1, (frame, d8)
+    assert r.ubo.frameCount == frames
+    got = r.read_accum()
+    assert acc[sub][..., 0].mean() > 0.01 and (got[..., 3] == 1.0).all()
+    assert np.array_equal(got[..., 0], got[..., 1]) and np.array_equal(got[..., 0], got[..., 2])
+    cnt = r.counters()
+    assert cnt["light_count"] == ML and cnt["eval_lights"] > ML   # beams are expanded into sub-points
+
+
+def test_c5_sphere_and_path_at_4k(fresh, pyoracle, oracle, cloud):
+    r = fresh
+    W, H, ML, GX = 3840, 2160, 1000, 32
+    n = int(os.environ.get("VR_TEST_C5_GRID", "1024"))
+    grid = cloud(n)
+    assert grid.nbytes < (1 << 32), "the reference's GLSL addressing is 32-bit (shaders/PNanoVDB_GLSL.h:28-30)"
+    r.set_grid(grid)
+    r.resize(W, H)
+    r.ubo = r.default_ubo()
+    r.update_ubo(maxLights=ML)
+    r.set_light_gen_groups(GX, 1, 1)
+    # ---- sphere lights
+    r.reset_accumulation()
+    r.draw_frame("sphere")
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=ML)
+    ol, oc, oem, _ = oracle.light_gen(grid, ou, (GX, 1, 1), 0)
+    gl, gc, gem = r.read_lights()
+    assert (gc, gem) == (oc, oem) and gl.tobytes() == ol.tobytes()
+    info = r.march_info()
+    cnt = r.counters()
+    assert info["samples"] == cnt["S_eff"]
+    if n >= 1024:   # one slot per lattice step inside the box: more than 2^32 at this size -> compact two-pass layout
+        assert not info["single_pass"] and info["slots"] == info["samples"], info
+    else:
+        assert info["single_pass"] and info["slots"] >= cnt["S_ref"], info
+    stride = 48
+    sub = (slice(None, None, stride), slice(None, None, stride))
+    fc = r.read_frame_color()
+    ofc, ocnt = oracle.gather(grid, ou, "sphere", ol, stride=stride)
+    rel, rmse = rel_err(fc[sub], ofc[sub])
+    assert rel <= REL_TOL and rmse <= RMSE_TOL, (rel, rmse)
+    assert ofc[sub].mean() > 0.01
+    # ---- path mode, frames 1 and 2 (the RNG seed is pixel * frameCount, shaders/path_compute_color.comp:36-37): bit-exact
+    stride = 16
+    sub = (slice(None, None, stride), slice(None, None, stride))
+    r.reset_accumulation()
+    acc = np.zeros((H, W, 4), np.float32)
+    acc[..., 3] = 1.0
+    for frame in (1, 2):
+        r.draw_frame("path")
+        ou = pyoracle.default_ubo(W, H, frameCount=frame, maxLights=ML)
+        ofc, _ = oracle.gather(grid, ou, "path", np.zeros(0, pyoracle.LIGHT_DTYPE), stride=stride)
+        fc = r.read_frame_color()
+        assert np.array_equal(fc[sub], ofc[sub]), f"path frame {frame}"
+        oracle.accumulate(ofc, frame, acc, None, path_mode=True)
+    assert ofc[sub].mean() > 1e-3
+    assert np.array_equal(r.read_accum()[sub][..., 0], acc[sub][..., 0])
+
+
+def test_c3_eight_band_tiled_render_equals_whole_frame(fresh, pyoracle, oracle, cloud):
+    from volumerenderer_b200.tiles import balanced_row_bands, band_tile
+    r = fresh
+    W, H, ML, GX = 1920, 1080, 4096, 128
+    grid = cloud(256)
+    r.set_grid(grid)
+    r.resize(W, H)
+    r.ubo = r.default_ubo()
+    r.update_ubo(maxLights=ML, frameCount=1)
+    r.reset_lights()
+    r.dispatch_light_gen("ray", (GX, 1, 1))
+    ou = pyoracle.default_ubo(W, H, frameCount=1, maxLights=ML)
+    ol, oc, oem, _ = oracle.light_gen(grid, ou, (GX, 1, 1), 0)
+    gl, gc, gem = r.read_lights()
+    assert gc == oc == ML and gem == oem and gl.tobytes() == ol.tobytes()
+    r.clear_image()
+    r.dispatch_compute_color("ray")
+    full = (r.read_frame_color(), r.read_accum(), r.read_image_rgba8())
+    cnt = r.counters()
+    assert cnt["eval_lights"] > 10 * ML       # about twelve sub-points per ray light at lightRayStepSize 0.3
+    bands = balanced_row_bands(r.row_sample_counts(), 8)
+    assert len(bands) == 8 and sum(h for _, h in bands) == H
+    r.clear_image()
+    for b in bands:
+        r.dispatch_compute_color("ray", band_tile(b, W))
+    tiled = (r.read_frame_color(), r.read_accum(), r.read_image_rgba8())
+    for a, b in zip(full, tiled):
+        assert np.array_equal(a, b)
+    # and the whole frame is the oracle's within the tolerance (pixel stride: the CPU needs seconds per thousand pixels)
+    stride = 60
+    sub = (slice(None, None, stride), slice(None, None, stride))
+    ofc, _ = oracle.gather(grid, ou, "ray", ol, stride=stride)
+    rel, rmse = rel_err(full[0][sub], ofc[sub])
+    assert rel <= REL_TOL and rmse <= RMSE_TOL, (rel, rmse)

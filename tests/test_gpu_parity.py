@@ -371,7 +371,9 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo, cam
     renderer.dispatch_compute_color(algo, (0, 0, W, 40))
     renderer.dispatch_compute_color(algo, (0, 40, W, H - 40))
     assert np.array_equal(renderer.read_frame_color(), res[8])
-    # a light within the near distance of the camera plane: no bounded pixel footprint, everything goes the exact way
+    # a light within the near distance of the camera plane has no bounded pixel footprint on that side: the flag kernel
+    # clamps the near plane and tests the tile's pixels exactly, so only segments that really come near are handed over
+    # (here none: the cloud is far from that light) and the frame still matches the exact kernel
     cam = np.zeros(1, pyoracle.LIGHT_DTYPE)
     cam["to"] = cam["from"] = np.float32(renderer.ubo.cameraPos[:]) + np.float32([0.3, -0.2, 0.1])
     cam["intensity"] = 1.0
@@ -379,6 +381,22 @@ def test_segment_kernel_near_lights(renderer, pyoracle, oracle, cloud, algo, cam
     for variant in (2, 8):
         renderer.set_eval_variant(variant)
         renderer.write_lights(lights2)
+        renderer.clear_image()
+        renderer.dispatch_compute_color("point")
+        res[variant] = renderer.read_frame_color()
+    seg = renderer.eval_segment_counts()
+    assert seg["exact"] < seg["segments"] * 8 + seg["leftovers"], seg
+    rel, rmse = rel_err(res[8], res[2])
+    assert rel <= 1e-4 and rmse <= 1e-6, (rel, rmse)
+    # an absurdly distant light (products of squared distances would leave FP32): everything goes the exact way, and the
+    # results are the exact kernel's bit for bit
+    far = np.zeros(1, pyoracle.LIGHT_DTYPE)
+    far["to"] = far["from"] = np.float32([1.0e6, 2.0e5, 3.0e5])
+    far["intensity"] = 1.0e9
+    lights3 = np.concatenate([lights[:50], far])
+    for variant in (2, 8):
+        renderer.set_eval_variant(variant)
+        renderer.write_lights(lights3)
         renderer.clear_image()
         renderer.dispatch_compute_color("point")
         res[variant] = renderer.read_frame_color()
@@ -425,7 +443,22 @@ def test_argument_errors(renderer, vr, cloud):
     with pytest.raises(vr.VrError) as e:
         renderer.dispatch_compute_color("point")
     assert e.value.code == 1 and "too small" in str(e.value)
+    # ... and so would the photon walk of light generation: vr_dispatch_light_gen and vr_render_frame refuse it before
+    # anything is enqueued, and the rejected frame leaves frameCount where it was
+    with pytest.raises(vr.VrError) as e:
+        renderer.dispatch_light_gen("point")
+    assert e.value.code == 1 and "too small" in str(e.value)
+    fc0 = renderer.ubo.frameCount
+    with pytest.raises(vr.VrError) as e:
+        renderer.draw_frame("point")
+    assert e.value.code == 1 and renderer.ubo.frameCount == fc0
+    with pytest.raises(vr.VrError):
+        renderer.draw_frame("point", (0, 0, 64, 64))   # tile outside the image: rejected up front as well
+    assert renderer.ubo.frameCount == fc0
     renderer.update_ubo(rayMarchingStepSize=1.0)
+    renderer.draw_frame("point")                        # the context is still usable
+    renderer.sync()
+    assert renderer.ubo.frameCount == fc0 + 1
     with pytest.raises(vr.VrError) as e:
         renderer.set_grid(np.zeros(4096, np.uint8))
     assert e.value.code == 3
@@ -538,3 +571,82 @@ def test_single_pass_march_equals_two_pass(vr, cloud, algo):
         assert two[0][3]["S_eff"] > 10000 and len(two[0][2]) == two[0][3]["S_eff"]
     finally:
         r.close()
+
+
+@pytest.mark.parametrize("algo", ["point", "beam"])
+def test_eval_side_stream_is_transparent(vr, cloud, algo):
+    """vr_set_eval_side_stream: the small evaluation kernels on a second stream or behind the big one: same bits."""
+    grid = cloud(64)
+    out = {}
+    for side in (1, 0):
+        with vr.VolumeRenderer(0) as r:
+            _setup(r, grid, 160, 96, maxLights=120)
+            r.set_eval_side_stream(side)
+            r.set_light_gen_groups(8, 1, 1)
+            for _ in range(3):
+                r.draw_frame(algo)
+            out[side] = (r.read_accum(), r.read_image_rgba8(), r.eval_segment_counts())
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1]) and out[0][2] == out[1][2]
+
+
+def test_tile_readback_async(renderer, cloud):
+    """vr_read_accum_f32_tile_async: the rows (or rectangle) a GPU rendered, placed into the caller's full image."""
+    W, H = 96, 64
+    _setup(renderer, cloud(64), W, H, maxLights=64)
+    renderer.set_light_gen_groups(4, 1, 1)
+    renderer.reset_accumulation()
+    renderer.draw_frame("point")
+    want = renderer.read_accum()
+    img = np.full((H, W, 4), -1.0, np.float32)
+    renderer.read_accum_tile_async((0, 16, W, 24), img)
+    renderer.draw_frame("point")                       # overwrites the accumulator while the copy is in flight
+    renderer.read_wait()
+    assert np.array_equal(img[16:40], want[16:40]) and (img[:16] == -1.0).all() and (img[40:] == -1.0).all()
+    img[:] = -1.0
+    want = renderer.read_accum()
+    renderer.read_accum_tile_async((8, 4, 40, 10), img)
+    renderer.read_wait()
+    assert np.array_equal(img[4:14, 8:48], want[4:14, 8:48])
+    img[4:14, 8:48] = -1.0
+    assert (img == -1.0).all()
+    renderer.set_light_gen_groups(1, 1, 1)
+
+
+def test_sample_parallel_progressive_sum(vr, cloud):
+    """SURVEY 8e, sample-parallel mode: G contexts render every G-th frame of a progressive run (vr_set_frame_step) into
+    float SUM accumulators (vr_set_accumulate_mode); sum of the sums / frames equals the sequential running average of
+    shaders/point_compute_color.comp:99-105 up to float reassociation (bound: frames * 2^-24 relative), with exactly
+    the light lists of the sequential run."""
+    grid = cloud(64)
+    W, H, G, frames = 96, 64, 3, 12
+    with vr.VolumeRenderer(0) as seq:
+        _setup(seq, grid, W, H, maxLights=80)
+        seq.set_light_gen_groups(6, 1, 1)
+        lists = []
+        for f in range(frames):
+            seq.draw_frame("point")
+            lists.append(seq.read_lights()[0].tobytes())
+        want = seq.read_accum()
+    total = np.zeros((H, W, 4), np.float64)
+    for rank in range(G):
+        with vr.VolumeRenderer(0) as r:
+            _setup(r, grid, W, H, maxLights=80, frameCount=rank)
+            r.set_light_gen_groups(6, 1, 1)
+            r.set_frame_step(G)
+            r.set_accumulate_mode("sum")
+            r.clear_image()
+            for k in range(frames // G):
+                r.draw_frame("point")
+                assert r.ubo.frameCount == rank + 1 + k * G
+                assert r.read_lights()[0].tobytes() == lists[rank + k * G]
+            part = r.read_accum()
+            total += part
+            if rank == 0:   # finish on one context: sum / frames, rgba8 from the average
+                r.finish_sum(frames // G)
+                avg = r.read_accum()
+                assert np.allclose(avg[..., :3], part[..., :3] / np.float32(frames // G), rtol=1e-6, atol=0)
+                assert np.array_equal(r.read_image_rgba8()[..., 0], np.rint(np.clip(avg[..., 0], 0, 1) * 255).astype(np.uint8))
+                assert r.ubo.frameCount == frames // G
+    got = (total[..., 0] / frames).astype(np.float32)
+    rel, rmse = rel_err(got, want[..., 0])
+    assert rel <= frames * 2.0 ** -22 and want[..., 0].max() > 0.01, (rel, rmse)

@@ -65,6 +65,7 @@ EXPORTS = [
     "vr_set_stream", "vr_set_grid_device", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
     "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
     "vr_io_last_error",
+    "vr_read_accum_f32_tile_async", "vr_set_eval_side_stream", "vr_set_frame_step", "vr_set_accumulate_mode", "vr_finish_sum", "vr_get_march_info",
 ]
 
 _lib = None
@@ -154,5 +155,11 @@ def load():
     L.vr_snapshot_save.argtypes = [P, C.c_char_p]
     L.vr_snapshot_load.argtypes = [P, C.c_char_p]
     L.vr_io_last_error.restype = C.c_char_p
+    L.vr_read_accum_f32_tile_async.argtypes = [P, C.POINTER(VrTile), P, U64]
+    L.vr_set_eval_side_stream.argtypes = [P, I]
+    L.vr_set_frame_step.argtypes = [P, U32]
+    L.vr_set_accumulate_mode.argtypes = [P, I]
+    L.vr_finish_sum.argtypes = [P, U32]
+    L.vr_get_march_info.argtypes = [P, C.POINTER(U64)]
     _lib = L
     return L

@@ -182,6 +182,15 @@ struct vr_ctx {
     uint64_t cached_samples = 0;  // length of the sample buffer's address range (= sample count when the buffer is compact)
     uint64_t cached_real = 0;     // number of samples in it
     bool march_single = true;     // vr_set_march_single_pass
+    uint32_t frame_step = 1;      // vr_set_frame_step: frameCount advances by this much per vr_render_frame
+    int accumulate_mode = 0;      // vr_set_accumulate_mode: 0 = running average (the reference), 1 = float sum
+    bool eval_side_stream = true; // vr_set_eval_side_stream
+    // what the current light list was generated from (vr_dispatch_light_gen / vr_render_frame): bounds the list length and
+    // the ray/beam segment lengths without reading the device, whatever vr_set_params did since
+    uint32_t lights_bound = 0;        // upper bound of counter->lightCount
+    float gen_light_pos[3] = {0, 0, 0};
+    int gen_pos_state = 0;            // 0: nothing generated since the counter reset, 1: every generation used gen_light_pos,
+                                      // 2: unknown end points (lights written by the caller, or several source positions)
     MarchKey gaps_refused;        // rays whose bound total does not fit 32-bit sample indices: two-pass march
     BoundKey bound_key;           // px_offsets hold the slots of these rays (single-pass layout), bound_extent their total
     uint64_t bound_extent = 0;
@@ -299,7 +308,7 @@ int open_timing_set(vr_ctx* c, vr_ctx::TimingSet** out) {
 // end point is the light source or a scatter position inside the root bbox (light_gen.comp:74-84), hence no segment is
 // longer than the diagonal of the world-space box around both. 0 = no usable bound.
 uint64_t expand_bound(const vr_ctx* c) {
-    if (c->lights_external) return 0;
+    if (c->gen_pos_state != 1) return 0;
     double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
     const VrGridDev& g = c->gdev;
     for (int corner = 0; corner < 8; corner++) {
@@ -311,15 +320,30 @@ uint64_t expand_bound(const vr_ctx* c) {
             lo[a] = w < lo[a] ? w : lo[a], hi[a] = w > hi[a] ? w : hi[a];
         }
     }
-    for (int a = 0; a < 3; a++) {
-        const double w = c->ubo.lightSourceWorldPos[a];
+    for (int a = 0; a < 3; a++) {  // the source position the list was generated with, not the current UBO's
+        const double w = c->gen_light_pos[a];
         lo[a] = w < lo[a] ? w : lo[a], hi[a] = w > hi[a] ? w : hi[a];
     }
     const double diag = sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1]) + (hi[2] - lo[2]) * (hi[2] - lo[2]));
     const double steps = floor(diag * 1.001 / (double)c->ubo.lightRayStepSize) + 2.0;
-    const double bound = steps * (double)c->ubo.maxLights;
+    const double bound = steps * (double)(c->lights_bound < c->light_capacity ? c->lights_bound : c->light_capacity);
     if (!(bound == bound) || bound > (double)(1ull << 26)) return 0;
     return (uint64_t)bound;
+}
+
+// bookkeeping for a light generation with parameters `u` into the CURRENT (lights, counter) pair: the shader appends at
+// most up to index maxLights - 1 and stores lightCount = maxLights beyond (light_gen.comp:79-87), so the counter never
+// exceeds the largest maxLights used since its reset
+void note_generation(vr_ctx* c, const vr_ubo& u, vr_algo algo) {
+    if (algo == VR_ALGO_PATH) return;
+    if (u.maxLights > c->lights_bound) c->lights_bound = u.maxLights;
+    if (c->gen_pos_state == 0) {
+        memcpy(c->gen_light_pos, u.lightSourceWorldPos, sizeof(c->gen_light_pos));
+        c->gen_pos_state = 1;
+    } else if (c->gen_pos_state == 1 && memcmp(c->gen_light_pos, u.lightSourceWorldPos, sizeof(c->gen_light_pos)) != 0) {
+        c->gen_pos_state = 2;
+    }
+    c->lights_external = false;
 }
 
 // light generation on stream `st` (shaders/light_gen.comp) with parameters `u` into (lights, counter), timed into `t`
@@ -746,6 +770,8 @@ int vr_reset_lights(vr_ctx* c) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaMemsetAsync(c->counter, 0, sizeof(VrLightCounter), c->stream));
+    c->lights_bound = 0;
+    c->gen_pos_state = 0;
     return VR_OK;
 }
 
@@ -757,6 +783,8 @@ int vr_write_lights(vr_ctx* c, const vr_ray_light* lights, uint32_t count) {
     if (count) VR_CUDA(c, cudaMemcpyAsync(c->lights.p, lights, (size_t)count * sizeof(vr_ray_light), cudaMemcpyHostToDevice, c->stream));
     c->lights_external = true;
     c->external_count = count;
+    c->lights_bound = count;
+    c->gen_pos_state = 2;  // arbitrary end points: no bound on the ray/beam segment lengths
     VrLightCounter h{count, 0u, (unsigned long long)count};
     VR_CUDA(c, cudaMemcpyAsync(c->counter, &h, sizeof(h), cudaMemcpyHostToDevice, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -771,6 +799,30 @@ int vr_clear_image(vr_ctx* c) {
     return check_stream(c);
 }
 
+// `t += step` stops advancing once step < ulp(t)/2, i.e. beyond ~1.6e7 steps per ray: the shader loops `while (t < tmax ...)`
+// (light_gen.comp:51, point_compute_color.comp:68) and ours would then never end. A ray that starts at `origin_world`
+// never has tmax beyond min(rayMaxDistance, distance to the far corner of the grid's box) (intersectAABB clips it once
+// and the light-generation walk never recomputes it, light_gen.comp:38-49), so that distance over the step bounds the
+// step count of the camera march, of the photon walk (its t restarts at 0 on every scatter) and of path mode alike.
+static int check_step_count(vr_ctx* c, const float origin_world[3], const char* what) {
+    const VrGridDev& g = c->gdev;
+    if (!(c->ubo.rayMarchingStepSize > 0.0f)) return fail(c, VR_E_ARG, "rayMarchingStepSize must be > 0 (the shader loop never ends at 0, src/main.cpp:684)");
+    const double sx = origin_world[0] - g.vec[0], sy = origin_world[1] - g.vec[1], sz = origin_world[2] - g.vec[2];
+    double far2 = 0.0;
+    for (int a = 0; a < 3; a++) {
+        const double ci = sx * g.inv[3 * a] + sy * g.inv[3 * a + 1] + sz * g.inv[3 * a + 2];
+        const double lo = fabs(ci - (double)g.bmin[a]), hi = fabs((double)g.bmax[a] + 1.0 - ci);
+        far2 += (lo > hi ? lo : hi) * (lo > hi ? lo : hi);
+    }
+    double reach = sqrt(far2);
+    const double maxd = (double)c->ubo.rayMaxDistance;
+    if (maxd == maxd && maxd < reach) reach = maxd > 0.0 ? maxd : 0.0;
+    if (!(reach / (double)c->ubo.rayMarchingStepSize <= 8.0e6))
+        return fail(c, VR_E_ARG, "rayMarchingStepSize %g is too small for this grid and %s: more than 8e6 steps per ray, the FP32 march would stop advancing",
+                    (double)c->ubo.rayMarchingStepSize, what);
+    return VR_OK;
+}
+
 static int check_light_gen_args(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz) {
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if ((int)algo < 0 || (int)algo > 4) return fail(c, VR_E_ARG, "unknown algorithm %d", (int)algo);
@@ -778,7 +830,18 @@ static int check_light_gen_args(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t g
     const uint64_t nphot = (uint64_t)gx * 4 * gy * 4 * gz;
     if (nphot > (1ull << 28)) return fail(c, VR_E_ARG, "%llu photons exceed the supported dispatch size", (unsigned long long)nphot);
     if (c->ubo.maxLights > c->light_capacity) return fail(c, VR_E_CAPACITY, "maxLights %u exceeds capacity %u", c->ubo.maxLights, c->light_capacity);
+    if (algo != VR_ALGO_PATH) return check_step_count(c, c->ubo.lightSourceWorldPos, "light source");  // path_light_gen.comp walks nothing
     return VR_OK;
+}
+
+// everything vr_dispatch_compute_color rejects that does not depend on the tile: checked before anything is enqueued
+static int check_gather_args(vr_ctx* c, vr_algo algo) {
+    if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if ((int)algo < 0 || (int)algo > 4) return fail(c, VR_E_ARG, "unknown algorithm %d", (int)algo);
+    if ((algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM) && !(c->ubo.lightRayStepSize > 0.0f))
+        return fail(c, VR_E_ARG, "lightRayStepSize must be > 0 for ray/beam (uint(len/0) is undefined, ray_compute_color.comp:15)");
+    return check_step_count(c, c->ubo.cameraPos, "camera");
 }
 
 int vr_dispatch_light_gen(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant) {
@@ -795,35 +858,16 @@ int vr_dispatch_light_gen(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t gy, uin
     }
     rc = enqueue_light_gen(c, c->stream, t, c->ubo, algo, gx, gy, gz, variant, c->lights.p, c->counter);
     if (rc != VR_OK) return rc;
-    if (algo != VR_ALGO_PATH) c->lights_external = false;
+    note_generation(c, c->ubo, algo);
     return check_stream(c);
 }
 
 int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
     if (!c) return VR_E_ARG;
-    if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
-    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
-    if ((int)algo < 0 || (int)algo > 4) return fail(c, VR_E_ARG, "unknown algorithm %d", (int)algo);
-    if ((algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM) && !(c->ubo.lightRayStepSize > 0.0f))
-        return fail(c, VR_E_ARG, "lightRayStepSize must be > 0 for ray/beam (uint(len/0) is undefined, ray_compute_color.comp:15)");
-    if (!(c->ubo.rayMarchingStepSize > 0.0f)) return fail(c, VR_E_ARG, "rayMarchingStepSize must be > 0");
-    {
-        // t += step stops advancing once step < ulp(t)/2, i.e. beyond ~1.6e7 steps per ray: the shader loop (and ours)
-        // would never end. The longest ray inside the grid's box runs from the camera to the box's far corner.
-        const VrGridDev& g = c->gdev;
-        const double sx = c->ubo.cameraPos[0] - g.vec[0], sy = c->ubo.cameraPos[1] - g.vec[1], sz = c->ubo.cameraPos[2] - g.vec[2];
-        double far2 = 0.0;
-        for (int a = 0; a < 3; a++) {
-            const double ci = sx * g.inv[3 * a] + sy * g.inv[3 * a + 1] + sz * g.inv[3 * a + 2];
-            const double lo = fabs(ci - (double)g.bmin[a]), hi = fabs((double)g.bmax[a] + 1.0 - ci);
-            far2 += (lo > hi ? lo : hi) * (lo > hi ? lo : hi);
-        }
-        if (sqrt(far2) / (double)c->ubo.rayMarchingStepSize > 8.0e6)
-            return fail(c, VR_E_ARG, "rayMarchingStepSize %g is too small for this grid and camera: more than 8e6 steps per ray, the FP32 march would stop advancing",
-                        (double)c->ubo.rayMarchingStepSize);
-    }
+    int rc = check_gather_args(c, algo);
+    if (rc != VR_OK) return rc;
     vr_tile tile;
-    int rc = validate_tile(c, tile_or_null, &tile);
+    rc = validate_tile(c, tile_or_null, &tile);
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
     cudaStream_t st = c->stream;
@@ -863,7 +907,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             if (n < 65536.0) nmax = (uint32_t)n;
         }
         if (nmax) VR_CUDA(c, c->path_tab.reserve((uint64_t)27 * (nmax + 1)));
-        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->fc_out, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax);
+        vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->fc_out, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax, c->accumulate_mode);
         cudaEventRecord(t->ev[5], st);
         cudaEventRecord(t->ev[6], st);
         t->pending = true, t->open = false;
@@ -969,7 +1013,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     }
     const bool expand = (algo == VR_ALGO_RAY || algo == VR_ALGO_BEAM);
     // lightCount lives on the device: launches are sized by maxLights (the shader's cap), kernels read the counter
-    uint32_t nl_launch = c->lights_external ? c->external_count : c->ubo.maxLights;
+    // (by the bound recorded when the list was generated: the shader loops over lightCount whatever maxLights is now)
+    uint32_t nl_launch = c->lights_bound;
     if (nl_launch > c->light_capacity) nl_launch = c->light_capacity;
     VR_CUDA(c, cudaMemsetAsync(c->expand_overflow, 0, sizeof(uint32_t), st));
     uint64_t eval_list_cap = nl_launch;  // upper bound of the evaluation list's length (the length itself lives on the device)
@@ -1009,7 +1054,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         if (rc != VR_OK) return rc;
         nt->open = true;
         vr_ubo nu = c->ubo;
-        nu.frameCount += 1;
+        nu.frameCount += c->frame_step;
         VR_CUDA(c, cudaEventRecord(c->ev_fork, st));
         VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
         VR_CUDA(c, cudaMemsetAsync(c->counter_alt, 0, sizeof(VrLightCounter), c->aux_stream));
@@ -1060,8 +1105,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             rho *= sqrtf(1000.0f / (float)eval_list_cap);
             if (rho < 0.1f) rho = 0.1f;
         }
-        static const bool seg_side = !(getenv("VR_SEG_SIDE") && atoi(getenv("VR_SEG_SIDE")) == 0);  // experiments: 0 = one stream
-        vrk_eval_point_seg(st, seg_side ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nreal, npix, c->px_counts.p, c->px_offsets.p, sl,
+        vrk_eval_point_seg(st, c->eval_side_stream ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nreal, npix, c->px_counts.p, c->px_offsets.p, sl,
                            c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)
@@ -1070,7 +1114,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         vrk_eval_point_packed(st, c->eval_variant == 8 ? 2 : c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1,
                               c->contrib.p, c->eval_redo);
     cudaEventRecord(t->ev[5], st);
-    vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8);
+    vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8, c->accumulate_mode);
     cudaEventRecord(t->ev[6], st);
     t->pending = true, t->open = false;
     return check_stream(c);
@@ -1088,10 +1132,19 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
     if (!c) return VR_E_ARG;
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    // every parameter check of both dispatches runs before anything is enqueued or frameCount changes: a rejected call
+    // leaves the context as it was
     int rc = check_light_gen_args(c, algo, c->lg_groups[0], c->lg_groups[1], c->lg_groups[2]);
     if (rc != VR_OK) return rc;
+    rc = check_gather_args(c, algo);
+    if (rc != VR_OK) return rc;
+    {
+        vr_tile probe;
+        rc = validate_tile(c, tile_or_null, &probe);
+        if (rc != VR_OK) return rc;
+    }
     VR_CUDA(c, cudaSetDevice(c->device));
-    c->ubo.frameCount += 1;  // src/main.cpp:712
+    c->ubo.frameCount += c->frame_step;  // src/main.cpp:712 (frame_step = 1 unless vr_set_frame_step)
     vr_ctx::TimingSet* t = nullptr;
     rc = open_timing_set(c, &t);
     if (rc != VR_OK) return rc;
@@ -1105,7 +1158,8 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
         // was evaluated: counter reset (:722-728) and light generation (:811-814) already happened, into the other pair
         std::swap(c->lights, c->lights_alt);
         std::swap(c->counter, c->counter_alt);
-        c->lights_external = false;
+        c->lights_bound = 0, c->gen_pos_state = 0;  // the other pair's counter was reset before its generation
+        note_generation(c, c->spec.ubo, algo);
         c->lg_in_flight = true;  // the gather joins on ev_lg_done
     } else {
         if (c->spec.valid) VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_lg_done, 0));  // a stale prefetch must drain first
@@ -1125,16 +1179,22 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
         VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
         rc = enqueue_light_gen(c, c->aux_stream, t, c->ubo, algo, gr[0], gr[1], gr[2], variant, c->lights.p, c->counter);
         if (rc != VR_OK) return rc;
-        if (algo != VR_ALGO_PATH) c->lights_external = false;
+        note_generation(c, c->ubo, algo);
         VR_CUDA(c, cudaEventRecord(c->ev_lg_done, c->aux_stream));
         c->lg_in_flight = true;
     }
     // steady state (same inputs as the previous frame): prefetch the next frame's lights once this frame's list is built
     c->prefetch_next = c->lg_prefetch && algo != VR_ALGO_PATH && c->prev_frame_valid && c->prev_frame_grid_gen == c->grid_gen &&
-                       same_frame_inputs(c->prev_frame_ubo, c->ubo) && c->prev_frame_ubo.frameCount + 1 == c->ubo.frameCount;
+                       same_frame_inputs(c->prev_frame_ubo, c->ubo) && c->prev_frame_ubo.frameCount + c->frame_step == c->ubo.frameCount;
     c->prev_frame_ubo = c->ubo, c->prev_frame_grid_gen = c->grid_gen, c->prev_frame_valid = true;
     rc = vr_dispatch_compute_color(c, algo, tile_or_null);
     c->prefetch_next = false;
+    if (rc != VR_OK) {
+        // the frame did not happen (a CUDA or allocation failure past the argument checks): frameCount goes back, and the
+        // steady-state bookkeeping starts over so that no prefetched light list is adopted for a frame that never ran
+        c->ubo.frameCount -= c->frame_step;
+        c->prev_frame_valid = false;
+    }
     return rc;
 }
 
@@ -1213,6 +1273,29 @@ int vr_read_accum_f32_async(vr_ctx* c, float* out) {
     c->copy_pending = true;
     return VR_OK;
 }
+/* The same for one tile (multi-GPU: every GPU returns the rows it rendered over its own PCIe link). `out` addresses the
+ * tile's first pixel in the caller's image, rows `out_pitch_bytes` apart. One read-back in flight per context. */
+int vr_read_accum_f32_tile_async(vr_ctx* c, const vr_tile* tile_or_null, float* out, uint64_t out_pitch_bytes) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (!out) return fail(c, VR_E_ARG, "NULL output buffer");
+    vr_tile tile;
+    int rc = validate_tile(c, tile_or_null, &tile);
+    if (rc != VR_OK) return rc;
+    if (out_pitch_bytes < (uint64_t)tile.w * 16) return fail(c, VR_E_ARG, "row pitch %llu is below the tile's row size", (unsigned long long)out_pitch_bytes);
+    VR_CUDA(c, cudaSetDevice(c->device));
+    if (c->copy_pending) VR_CUDA(c, cudaEventSynchronize(c->ev_copy_done));
+    const size_t row = (size_t)tile.w * 16;
+    VR_CUDA(c, c->accum_snapshot.reserve((uint64_t)tile.w * tile.h * 4));
+    const float4* src = c->accum + (size_t)tile.y0 * c->width + tile.x0;
+    VR_CUDA(c, cudaMemcpy2DAsync(c->accum_snapshot.p, row, src, (size_t)c->width * 16, row, tile.h, cudaMemcpyDeviceToDevice, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_copy_ready, c->stream));
+    VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_copy_ready, 0));
+    VR_CUDA(c, cudaMemcpy2DAsync(out, (size_t)out_pitch_bytes, c->accum_snapshot.p, row, row, tile.h, cudaMemcpyDeviceToHost, c->copy_stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_copy_done, c->copy_stream));
+    c->copy_pending = true;
+    return VR_OK;
+}
 int vr_read_wait(vr_ctx* c) {
     if (!c) return VR_E_ARG;
     if (c->copy_pending) {
@@ -1286,7 +1369,7 @@ int vr_accumulate_frame_color(vr_ctx* c, const vr_tile* tile_or_null) {
     int rc = validate_tile(c, tile_or_null, &tile);
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
-    vrk_accumulate(c->stream, c->ubo, tile, c->frame_color, c->accum, c->rgba8);
+    vrk_accumulate(c->stream, c->ubo, tile, c->frame_color, c->accum, c->rgba8, c->accumulate_mode);
     return check_stream(c);
 }
 
@@ -1519,6 +1602,14 @@ int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {
     return rc;
 }
 
+int vr_get_march_info(vr_ctx* c, uint64_t out[3]) {
+    if (!c || !out) return VR_E_ARG;
+    out[0] = (c->march_key.valid && c->march_key.gaps) ? 1u : 0u;
+    out[1] = c->cached_samples;
+    out[2] = c->cached_real;
+    return VR_OK;
+}
+
 int vr_set_march_single_pass(vr_ctx* c, int enabled) {
     if (!c) return VR_E_ARG;
     c->march_single = enabled != 0;
@@ -1533,6 +1624,37 @@ int vr_get_eval_redo_count(vr_ctx* c, uint64_t* ctas) {
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     *ctas = h;
     return VR_OK;
+}
+
+int vr_set_eval_side_stream(vr_ctx* c, int enabled) {
+    if (!c) return VR_E_ARG;
+    c->eval_side_stream = enabled != 0;
+    return VR_OK;
+}
+
+int vr_set_frame_step(vr_ctx* c, uint32_t step) {
+    if (!c) return VR_E_ARG;
+    if (step == 0 || step > (1u << 20)) return fail(c, VR_E_ARG, "frame step %u out of range", step);
+    c->frame_step = step;
+    c->prev_frame_valid = false;  // the prefetched list (if any) was generated for frameCount + the old step
+    return VR_OK;
+}
+
+int vr_set_accumulate_mode(vr_ctx* c, int mode) {
+    if (!c) return VR_E_ARG;
+    if (mode != VR_ACCUM_AVERAGE && mode != VR_ACCUM_SUM) return fail(c, VR_E_ARG, "unknown accumulate mode %d", mode);
+    c->accumulate_mode = mode;
+    return VR_OK;
+}
+
+int vr_finish_sum(vr_ctx* c, uint32_t total_frames) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (total_frames == 0) return fail(c, VR_E_ARG, "vr_finish_sum: total_frames must be >= 1");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    vrk_finish_sum(c->stream, c->accum, c->rgba8, (uint64_t)c->width * c->height, (float)total_frames);
+    c->ubo.frameCount = total_frames;
+    return check_stream(c);
 }
 
 int vr_set_light_prefetch(vr_ctx* c, int enabled) {

@@ -95,11 +95,14 @@ int list_grids(const std::vector<uint8_t>& file, std::vector<FoundGrid>& out, co
                 }
                 const uint64_t fsz = rd<uint64_t>(p, q + 8);
                 const uint32_t name = rd<uint32_t>(p, q + 136);
-                if (name > 4096 || fsz > n) ok = false;
+                if (name > 4096 || fsz > n || total > n - fsz) {  // sums of 64-bit file fields must not wrap
+                    ok = false;
+                    break;
+                }
                 total += fsz;
                 q += kFileMeta + name;
             }
-            as_file = ok && q + total <= n;
+            as_file = ok && q <= n && total <= n - q;
         }
         if (as_file) {
             const uint16_t count = rd<uint16_t>(p, pos + 12), codec = rd<uint16_t>(p, pos + 14);
@@ -116,24 +119,25 @@ int list_grids(const std::vector<uint8_t>& file, std::vector<FoundGrid>& out, co
                 const uint32_t name = rd<uint32_t>(p, q + 136);
                 if (rd<uint16_t>(p, q + 168) != 0 || fsz != fg.size)
                     return io_fail(VR_E_BADGRID, "%s: compressed grid inside the file is not supported", path);
-                if (q + kFileMeta + name > n) return io_fail(VR_E_BADGRID, "%s: truncated grid name", path);
+                if (name > n || q + kFileMeta > n - name) return io_fail(VR_E_BADGRID, "%s: truncated grid name", path);
                 if (name) fg.name.assign((const char*)p + q + kFileMeta, strnlen((const char*)p + q + kFileMeta, name));
                 q += kFileMeta + name;
                 seg.push_back(fg);
             }
             for (auto& fg : seg) {
-                if (q + fg.size > n) return io_fail(VR_E_BADGRID, "%s: truncated grid data", path);
+                if (q > n || fg.size > n - q) return io_fail(VR_E_BADGRID, "%s: truncated grid data", path);
                 fg.offset = q;
                 q += fg.size;
                 out.push_back(fg);
             }
+            if (q <= pos) return io_fail(VR_E_BADGRID, "%s: malformed segment", path);  // the scan must advance
             pos = q;
         } else if (plausible_raw_grid(p + pos, n - pos)) {
             FoundGrid fg;
             fg.offset = pos, fg.size = rd<uint64_t>(p, pos + 32), fg.type = rd<uint32_t>(p, pos + 636);
             fg.name.assign((const char*)p + pos + 40, strnlen((const char*)p + pos + 40, 256));
             out.push_back(fg);
-            pos += fg.size;
+            pos += fg.size;  // plausible_raw_grid: kGridData + 128 <= size <= n - pos, so this advances and cannot wrap
         } else {
             if (out.empty()) return io_fail(VR_E_BADGRID, "%s: not a NanoVDB file or raw grid buffer", path);
             break;  // trailing bytes after the last grid
@@ -294,13 +298,31 @@ int vr_snapshot_load(vr_ctx* ctx, const char* path) {
     FILE* f = fopen(path, "rb");
     if (!f) return io_fail(VR_E_ARG, "cannot read %s", path);
     VrSnapHeader hd{};
+    // the image limits of vr_resize apply before anything is sized from the header
     if (fread(&hd, sizeof(hd), 1, f) != 1 || memcmp(hd.magic, "VRSNAP01", 8) != 0 || hd.width == 0 || hd.height == 0 ||
-        hd.accum_bytes != (uint64_t)hd.width * hd.height * 16 || hd.rgba8_bytes != (uint64_t)hd.width * hd.height * 4) {
+        hd.width > 65536 || hd.height > 65536 || hd.accum_bytes != (uint64_t)hd.width * hd.height * 16 || hd.rgba8_bytes != (uint64_t)hd.width * hd.height * 4) {
         fclose(f);
         return io_fail(VR_E_ARG, "%s is not a libvr snapshot", path);
     }
-    std::vector<float> accum((size_t)hd.width * hd.height * 4);
-    std::vector<uint8_t> img((size_t)hd.width * hd.height * 4);
+    {   // the payload the header announces must be in the file before buffers are sized from it
+        const long at = ftell(f);
+        fseek(f, 0, SEEK_END);
+        const long end = ftell(f);
+        fseek(f, at, SEEK_SET);
+        if (at < 0 || end < at || (uint64_t)(end - at) < hd.accum_bytes + hd.rgba8_bytes) {
+            fclose(f);
+            return io_fail(VR_E_ARG, "%s: truncated snapshot", path);
+        }
+    }
+    std::vector<float> accum;
+    std::vector<uint8_t> img;
+    try {
+        accum.resize((size_t)hd.width * hd.height * 4);
+        img.resize((size_t)hd.width * hd.height * 4);
+    } catch (...) {
+        fclose(f);
+        return io_fail(VR_E_ARG, "%s: out of host memory for the snapshot (%llu pixels)", path, (unsigned long long)hd.width * hd.height);
+    }
     const bool ok = fread(accum.data(), 1, hd.accum_bytes, f) == hd.accum_bytes && fread(img.data(), 1, hd.rgba8_bytes, f) == hd.rgba8_bytes;
     fclose(f);
     if (!ok) return io_fail(VR_E_ARG, "%s: truncated snapshot", path);

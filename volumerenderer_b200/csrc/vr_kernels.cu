@@ -20,7 +20,6 @@
 // and uses MUFU.RCP; its results are within a few ulp per term (tolerance 1e-3 relative on the pixel, BASELINE.json).
 #include <cuda_runtime.h>
 #include <stdint.h>
-#include <stdlib.h>
 
 #include "vr_kernels.cuh"
 
@@ -881,9 +880,12 @@ __global__ void __launch_bounds__(256) k_build_segments(const uint32_t* __restri
 // rotation, point_compute_color.comp:23-33) that passes within rho of v = L - camera has a point q with |q - v| <= rho,
 // so its image-plane coordinates x = q.x/q.z, y = q.y/q.z lie in the box spanned by (v.x -+ rho)/(v.z -+ rho); the pixels
 // of that box are tested exactly (distance of the light from the ray, position of the foot point against the span of
-// each of the pixel's segments). rho already carries a safety margin; if a light's ball reaches the camera plane the
-// kernel gives up and flags everything (flag_all). Flags are what k_eval_seg reads to hand a segment to the exact kernel.
-__global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __restrict__ lights, const unsigned long long* __restrict__ nlights_dev,
+// each of the pixel's segments). rho already carries a safety margin. A light whose ball reaches the camera plane (the
+// camera sits inside or beside the medium) has no bounded box on that side: the near plane is clamped to a tiny positive
+// depth, the box then covers the tile in that direction and the exact per-pixel test decides. Only an absurdly distant
+// light makes the kernel give up and flag everything (flag_all). Flags are what k_eval_seg reads to hand a segment to
+// the exact kernel.
+__global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* __restrict__ lights, const unsigned long long* __restrict__ nlights_dev,
                                                             vr_ubo u, float tan_scale, vr_tile tile, const uint32_t* __restrict__ counts,
                                                             const unsigned long long* __restrict__ offsets,
                                                             const VrSample* __restrict__ samples, VrSegLists sl, float rho) {
@@ -896,13 +898,10 @@ __global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __
         if (threadIdx.x == 0) *sl.flag_all = 1u;
         continue;
     }
-    if (vz + rho < 0.0f) continue;  // behind the camera plane by more than rho: no forward ray comes near
-    if (vz - rho <= 1.0e-3f * rho) {
-        if (threadIdx.x == 0) *sl.flag_all = 1u;
-        continue;
-    }
+    if (vz + rho <= 0.0f) continue;  // behind the camera plane by more than rho: no forward ray comes near
     const float W = (float)u.framebufferDim[0], H = (float)u.framebufferDim[1], aspect = W / H;
-    const float zn = vz - rho, zf = vz + rho;
+    // points of the ball that a forward ray can reach have depth in (0, vz + rho]
+    const float zn = fmaxf(vz - rho, 1.0e-6f * rho), zf = vz + rho;
     const float xa = (vx - rho) / ((vx - rho) < 0.0f ? zn : zf), xb = (vx + rho) / ((vx + rho) < 0.0f ? zf : zn);
     const float ya = (vy - rho) / ((vy - rho) < 0.0f ? zn : zf), yb = (vy + rho) / ((vy + rho) < 0.0f ? zf : zn);
     // x = ((2 (px + 0.5) / W) - 1) * aspect * tan  <=>  px = (x / (aspect * tan) + 1) * W / 2 - 0.5 ; y decreases with py
@@ -928,12 +927,25 @@ __global__ void __launch_bounds__(64) k_flag_near_segments(const VrEvalLight* __
         const uint32_t nseg = counts[pix] >> 3;
         if (!nseg) continue;
         const uint32_t off = (uint32_t)offsets[pix], sb = sl.seg_base[pix];
-        for (uint32_t k = 0; k < nseg; k++) {
-            const float4 p0 = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k);
-            const float4 p1 = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k + 7u);
-            const float s0 = (p0.x - cx) * dx + (p0.y - cy) * dy + (p0.z - cz) * dz;
-            const float s1 = (p1.x - cx) * dx + (p1.y - cy) * dy + (p1.z - cz) * dz;
-            if (b > s0 - rho && b < s1 + rho) sl.flags[sb + k] = 1;
+        // the segments are consecutive along the ray: stop behind the foot point (four at a time, loads issued together)
+        for (uint32_t k0 = 0; k0 < nseg; k0 += 4) {
+            float4 p0[4], p1[4];
+#pragma unroll
+            for (uint32_t q = 0; q < 4; q++) {
+                const uint32_t k = k0 + q < nseg ? k0 + q : nseg - 1;
+                p0[q] = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k);
+                p1[q] = __ldg(reinterpret_cast<const float4*>(samples) + off + 8u * k + 7u);
+            }
+            bool beyond = false;
+#pragma unroll
+            for (uint32_t q = 0; q < 4; q++) {
+                if (k0 + q >= nseg) break;
+                const float s0 = (p0[q].x - cx) * dx + (p0[q].y - cy) * dy + (p0[q].z - cz) * dz;
+                const float s1 = (p1[q].x - cx) * dx + (p1[q].y - cy) * dy + (p1[q].z - cz) * dz;
+                if (b > s0 - rho && b < s1 + rho) sl.flags[sb + k0 + q] = 1;
+                beyond = s0 - rho >= b;
+            }
+            if (beyond) break;
         }
     }
     }
@@ -1003,10 +1015,24 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     const uint32_t* __restrict__ tab_flag = LEN == 16 ? sl.seg16_flag : sl.seg_flag;
     const uint64_t seg_base = (uint64_t)blockIdx.x * SEG_PER_CTA;
     if (seg_base >= nseg) return;  // the launch is sized by the capacity, the segment count lives on the device
+    const uint32_t tid = threadIdx.x;
+    const bool redo_all = *sl.flag_all != 0u;
+    {
+        // a CTA whose entries are all on the exact kernel's list already (near a light, or flag_all) has nothing to evaluate
+        bool listed = true;
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
+            if (seg < nseg && !redo_all) {
+                const uint32_t fi = tab_flag[seg];
+                listed = listed && (sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0));
+            }
+        }
+        if (__syncthreads_and(listed)) return;
+    }
     const uint64_t nlights = *nlights_dev;
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
-    const uint32_t tid = threadIdx.x;
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
@@ -1023,7 +1049,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     float2 s[LEN], acc[LEN], A[3], D[3];
     float sw[2][KEEP_W ? LEN : 1];
     uint32_t first[2];
-    const bool redo_all = *sl.flag_all != 0u;
     bool redo[2] = {false, false};  // per segment, so that what the exact kernel evaluates does not depend on the pairing
     bool skip[2] = {false, false};  // on the exact kernel's list already: that kernel (another stream) owns the result
 #pragma unroll
@@ -1080,7 +1105,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             else A[c].y = a[c], D[c].y = d[c];
         }
     }
-
     for (uint64_t tl = 0; tl < ntiles; tl++) {
         const uint32_t buf = (uint32_t)(tl & 1);
         if (tid == 0 && tl + 1 < ntiles) {
@@ -1189,10 +1213,17 @@ __device__ __forceinline__ unsigned char to_unorm8(float v) {
     if (v != v) v = 0.0f;
     return (unsigned char)__float2int_rn(vr_mul(v, 255.0f));
 }
-// progressive average of point_compute_color.comp:99-105 on the float accumulator and on the rgba8 image
+// progressive average of point_compute_color.comp:99-105 on the float accumulator and on the rgba8 image.
+// nn == 0 selects the SUM mode of vr_set_accumulate_mode (sample-parallel progressive rendering): the float accumulator
+// adds the frame colour, the rgba8 image is left alone (its quantised running average is sequential by construction).
 __device__ __forceinline__ void accumulate_pixel(float fc, float nm1, float nn, float4* accum, uchar4* rgba8, uint64_t gp) {
     const float4 prev = accum[gp];
     float4 nw;
+    if (nn == 0.0f) {
+        nw.x = vr_add(prev.x, fc), nw.y = vr_add(prev.y, fc), nw.z = vr_add(prev.z, fc), nw.w = 1.0f;
+        accum[gp] = nw;
+        return;
+    }
     nw.x = vr_div(vr_add(vr_mul(prev.x, nm1), fc), nn);
     nw.y = vr_div(vr_add(vr_mul(prev.y, nm1), fc), nn);
     nw.z = vr_div(vr_add(vr_mul(prev.z, nm1), fc), nn);
@@ -1215,7 +1246,7 @@ __device__ __forceinline__ void store_frame_color(const VrFrameColorOut& o, uint
 __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const uint32_t* __restrict__ counts,
                                                   const unsigned long long* __restrict__ offsets, const float* __restrict__ contrib,
                                                   const VrLightCounter* __restrict__ counter, VrFrameColorOut frame_color,
-                                                  float4* __restrict__ accum, uchar4* __restrict__ rgba8) {
+                                                  float4* __restrict__ accum, uchar4* __restrict__ rgba8, int sum_mode) {
     const uint64_t pix = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= (uint64_t)tile.w * tile.h) return;
     const uint32_t lx = (uint32_t)(pix % tile.w), ly = (uint32_t)(pix / tile.w);
@@ -1228,19 +1259,51 @@ __global__ void __launch_bounds__(256) k_resolve(vr_ubo u, vr_tile tile, const u
     fc = vr_clamp(fc, 0.0f, 1.0f);
     if (fc != fc) fc = 0.0f;  // lightCount == 0 -> 0/0; a NaN stores as 0 (Appendix B)
     store_frame_color(frame_color, gp, fc);
-    const float total = vr_u2f(u.frameCount);  // float totalInvocations = frameCount * 1
+    const float total = sum_mode ? 0.0f : vr_u2f(u.frameCount);  // float totalInvocations = frameCount * 1
     accumulate_pixel(fc, vr_sub(total, 1.0f), total, accum, rgba8, gp);
 }
 
 // running average of an already known frame colour (rows rendered by another GPU and exchanged over NVLink)
 __global__ void __launch_bounds__(256) k_accumulate(vr_ubo u, vr_tile tile, const float* __restrict__ frame_color,
-                                                     float4* __restrict__ accum, uchar4* __restrict__ rgba8) {
+                                                     float4* __restrict__ accum, uchar4* __restrict__ rgba8, int sum_mode) {
     const uint64_t pix = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= (uint64_t)tile.w * tile.h) return;
     const uint32_t lx = (uint32_t)(pix % tile.w), ly = (uint32_t)(pix / tile.w);
     const uint64_t gp = (uint64_t)(tile.y0 + ly) * u.framebufferDim[0] + (tile.x0 + lx);
-    const float total = vr_u2f(u.frameCount);
+    const float total = sum_mode ? 0.0f : vr_u2f(u.frameCount);
     accumulate_pixel(frame_color[gp], vr_sub(total, 1.0f), total, accum, rgba8, gp);
+}
+// end of a sample-parallel progressive run: the float accumulator holds the SUM of `total` frame colours (this GPU's, plus
+// the other GPUs' after the reduce); make it their average and derive the rgba8 image from that average
+__global__ void __launch_bounds__(256) k_finish_sum(float4* __restrict__ accum, uchar4* __restrict__ rgba8, uint64_t npix, float total) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 s = accum[p];
+    const float4 a = make_float4(vr_div(s.x, total), vr_div(s.y, total), vr_div(s.z, total), 1.0f);
+    accum[p] = a;
+    rgba8[p] = make_uchar4(to_unorm8(a.x), to_unorm8(a.y), to_unorm8(a.z), 255);
+}
+// dst += src over n float4 (the reduce of the sample-parallel mode inside one process: src is a peer GPU's accumulator)
+__global__ void __launch_bounds__(256) k_add_accum(float4* __restrict__ dst, const float4* __restrict__ src, uint64_t npix) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 a = dst[p], b = src[p];
+    dst[p] = make_float4(vr_add(a.x, b.x), vr_add(a.y, b.y), vr_add(a.z, b.z), 1.0f);
+}
+// Cross-GPU barrier inside one process (vr_group): GPU `self` announces epoch `epoch` in every GPU's flag array (peer
+// stores over NVLink) and waits until all n GPUs have announced it in its own. The stores of the kernels that ran before
+// this one on the stream (frame colours written to the peers' buffers by k_resolve) are ordered in front of the flag by
+// the system-scope fence, so a GPU that sees the flag also sees them.
+__global__ void k_peer_barrier(VrPeerFlags f, uint32_t self, uint32_t n, uint32_t epoch) {
+    const uint32_t q = threadIdx.x;
+    if (q < n) {
+        __threadfence_system();
+        volatile uint32_t* dst = f.flags[q] + self;
+        *dst = epoch;
+        volatile uint32_t* mine = f.flags[self] + q;
+        while ((int32_t)(*mine - epoch) < 0) __nanosleep(64);
+        __threadfence_system();
+    }
 }
 
 // =====================================================================================================
@@ -1272,7 +1335,7 @@ __global__ void k_path_table(VrGridDev g, vr_ubo u, uint32_t nmax, float* __rest
 
 __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile, VrFrameColorOut frame_color,
                                                float4* __restrict__ accum, uchar4* __restrict__ rgba8, VrWorkCounters* wc,
-                                               const float* __restrict__ tab, uint32_t nmax) {
+                                               const float* __restrict__ tab, uint32_t nmax, int sum_mode) {
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -1346,7 +1409,7 @@ __global__ void __launch_bounds__(128) k_path(VrGridDev g, vr_ubo u, float tan_s
         const uint64_t gp = (uint64_t)py * u.framebufferDim[0] + px;
         store_frame_color(frame_color, gp, fc);
         // (previousColor * (contributionCount - 1) + frameColor) / contributionCount with uint contributionCount
-        accumulate_pixel(fc, vr_u2f(u.frameCount - 1u), vr_u2f(u.frameCount), accum, rgba8, gp);
+        accumulate_pixel(fc, vr_u2f(u.frameCount - 1u), sum_mode ? 0.0f : vr_u2f(u.frameCount), accum, rgba8, gp);
     }
     if (wc) {
         unsigned long long a = sref, b = seff;
@@ -1724,8 +1787,7 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
     // the exact kernel's list restarts from the leftovers every frame
     cudaMemcpyAsync(sl.counts + 2, sl.counts + 1, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
     const uint64_t seg_cap = nsamples / SEG_LEN;
-    static const int small_env = getenv("VR_LIST_SMALL") ? atoi(getenv("VR_LIST_SMALL")) : 1;
-    const bool small = small_env && nsamples < 40ull * 1000 * 1000;
+    const bool small = nsamples < 40ull * 1000 * 1000;  // short lists: 4 samples per thread, twice the CTAs at half the duration
     const unsigned grid16 = (unsigned)((seg_cap / 2 + SEG_PER_CTA - 1) / SEG_PER_CTA);
     const uint64_t cap8 = sphere ? seg_cap : (seg_cap < npix ? seg_cap : npix);  // point-type: at most one odd segment per pixel
     const unsigned grid8 = (unsigned)((cap8 + SEG_PER_CTA - 1) / SEG_PER_CTA);
@@ -1736,7 +1798,7 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
         const float margin = 1.02f * (rho + (sphere ? radius : 0.0f)) + 1.0e-3f;
         if (nlights_capacity) {
             VR_COUNT(1);
-            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 64, 0, st>>>(
+            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 128, 0, st>>>(
                 lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples, sl, margin);
         }
         if (!sphere && seg_cap / 2) {
@@ -1792,27 +1854,42 @@ void vrk_eval(cudaStream_t st, int sphere, const VrSample* samples, uint64_t nsa
         k_eval<false, S><<<grid, EVAL_THREADS, 0, st>>>(samples, nsamples, lights, nlights_dev, radius, out);
 }
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
-                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8) {
+                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8,
+                 int sum_mode) {
     VR_COUNT(1);
     const uint64_t npix = (uint64_t)tile.w * tile.h;
     if (!npix) return;
-    k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8);
+    k_resolve<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, counts, offsets, contrib, counter, frame_color, accum, rgba8, sum_mode);
 }
-void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8) {
+void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8, int sum_mode) {
     VR_COUNT(1);
     const uint64_t npix = (uint64_t)tile.w * tile.h;
     if (!npix) return;
-    k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, frame_color, accum, rgba8);
+    k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(u, tile, frame_color, accum, rgba8, sum_mode);
+}
+void vrk_finish_sum(cudaStream_t st, float4* accum, uchar4* rgba8, uint64_t npix, float total) {
+    if (!npix) return;
+    VR_COUNT(1);
+    k_finish_sum<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(accum, rgba8, npix, total);
+}
+void vrk_add_accum(cudaStream_t st, float4* dst, const float4* src, uint64_t npix) {
+    if (!npix) return;
+    VR_COUNT(1);
+    k_add_accum<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(dst, src, npix);
+}
+void vrk_peer_barrier(cudaStream_t st, const VrPeerFlags& f, uint32_t self, uint32_t n, uint32_t epoch) {
+    VR_COUNT(1);
+    k_peer_barrier<<<1, 32, 0, st>>>(f, self, n, epoch);
 }
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrFrameColorOut& frame_color,
-              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax) {
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax, int sum_mode) {
     VR_COUNT(1);
     if (tab) {
         VR_COUNT(1);
         k_path_table<<<1, 32, 0, st>>>(g, u, nmax, tab);
     }
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
-    k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc, tab, nmax);
+    k_path<<<grid, 128, 0, st>>>(g, u, tan_scale, tile, frame_color, accum, rgba8, wc, tab, nmax, sum_mode);
 }
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density) {
     VR_COUNT(1);

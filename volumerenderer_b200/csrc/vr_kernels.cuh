@@ -31,6 +31,12 @@ struct VrFrameColorOut {
     uint32_t npeers;
 };
 
+// flag arrays of the in-process cross-GPU barrier (vr_group): flags[g] is GPU g's array of VR_MAX_PEERS epochs, mapped
+// into every GPU of the group through CUDA peer access
+struct VrPeerFlags {
+    uint32_t* flags[VR_MAX_PEERS];
+};
+
 struct VrWorkCounters {
     unsigned long long S_ref, S_eff;
 };
@@ -108,13 +114,19 @@ void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t n
                             const unsigned long long* nlights_dev, float radius, float* out);
 // ---- per-pixel reduction + clamp + progressive average (shaders/point_compute_color.comp:97-105)
 void vrk_resolve(cudaStream_t st, const vr_ubo& u, vr_tile tile, const uint32_t* counts, const unsigned long long* offsets,
-                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8);
+                 const float* contrib, const VrLightCounter* counter, const VrFrameColorOut& frame_color, float4* accum, uchar4* rgba8,
+                 int sum_mode);
 // running average (same arithmetic as vrk_resolve) of frame colours that are already in frame_color for this tile
-void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8);
+void vrk_accumulate(cudaStream_t st, const vr_ubo& u, vr_tile tile, const float* frame_color, float4* accum, uchar4* rgba8, int sum_mode);
+// sample-parallel progressive mode (vr_set_accumulate_mode): accumulator = sum / total, rgba8 from that average; dst += src
+void vrk_finish_sum(cudaStream_t st, float4* accum, uchar4* rgba8, uint64_t npix, float total);
+void vrk_add_accum(cudaStream_t st, float4* dst, const float4* src, uint64_t npix);
+// in-process cross-GPU barrier on `st` (GPU `self` of n, epoch counts up from 1)
+void vrk_peer_barrier(cudaStream_t st, const VrPeerFlags& f, uint32_t self, uint32_t n, uint32_t epoch);
 // ---- path mode (shaders/path_compute_color.comp), fully fused per pixel
 // tab (27 * (nmax + 1) floats, may be NULL) receives the shadow-term table: light after n multiplies, per neighbour voxel
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrFrameColorOut& frame_color,
-              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax);
+              float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax, int sum_mode);
 // ---- CPU_test/main.cpp:25-43, 89-126
 void vrk_cpu_test(cudaStream_t st, const VrGridDev& g, uint32_t w, uint32_t h, float aspect, float scale, float* density);
 // ---- traversal test hook

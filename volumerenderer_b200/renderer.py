@@ -238,6 +238,31 @@ class VolumeRenderer:
     def read_wait(self):
         self._check(self._L.vr_read_wait(self._ctx))
 
+    def read_accum_tile_async(self, tile, out_image):
+        """vr_read_accum_f32_tile_async: the accumulator's pixels of `tile` into the same pixels of `out_image`, an
+        (H, W, 4) float32 array of the full image (ideally pinned; may be shared between processes)."""
+        assert out_image.dtype == np.float32 and out_image.shape == (self.height, self.width, 4) and out_image.flags["C_CONTIGUOUS"]
+        x0, y0 = int(tile[0]), int(tile[1])
+        ptr = out_image.ctypes.data + (y0 * self.width + x0) * 16
+        self._check(self._L.vr_read_accum_f32_tile_async(self._ctx, C.byref(VrTile(*tile)), C.c_void_p(ptr), self.width * 16))
+
+    def set_eval_side_stream(self, enabled):
+        """vr_set_eval_side_stream: second stream for the small evaluation kernels (default on); results identical."""
+        self._check(self._L.vr_set_eval_side_stream(self._ctx, int(bool(enabled))))
+
+    # ------------------------------------------------------------------ sample-parallel progressive mode
+    def set_frame_step(self, step):
+        """vr_set_frame_step: draw_frame advances frameCount by `step` (rank r of G: frameCount = r, step = G)."""
+        self._check(self._L.vr_set_frame_step(self._ctx, int(step)))
+
+    def set_accumulate_mode(self, mode):
+        """'average' (the reference's running average) or 'sum' (float sum of the frame colours; include/vr.h)."""
+        self._check(self._L.vr_set_accumulate_mode(self._ctx, {"average": 0, "sum": 1}.get(mode, mode)))
+
+    def finish_sum(self, total_frames):
+        """vr_finish_sum: accumulator = sum / total_frames, rgba8 from that average, frameCount = total_frames."""
+        self._check(self._L.vr_finish_sum(self._ctx, int(total_frames)))
+
     def read_image_rgba8(self):
         out = np.zeros((self.height, self.width, 4), np.uint8)
         self._check(self._L.vr_read_image_rgba8(self._ctx, out.ctypes.data_as(C.c_void_p)))
@@ -279,6 +304,12 @@ class VolumeRenderer:
         a, i, f, s = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
         self._check(self._L.vr_get_device_buffers(self._ctx, C.byref(a), C.byref(i), C.byref(f), C.byref(s)))
         return dict(accum=a.value, rgba8=i.value, frame_color=f.value, stream=s.value)
+
+    def march_info(self):
+        """Layout of the last gather's sample buffer: dict(single_pass, slots, samples)."""
+        a = (C.c_uint64 * 3)()
+        self._check(self._L.vr_get_march_info(self._ctx, a))
+        return dict(single_pass=bool(a[0]), slots=int(a[1]), samples=int(a[2]))
 
     def set_march_single_pass(self, enabled):
         """vr_set_march_single_pass: 1 (default) = one march per frame into a sample buffer with gaps; 0 = count + fill."""
