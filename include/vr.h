@@ -162,6 +162,8 @@ int vr_read_wait(vr_ctx* ctx);
  * instead of one GPU pulling the whole image. `out` addresses the tile's first pixel in the caller's image (pinned memory,
  * possibly shared between the ranks' processes), rows out_pitch_bytes apart. One read-back in flight per context. */
 int vr_read_accum_f32_tile_async(vr_ctx* ctx, const vr_tile* tile_or_null, float* out, uint64_t out_pitch_bytes);
+/* the rgba8 pixels of one tile (blocking); `out` addresses the tile's first pixel, rows out_pitch_bytes apart */
+int vr_read_image_rgba8_tile(vr_ctx* ctx, const vr_tile* tile_or_null, uint8_t* out, uint64_t out_pitch_bytes);
 int vr_read_frame_color_f32(vr_ctx* ctx, float* out);      /* width*height floats: the last frame's clamp()ed colour, R=G=B */
 int vr_write_accum_f32(vr_ctx* ctx, const float* in, uint32_t frame_count); /* restore a snapshot (resume) */
 int vr_write_image_rgba8(vr_ctx* ctx, const uint8_t* in);
@@ -218,16 +220,17 @@ int vr_set_eval_side_stream(vr_ctx* ctx, int enabled);
  * keep a float SUM of their frame colours; one reduce(sum) and a division replace the sequential running average of
  * shaders/point_compute_color.comp:99-105 (equal up to float reassociation; the rgba8 running average, re-quantised every
  * frame, is sequential by construction and is not available in this mode).
- *   vr_set_frame_step(step)       vr_render_frame advances frameCount by `step` instead of 1 (src/main.cpp:712): rank r
- *                                 of G sets ubo.frameCount = r with vr_set_params and step = G, and renders frames
- *                                 r+1, r+1+G, ... with exactly the light lists the sequential run generates for them
+ *   vr_set_frame_step(first, step)  the next vr_render_frame is frame number `first` (0: frameCount + step as usual) and
+ *                                 every later one advances frameCount by `step` instead of 1 (src/main.cpp:712): rank r
+ *                                 of G calls (r + 1, G) and renders frames r+1, r+1+G, ... with exactly the light
+ *                                 lists the sequential run generates for them; (0, 1) restores the default
  *   vr_set_accumulate_mode(SUM)   the float accumulator adds each frame colour instead of averaging; rgba8 is not touched;
  *                                 clear with vr_clear_image (the implicit clear only happens at frameCount == 1)
  *   vr_finish_sum(total)          after the sums were reduced into this context's accumulator (vr_get_device_buffers +
  *                                 NCCL, or vr_group_render_progressive): accumulator = sum / total, rgba8 = UNORM8 of
  *                                 that average, frameCount = total */
 enum { VR_ACCUM_AVERAGE = 0, VR_ACCUM_SUM = 1 };
-int vr_set_frame_step(vr_ctx* ctx, uint32_t step);
+int vr_set_frame_step(vr_ctx* ctx, uint32_t first, uint32_t step);
 int vr_set_accumulate_mode(vr_ctx* ctx, int mode);
 int vr_finish_sum(vr_ctx* ctx, uint32_t total_frames);
 
@@ -342,6 +345,55 @@ int vr_timer_stop(vr_ctx* ctx, float* elapsed_ms); /* records, synchronises and 
  * kind 2: the point-light inner loop with operands in registers (3 FADD, FMUL, 2 FFMA, FSETP, MUFU.RCP, FFMA) -> 1e12 eval/s
  * kind 3: dependent FFMA2 (packed FP32x2) chains -> TFLOP/s; kind 4: the packed point-light inner loop -> 1e12 eval/s */
 int vr_ubench(vr_ctx* ctx, int kind, double* result);
+
+/* ---- several GPUs of one node from ONE process (the reference is single-GPU, src/main.cpp:265-270).
+ * A group owns one context per GPU, each driven by its own host thread, with CUDA peer access between all of them.
+ * Frames are image-tiled: GPU i renders a band of rows (grid, UBO and light list replicated; light generation is
+ * deterministic and repeated on every GPU) and keeps the progressive accumulator of that band -- the path has no exchange
+ * step; the bands meet where the image is consumed (vr_group_read_*: every GPU returns its rows over its own PCIe link).
+ * VR_EXCHANGE_ALLGATHER additionally leaves the whole image on every GPU after every frame: the resolve kernel stores
+ * the band's frame colours to all GPUs through peer mappings over NVLink, a flag-based device-side barrier orders them,
+ * every GPU averages the rows it did not render. Results are bit-identical to a one-GPU render in both modes.
+ * Calls are issued by one thread at a time; vr_group_ctx gives the per-GPU context for everything not wrapped here
+ * (timings, counters, options): set those identically on every GPU. */
+typedef struct vr_group vr_group;
+enum { VR_EXCHANGE_NONE = 0, VR_EXCHANGE_ALLGATHER = 1 };
+/* cuda_devices == NULL: devices 0..n-1. A device may be listed more than once (several bands on one GPU: how the group
+ * logic is tested on a one-GPU box). */
+int vr_group_create(const int* cuda_devices, uint32_t n, vr_group** out);
+int vr_group_destroy(vr_group* g);
+const char* vr_group_last_error(const vr_group* g); /* g may be NULL: error of a failed vr_group_create on this thread */
+uint32_t vr_group_size(const vr_group* g);
+vr_ctx* vr_group_ctx(vr_group* g, uint32_t i);
+/* the volume crosses PCIe once (to the first GPU) and is replicated GPU to GPU over NVLink (vr_set_grid_device) */
+int vr_group_set_grid(vr_group* g, const void* nanovdb_bytes, uint64_t size);
+int vr_group_resize(vr_group* g, uint32_t width, uint32_t height);
+int vr_group_set_params(vr_group* g, const vr_ubo* params);
+int vr_group_get_params(vr_group* g, vr_ubo* params);
+int vr_group_set_max_lights_capacity(vr_group* g, uint32_t n);
+int vr_group_set_light_gen_groups(vr_group* g, uint32_t gx, uint32_t gy, uint32_t gz, vr_lightgen_variant variant);
+int vr_group_set_exchange(vr_group* g, int mode);
+int vr_group_reset_accumulation(vr_group* g);
+/* row bands, one per GPU in GPU order: contiguous, non-empty, covering the image. vr_group_balance chooses them: a per-row
+ * cost model from one measured frame (evaluation time follows the row's non-zero-density samples, the march's the row),
+ * then `rounds` rounds of measured feedback (each GPU reports the device time of its band); the best split seen is kept.
+ * It renders untimed frames, resets the accumulation and restores the parameters. */
+int vr_group_set_bands(vr_group* g, const uint32_t* y0, const uint32_t* h);
+int vr_group_get_bands(vr_group* g, uint32_t* y0, uint32_t* h);
+int vr_group_balance(vr_group* g, vr_algo algo, uint32_t rounds);
+/* the compute section of drawFrame (src/main.cpp:712-837) on every GPU, each for its band; returns once enqueued */
+int vr_group_render_frame(vr_group* g, vr_algo algo);
+int vr_group_sync(vr_group* g);
+int vr_group_read_accum_f32(vr_group* g, float* out);       /* width*height*4 floats; every GPU copies its own rows */
+int vr_group_read_accum_f32_async(vr_group* g, float* out); /* pinned memory; valid after vr_group_read_wait */
+int vr_group_read_wait(vr_group* g);
+int vr_group_read_image_rgba8(vr_group* g, uint8_t* out);
+/* sample-parallel progressive run (vr_set_frame_step / vr_set_accumulate_mode above): frames 1..frames go round-robin to
+ * the GPUs, each renders WHOLE images into a float sum; the first GPU adds the others' sums in GPU order (peer reads over
+ * NVLink), divides, and holds the result (float accumulator, rgba8 of the average, frameCount = frames). */
+int vr_group_render_progressive(vr_group* g, vr_algo algo, uint32_t frames);
+/* device time of `frames` tiled frames: CUDA events on every GPU's stream, maximum over the GPUs; per_gpu_ms may be NULL */
+int vr_group_time_frames(vr_group* g, vr_algo algo, uint32_t frames, float* ms_per_frame_max, float* per_gpu_ms);
 
 /* library facts */
 const char* vr_version(void);

@@ -4,6 +4,10 @@ import sys
 import numpy as np
 import pytest
 
+# several contexts (5 streams each) share one GPU in the vr_group tests: with the default of 8 hardware queues their streams
+# would alias and a spinning barrier kernel could block the peer it waits for; must be set before CUDA initialises
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -123,3 +123,30 @@ def test_path_mode_shadow_table_bit_exact(vr, pyoracle, oracle, cloud, step, lig
     assert (cnt["S_ref"], cnt["S_eff"]) == (ocnt["S_ref"], ocnt["S_eff"])
     assert np.array_equal(fc, ofc)
     assert ofc.max() > 0
+
+
+@pytest.mark.parametrize("exchange", ["none", "allgather"])
+def test_headless_multi_gpu_equals_single_context(vr, cloud, tmp_path, exchange):
+    """vr_headless --devices ... (the C++ multi-GPU host: vr_group_*, band balancer, per-GPU read-back) writes the image a
+    single context renders, bit for bit; with one GPU in the box the device is listed several times (bands on one GPU)."""
+    import torch
+    nd = max(1, torch.cuda.device_count())
+    devs = ",".join(str(i % nd) for i in range(4))
+    ppm, pfm = str(tmp_path / "g.ppm"), str(tmp_path / "g.pfm")
+    env = dict(os.environ, CUDA_DEVICE_MAX_CONNECTIONS="32")
+    run = subprocess.run([vr.HEADLESS_PATH, "--devices", devs, "--exchange", exchange, "--grid", "cloud:64", "--algo", "sphere",
+                          "--size", "160x96", "--frames", "3", "--lightgen", "6", "--set", "maxLights=90", "--balance-rounds", "2",
+                          "--bench", "2", "--ppm", ppm, "--pfm", pfm], capture_output=True, text=True, env=env, timeout=300)
+    assert run.returncode == 0, run.stderr
+    info = json.loads(run.stdout.strip().splitlines()[-1])
+    assert info["gpus"] == 4 and info["frames"] == 3 and sum(h for _, h in info["bands"]) == 96 and info["ms_per_frame_device"] > 0
+    with vr.VolumeRenderer(0) as r:
+        r.set_grid(cloud(64))
+        r.resize(160, 96)
+        r.ubo = r.default_ubo()
+        r.update_ubo(maxLights=90)
+        r.set_light_gen_groups(6, 1, 1)
+        for _ in range(3):
+            r.draw_frame("sphere")
+        assert np.array_equal(_read_ppm(ppm), r.read_image_rgba8()[..., :3])
+        assert np.array_equal(_read_pfm(pfm), r.read_accum()[..., :3])

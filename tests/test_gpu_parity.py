@@ -630,9 +630,9 @@ def test_sample_parallel_progressive_sum(vr, cloud):
     total = np.zeros((H, W, 4), np.float64)
     for rank in range(G):
         with vr.VolumeRenderer(0) as r:
-            _setup(r, grid, W, H, maxLights=80, frameCount=rank)
+            _setup(r, grid, W, H, maxLights=80)
             r.set_light_gen_groups(6, 1, 1)
-            r.set_frame_step(G)
+            r.set_frame_step(rank + 1, G)
             r.set_accumulate_mode("sum")
             r.clear_image()
             for k in range(frames // G):

@@ -65,7 +65,12 @@ EXPORTS = [
     "vr_set_stream", "vr_set_grid_device", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
     "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
     "vr_io_last_error",
-    "vr_read_accum_f32_tile_async", "vr_set_eval_side_stream", "vr_set_frame_step", "vr_set_accumulate_mode", "vr_finish_sum", "vr_get_march_info",
+    "vr_read_accum_f32_tile_async", "vr_set_eval_side_stream", "vr_set_frame_step", "vr_set_accumulate_mode", "vr_finish_sum", "vr_get_march_info", "vr_read_image_rgba8_tile",
+    "vr_group_create", "vr_group_destroy", "vr_group_last_error", "vr_group_size", "vr_group_ctx", "vr_group_set_grid", "vr_group_resize",
+    "vr_group_set_params", "vr_group_get_params", "vr_group_set_max_lights_capacity", "vr_group_set_light_gen_groups",
+    "vr_group_set_exchange", "vr_group_reset_accumulation", "vr_group_set_bands", "vr_group_get_bands", "vr_group_balance",
+    "vr_group_render_frame", "vr_group_sync", "vr_group_read_accum_f32", "vr_group_read_accum_f32_async", "vr_group_read_wait",
+    "vr_group_read_image_rgba8", "vr_group_render_progressive", "vr_group_time_frames",
 ]
 
 _lib = None
@@ -157,9 +162,37 @@ def load():
     L.vr_io_last_error.restype = C.c_char_p
     L.vr_read_accum_f32_tile_async.argtypes = [P, C.POINTER(VrTile), P, U64]
     L.vr_set_eval_side_stream.argtypes = [P, I]
-    L.vr_set_frame_step.argtypes = [P, U32]
+    L.vr_set_frame_step.argtypes = [P, U32, U32]
     L.vr_set_accumulate_mode.argtypes = [P, I]
     L.vr_finish_sum.argtypes = [P, U32]
     L.vr_get_march_info.argtypes = [P, C.POINTER(U64)]
+    L.vr_read_image_rgba8_tile.argtypes = [P, C.POINTER(VrTile), P, U64]
+    L.vr_group_create.argtypes = [C.POINTER(I), U32, C.POINTER(P)]
+    L.vr_group_destroy.argtypes = [P]
+    L.vr_group_last_error.restype = C.c_char_p
+    L.vr_group_last_error.argtypes = [P]
+    L.vr_group_size.argtypes = [P]
+    L.vr_group_size.restype = U32
+    L.vr_group_ctx.argtypes = [P, U32]
+    L.vr_group_ctx.restype = P
+    L.vr_group_set_grid.argtypes = [P, P, U64]
+    L.vr_group_resize.argtypes = [P, U32, U32]
+    L.vr_group_set_params.argtypes = [P, C.POINTER(VrUbo)]
+    L.vr_group_get_params.argtypes = [P, C.POINTER(VrUbo)]
+    L.vr_group_set_max_lights_capacity.argtypes = [P, U32]
+    L.vr_group_set_light_gen_groups.argtypes = [P, U32, U32, U32, I]
+    L.vr_group_set_exchange.argtypes = [P, I]
+    L.vr_group_reset_accumulation.argtypes = [P]
+    L.vr_group_set_bands.argtypes = [P, C.POINTER(U32), C.POINTER(U32)]
+    L.vr_group_get_bands.argtypes = [P, C.POINTER(U32), C.POINTER(U32)]
+    L.vr_group_balance.argtypes = [P, I, U32]
+    L.vr_group_render_frame.argtypes = [P, I]
+    L.vr_group_sync.argtypes = [P]
+    L.vr_group_read_accum_f32.argtypes = [P, P]
+    L.vr_group_read_accum_f32_async.argtypes = [P, P]
+    L.vr_group_read_wait.argtypes = [P]
+    L.vr_group_read_image_rgba8.argtypes = [P, P]
+    L.vr_group_render_progressive.argtypes = [P, I, U32]
+    L.vr_group_time_frames.argtypes = [P, I, U32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     _lib = L
     return L

@@ -183,6 +183,7 @@ struct vr_ctx {
     uint64_t cached_real = 0;     // number of samples in it
     bool march_single = true;     // vr_set_march_single_pass
     uint32_t frame_step = 1;      // vr_set_frame_step: frameCount advances by this much per vr_render_frame
+    uint32_t frame_first = 0;     // ... after the next frame, which is number frame_first (0: no override)
     int accumulate_mode = 0;      // vr_set_accumulate_mode: 0 = running average (the reference), 1 = float sum
     bool eval_side_stream = true; // vr_set_eval_side_stream
     // what the current light list was generated from (vr_dispatch_light_gen / vr_render_frame): bounds the list length and
@@ -1144,7 +1145,9 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
         if (rc != VR_OK) return rc;
     }
     VR_CUDA(c, cudaSetDevice(c->device));
-    c->ubo.frameCount += c->frame_step;  // src/main.cpp:712 (frame_step = 1 unless vr_set_frame_step)
+    const uint32_t frame_before = c->ubo.frameCount, first_before = c->frame_first;
+    if (c->frame_first) c->ubo.frameCount = c->frame_first, c->frame_first = 0;  // vr_set_frame_step
+    else c->ubo.frameCount += c->frame_step;                                    // src/main.cpp:712
     vr_ctx::TimingSet* t = nullptr;
     rc = open_timing_set(c, &t);
     if (rc != VR_OK) return rc;
@@ -1192,7 +1195,7 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
     if (rc != VR_OK) {
         // the frame did not happen (a CUDA or allocation failure past the argument checks): frameCount goes back, and the
         // steady-state bookkeeping starts over so that no prefetched light list is adopted for a frame that never ran
-        c->ubo.frameCount -= c->frame_step;
+        c->ubo.frameCount = frame_before, c->frame_first = first_before;
         c->prev_frame_valid = false;
     }
     return rc;
@@ -1254,6 +1257,21 @@ int vr_read_lights(vr_ctx* c, vr_ray_light* out, uint32_t capacity, uint32_t* co
 int vr_read_image_rgba8(vr_ctx* c, uint8_t* out) { VR_READ_IMAGE(c, out, c->rgba8, (size_t)c->width * c->height * 4); }
 int vr_read_accum_f32(vr_ctx* c, float* out) { VR_READ_IMAGE(c, out, c->accum, (size_t)c->width * c->height * 16); }
 int vr_read_frame_color_f32(vr_ctx* c, float* out) { VR_READ_IMAGE(c, out, c->frame_color, (size_t)c->width * c->height * 4); }
+
+int vr_read_image_rgba8_tile(vr_ctx* c, const vr_tile* tile_or_null, uint8_t* out, uint64_t out_pitch_bytes) {
+    if (!c) return VR_E_ARG;
+    if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
+    if (!out) return fail(c, VR_E_ARG, "NULL output buffer");
+    vr_tile tile;
+    int rc = validate_tile(c, tile_or_null, &tile);
+    if (rc != VR_OK) return rc;
+    if (out_pitch_bytes < (uint64_t)tile.w * 4) return fail(c, VR_E_ARG, "row pitch %llu is below the tile's row size", (unsigned long long)out_pitch_bytes);
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const uchar4* src = c->rgba8 + (size_t)tile.y0 * c->width + tile.x0;
+    VR_CUDA(c, cudaMemcpy2DAsync(out, (size_t)out_pitch_bytes, src, (size_t)c->width * 4, (size_t)tile.w * 4, tile.h, cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VR_OK;
+}
 
 /* Asynchronous read-back of the float accumulator: the image is snapshotted on the render stream (device-to-device), the
  * copy to the host runs on a copy stream underneath the frames enqueued afterwards. */
@@ -1632,10 +1650,11 @@ int vr_set_eval_side_stream(vr_ctx* c, int enabled) {
     return VR_OK;
 }
 
-int vr_set_frame_step(vr_ctx* c, uint32_t step) {
+int vr_set_frame_step(vr_ctx* c, uint32_t first, uint32_t step) {
     if (!c) return VR_E_ARG;
     if (step == 0 || step > (1u << 20)) return fail(c, VR_E_ARG, "frame step %u out of range", step);
     c->frame_step = step;
+    c->frame_first = first;
     c->prev_frame_valid = false;  // the prefetched list (if any) was generated for frameCount + the old step
     return VR_OK;
 }

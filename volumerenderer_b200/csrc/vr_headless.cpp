@@ -8,6 +8,9 @@
 //   vr_headless --grid cloud:256 --algo point --frames 16 --size 1920x1080 --set maxLights=1000 --lightgen 32 --ppm out.ppm
 //   vr_headless --config scene.json            {"grid": "bunny.nvdb", "algo": "beam", "frames": 64, "beamRadius": 0.1, ...}
 //   vr_headless --grid sphere:32 --cpu-test density.ppm      (CPU_test/main.cpp: fixed camera, 256x256, 1200 steps)
+//   vr_headless --gpus 8 --grid cloud:256 --algo point --size 1920x1080 --lightgen 32 --frames 64 --bench 20
+//                                                             (one process, 8 GPUs: vr_group_*, image bands, csrc/vr_group.cu)
+//   vr_headless --gpus 8 --progressive 1 --algo beam --frames 64 ...   (sample-parallel: frame f on GPU f mod 8, one reduce)
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -27,6 +30,10 @@ struct Options {
     uint32_t width = 1024, height = 1024;  // the reference window (src/main.cpp:40-41)
     uint32_t frames = 1, gx = 1, gy = 1, gz = 1;
     int device = 0, keep_origin = 0, quiet = 0, march_cache = 0;
+    // several GPUs from this one process (vr_group_*): image bands, or whole frames round-robin (--progressive)
+    int gpus = 1, progressive = 0, balance_rounds = 6;
+    uint32_t bench = 0;  // time this many extra frames with CUDA events after the run (maximum over the GPUs)
+    std::string exchange = "none", devices;
     // opt-in physics (vr_options) and the reference's commented-out radius update (src/main.cpp:609-618, :713)
     int trilinear = 0, light_transmittance = 0, phase_hg = 0, radius_shrink = 0;
     double hg_g = 0.0, radius_alpha = 0.0;
@@ -113,6 +120,12 @@ void set_option(Options& o, const std::string& key, const std::string& val) {
     else if (key == "save-nvdb" || key == "saveNvdb") o.save_nvdb = val;
     else if (key == "frames") o.frames = (uint32_t)parse_numbers(val).at(0);
     else if (key == "device") o.device = (int)parse_numbers(val).at(0);
+    else if (key == "gpus") o.gpus = (int)parse_numbers(val).at(0);
+    else if (key == "devices") o.devices = val;
+    else if (key == "progressive") o.progressive = (int)parse_numbers(val).at(0);
+    else if (key == "balance-rounds" || key == "balanceRounds") o.balance_rounds = (int)parse_numbers(val).at(0);
+    else if (key == "bench") o.bench = (uint32_t)parse_numbers(val).at(0);
+    else if (key == "exchange") o.exchange = val;
     else if (key == "width") o.width = (uint32_t)parse_numbers(val).at(0);
     else if (key == "height") o.height = (uint32_t)parse_numbers(val).at(0);
     else if (key == "march-cache" || key == "marchCache") o.march_cache = (int)parse_numbers(val).at(0);
@@ -231,7 +244,91 @@ void usage() {
          "  --save-nvdb FILE         write the volume as an uncompressed .nvdb\n"
          "  --trilinear 0|1  --phase-hg G  --light-transmittance 0|1   opt-in physics the reference lacks (vr_options)\n"
          "  --radius-update ALPHA    beamRadius = calculateRadius(beamRadius, ALPHA) before every frame (src/main.cpp:609-618)\n"
+         "  --gpus N | --devices a,b,..   several GPUs from this process (image bands balanced by measured feedback;\n"
+         "                           a device may be listed twice: several bands on one GPU)\n"
+         "  --exchange none|allgather     none: every GPU keeps the average of its band (default); allgather: the whole image\n"
+         "                           on every GPU after every frame (peer stores from the resolve kernel + device barrier)\n"
+         "  --progressive 1          sample-parallel progressive run: frame f on GPU f mod N, float sums, one reduce\n"
+         "  --balance-rounds R       feedback rounds of the band balancer (default 6)\n"
+         "  --bench K                afterwards time K more frames with CUDA events (prints ms_per_frame_device)\n"
          "  --march-cache 0|1  --device D  --quiet");
+}
+
+void gcheck(int rc, vr_group* g, const char* what) {
+    if (rc == VR_OK) return;
+    fprintf(stderr, "vr_headless: %s failed (status %d): %s\n", what, rc, vr_group_last_error(g));
+    exit(1);
+}
+
+// the frame loop on several GPUs of this node (vr_group_*): what `--gpus N` / `--devices` select
+int run_group(const Options& o, void* grid, uint64_t grid_size) {
+    std::vector<int> devs;
+    if (!o.devices.empty()) for (double d : parse_numbers(o.devices)) devs.push_back((int)d);
+    else for (int i = 0; i < o.gpus; i++) devs.push_back(i);
+    if (!o.cpu_test.empty() || !o.snap_in.empty() || !o.snap_out.empty() || o.radius_shrink)
+        die("--cpu-test, snapshots and --radius-update are one-GPU options");
+    const vr_algo algo = parse_algo(o.algo);
+    vr_group* g = nullptr;
+    gcheck(vr_group_create(devs.data(), (uint32_t)devs.size(), &g), nullptr, "vr_group_create");
+    const uint32_t n = vr_group_size(g);
+    gcheck(vr_group_set_grid(g, grid, grid_size), g, "vr_group_set_grid");
+    vr_grid_free(grid);
+    if (!o.quiet) fprintf(stderr, "%s, %u GPUs, grid %s: %.2f MB\n", vr_version(), n, o.grid.c_str(), grid_size / 1e6);
+    gcheck(vr_group_resize(g, o.width, o.height), g, "vr_group_resize");
+    vr_ubo u;
+    vr_default_params(&u, o.width, o.height);
+    for (auto& kv : o.sets) apply_field(u, kv.first, kv.second, o.quiet != 0);
+    if (u.maxLights > 87500) gcheck(vr_group_set_max_lights_capacity(g, u.maxLights), g, "vr_group_set_max_lights_capacity");
+    gcheck(vr_group_set_params(g, &u), g, "vr_group_set_params");
+    gcheck(vr_group_set_light_gen_groups(g, o.gx, o.gy, o.gz, o.keep_origin ? VR_LG_KEEP_ORIGIN : VR_LG_RESET_ORIGIN), g, "vr_group_set_light_gen_groups");
+    vr_options phys = {(uint32_t)(o.trilinear != 0), (uint32_t)o.phase_hg, (float)o.hg_g, (uint32_t)(o.light_transmittance != 0)};
+    for (uint32_t i = 0; i < n; i++) check(vr_set_options(vr_group_ctx(g, i), &phys), vr_group_ctx(g, i), "vr_set_options");
+    if (o.exchange == "allgather") gcheck(vr_group_set_exchange(g, VR_EXCHANGE_ALLGATHER), g, "vr_group_set_exchange");
+    else if (o.exchange != "none") die("--exchange takes none|allgather");
+
+    std::vector<uint32_t> y0(n), bh(n);
+    const auto t0 = std::chrono::steady_clock::now();
+    if (o.progressive) {
+        gcheck(vr_group_render_progressive(g, algo, o.frames), g, "vr_group_render_progressive");
+    } else {
+        gcheck(vr_group_balance(g, algo, (uint32_t)o.balance_rounds), g, "vr_group_balance");
+        for (uint32_t f = 0; f < o.frames; f++) gcheck(vr_group_render_frame(g, algo), g, "vr_group_render_frame");
+        gcheck(vr_group_sync(g), g, "vr_group_sync");
+    }
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    vr_group_get_bands(g, y0.data(), bh.data());
+    vr_group_get_params(g, &u);
+
+    const size_t npix = (size_t)o.width * o.height;
+    if (!o.ppm.empty()) {
+        std::vector<uint8_t> img(npix * 4);
+        if (o.progressive) check(vr_read_image_rgba8(vr_group_ctx(g, 0), img.data()), vr_group_ctx(g, 0), "vr_read_image_rgba8");
+        else gcheck(vr_group_read_image_rgba8(g, img.data()), g, "vr_group_read_image_rgba8");
+        check(vr_image_write_ppm(o.ppm.c_str(), img.data(), o.width, o.height), nullptr, "vr_image_write_ppm");
+    }
+    if (!o.pfm.empty()) {
+        std::vector<float> acc(npix * 4);
+        if (o.progressive) check(vr_read_accum_f32(vr_group_ctx(g, 0), acc.data()), vr_group_ctx(g, 0), "vr_read_accum_f32");
+        else gcheck(vr_group_read_accum_f32(g, acc.data()), g, "vr_group_read_accum_f32");
+        check(vr_image_write_pfm(o.pfm.c_str(), acc.data(), o.width, o.height, 4), nullptr, "vr_image_write_pfm");
+    }
+    float dev_ms = 0.0f;
+    std::vector<float> per(n, 0.0f);
+    if (o.bench && !o.progressive) {
+        for (int w = 0; w < 3; w++) gcheck(vr_group_render_frame(g, algo), g, "vr_group_render_frame");
+        gcheck(vr_group_time_frames(g, algo, o.bench, &dev_ms, per.data()), g, "vr_group_time_frames");
+    }
+    if (!o.quiet) {
+        printf("{\"gpus\": %u, \"mode\": \"%s\", \"exchange\": \"%s\", \"frames\": %u, \"frameCount\": %u, \"wall_ms_total\": %.3f, \"algo\": \"%s\", "
+               "\"width\": %u, \"height\": %u, \"bands\": [", n, o.progressive ? "sample-parallel" : "image bands", o.exchange.c_str(), o.frames,
+               u.frameCount, ms, o.algo.c_str(), o.width, o.height);
+        for (uint32_t i = 0; i < n; i++) printf("%s[%u, %u]", i ? ", " : "", y0[i], bh[i]);
+        printf("], \"ms_per_frame_device\": %.4f, \"per_gpu_ms\": [", dev_ms);
+        for (uint32_t i = 0; i < n; i++) printf("%s%.4f", i ? ", " : "", per[i]);
+        printf("]}\n");
+    }
+    vr_group_destroy(g);
+    return 0;
 }
 
 }  // namespace
@@ -265,6 +362,8 @@ int main(int argc, char** argv) {
     uint64_t grid_size = 0;
     load_grid(o, &grid, &grid_size);
     if (!o.save_nvdb.empty()) check(vr_grid_save_nvdb(o.save_nvdb.c_str(), grid, grid_size, 0), nullptr, "vr_grid_save_nvdb");
+
+    if (o.gpus > 1 || !o.devices.empty()) return run_group(o, grid, grid_size);
 
     vr_ctx* ctx = nullptr;
     check(vr_create(o.device, &ctx), nullptr, "vr_create");

@@ -1293,15 +1293,27 @@ __global__ void __launch_bounds__(256) k_add_accum(float4* __restrict__ dst, con
 // Cross-GPU barrier inside one process (vr_group): GPU `self` announces epoch `epoch` in every GPU's flag array (peer
 // stores over NVLink) and waits until all n GPUs have announced it in its own. The stores of the kernels that ran before
 // this one on the stream (frame colours written to the peers' buffers by k_resolve) are ordered in front of the flag by
-// the system-scope fence, so a GPU that sees the flag also sees them.
-__global__ void k_peer_barrier(VrPeerFlags f, uint32_t self, uint32_t n, uint32_t epoch) {
+// the system-scope fence, so a GPU that sees the flag also sees them. A peer that never arrives (its host thread failed,
+// or its stream is queued behind this very kernel) must not hang the GPU: after timeout_ns the wait gives up and leaves
+// a mark in word VR_MAX_PEERS of this GPU's array, which vr_group_sync reports.
+__global__ void k_peer_barrier(VrPeerFlags f, uint32_t self, uint32_t n, uint32_t epoch, unsigned long long timeout_ns) {
     const uint32_t q = threadIdx.x;
     if (q < n) {
         __threadfence_system();
         volatile uint32_t* dst = f.flags[q] + self;
         *dst = epoch;
         volatile uint32_t* mine = f.flags[self] + q;
-        while ((int32_t)(*mine - epoch) < 0) __nanosleep(64);
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int32_t)(*mine - epoch) < 0) {
+            __nanosleep(64);
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > timeout_ns) {
+                f.flags[self][VR_MAX_PEERS] = epoch;
+                break;
+            }
+        }
         __threadfence_system();
     }
 }
@@ -1879,7 +1891,7 @@ void vrk_add_accum(cudaStream_t st, float4* dst, const float4* src, uint64_t npi
 }
 void vrk_peer_barrier(cudaStream_t st, const VrPeerFlags& f, uint32_t self, uint32_t n, uint32_t epoch) {
     VR_COUNT(1);
-    k_peer_barrier<<<1, 32, 0, st>>>(f, self, n, epoch);
+    k_peer_barrier<<<1, 32, 0, st>>>(f, self, n, epoch, 10ull * 1000 * 1000 * 1000);
 }
 void vrk_path(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrFrameColorOut& frame_color,
               float4* accum, uchar4* rgba8, VrWorkCounters* wc, float* tab, uint32_t nmax, int sum_mode) {

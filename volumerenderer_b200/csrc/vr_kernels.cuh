@@ -31,8 +31,8 @@ struct VrFrameColorOut {
     uint32_t npeers;
 };
 
-// flag arrays of the in-process cross-GPU barrier (vr_group): flags[g] is GPU g's array of VR_MAX_PEERS epochs, mapped
-// into every GPU of the group through CUDA peer access
+// flag arrays of the in-process cross-GPU barrier (vr_group): flags[g] is GPU g's array of VR_MAX_PEERS epochs (+ one word
+// that a timed-out wait sets), mapped into every GPU of the group through CUDA peer access
 struct VrPeerFlags {
     uint32_t* flags[VR_MAX_PEERS];
 };

@@ -251,9 +251,10 @@ class VolumeRenderer:
         self._check(self._L.vr_set_eval_side_stream(self._ctx, int(bool(enabled))))
 
     # ------------------------------------------------------------------ sample-parallel progressive mode
-    def set_frame_step(self, step):
-        """vr_set_frame_step: draw_frame advances frameCount by `step` (rank r of G: frameCount = r, step = G)."""
-        self._check(self._L.vr_set_frame_step(self._ctx, int(step)))
+    def set_frame_step(self, first, step):
+        """vr_set_frame_step: the next draw_frame is frame `first` (0: as usual), later ones advance frameCount by `step`
+        (rank r of G: first = r + 1, step = G)."""
+        self._check(self._L.vr_set_frame_step(self._ctx, int(first), int(step)))
 
     def set_accumulate_mode(self, mode):
         """'average' (the reference's running average) or 'sum' (float sum of the frame colours; include/vr.h)."""
