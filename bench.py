@@ -12,8 +12,10 @@ samples with non-zero density x lights) divided by the frame time; ms
   python bench.py --impl reference [...]                          the reference's shader source on the host cores
 
 N>1 partitions the frame into row bands balanced by a measured per-row cost (grid and lights replicated, light
-generation repeated on every rank) and exchanges the bands' frame colours over NCCL inside the timed region: strong
-scaling.
+generation repeated on every rank). Pixels are independent, so the path has no exchange step: every rank keeps the
+progressive accumulator of its band (--exchange none, the default) and the bands meet in host memory, each rank copying
+its rows over its own PCIe link (the e2e leg). --exchange peer|nccl additionally leaves the whole image on every GPU after
+every frame (fused peer stores from the resolve kernel, or one grouped NCCL send/recv). Strong scaling.
 """
 import argparse
 import ctypes
@@ -138,12 +140,16 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------ CPU arms
-def cpu_workload(cfg, frame):
-    """Grid, UBO and the frame's light list for the CPU arms (built with the product's host-side grid writer and the
-    oracle's light generation; neither is inside a timed region)."""
-    import volumerenderer_b200 as vr
+def cpu_workload(cfg, frame, ref=None):
+    """Grid, UBO and the frame's light list for the CPU arms (neither is inside a timed region). With oracle/_ref present
+    the grid comes from the reference's vendored NanoVDB builder (the same voxels; the reference arm then maps no product
+    library at all), else from the product's host-side grid writer."""
     from oracle import pyoracle
-    grid = vr.build_cloud_grid(cfg["n"])
+    if ref is not None:
+        grid = ref.make_cloud(cfg["n"])
+    else:
+        import volumerenderer_b200 as vr
+        grid = vr.build_cloud_grid(cfg["n"])
     orc = pyoracle.Oracle()
     u = pyoracle.default_ubo(cfg["W"], cfg["H"], frameCount=frame, maxLights=cfg["max_lights"])
     lights, count, _, _ = orc.light_gen(grid, u, (cfg["gx"], 1, 1), 0)
@@ -179,8 +185,8 @@ def reference_arm(args, cfg):
     oracle/_ref) on all host threads; falls back to the oracle port when oracle/_ref was never built."""
     from oracle import pyoracle
     threads = os.cpu_count() or 1
-    grid, orc, u, lights = cpu_workload(cfg, 1)
     ref = pyoracle.Ref() if pyoracle.have_ref() else None
+    grid, orc, u, lights = cpu_workload(cfg, 1, ref)
     kind = "reference" if ref is not None else "port"
     algo = cfg["algo"]
     t_probe = run_cpu(kind, orc, ref, grid, u, algo, lights, 32, threads)
@@ -202,12 +208,49 @@ def reference_arm(args, cfg):
         "impl": "reference", "metric": "light_pixel_contributions_per_s", "value": value, "unit": "contributions/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": cfg["desc"], "pixel_stride": stride},
-        "cpu_baseline": {"value": value, "unit": "contributions/s", "cores": threads, "kind": kind, "sample": sample},
+        "config": {"workload": cfg["desc"]},
+        "cpu_baseline": {"value": value, "unit": "contributions/s", "cores": threads, "kind": kind, "sample": sample,
+                         "pixel_stride": stride},
         "e2e": {"value": value, "unit": "contributions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "full_frame_ms_equiv": dt * 1e3 * stride * stride,
     }
     print(json.dumps(line), flush=True)
+
+
+class SharedHostImages:
+    """N > 1: `count` (H, W, 4) float32 images in POSIX shared memory that every rank maps and page-locks
+    (cudaHostRegister), so that each GPU copies the rows it rendered straight into ONE host image over its own PCIe link."""
+
+    def __init__(self, count, H, W, rank, dist):
+        import torch
+        from multiprocessing import resource_tracker, shared_memory
+        self.nbytes = count * H * W * 16
+        box = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=self.nbytes)
+            box[0] = self.shm.name
+        dist.broadcast_object_list(box, src=0)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=box[0])
+            try:   # only the creating rank unlinks the segment
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.owner = rank == 0
+        self.images = np.ndarray((count, H, W, 4), np.float32, buffer=self.shm.buf)
+        self.ptr = self.images.ctypes.data
+        rc = torch.cuda.cudart().cudaHostRegister(self.ptr, self.nbytes, 0)
+        if int(rc) != 0:
+            raise RuntimeError(f"cudaHostRegister failed ({rc})")
+
+    def close(self, dist):
+        import torch
+        torch.cuda.cudart().cudaHostUnregister(self.ptr)
+        self.images = None
+        dist.barrier()
+        self.shm.close()
+        if self.owner:
+            self.shm.unlink()
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -218,7 +261,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
-    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"], help="N>1 tile exchange")
+    ap.add_argument("--exchange", default="none", choices=["none", "auto", "peer", "nccl"],
+                    help="N>1: none = every rank keeps the accumulator of its band (default); peer/nccl/auto = all-gather of the "
+                         "bands' frame colours every frame (whole image on every GPU)")
+    ap.add_argument("--balance-rounds", type=int, default=6, help="N>1: rounds of measured feedback for the band split")
     ap.add_argument("--eval-variant", type=int, default=8, choices=[0, 1, 2, 3, 8],
                     help="evaluation kernel for point/ray lists: 8 = ray-segment kernel (default), 2 = exact packed kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
@@ -285,9 +331,13 @@ def main():
         cost = tiles.row_costs(r.row_sample_counts(), tm["march_ms"], tm["eval_ms"])
         set_bands(tiles.balanced_row_bands(cost, world))
         fc_t = tiles.frame_color_as_tensor(r)
-        # measured feedback (untimed): each rank reports the device time of its band, the row costs are rescaled
-        for _ in range(3):
+        # measured feedback (untimed): each rank reports the device time of its band, the row costs are rescaled; the
+        # per-band time is a staircase in CTA waves, so the split need not improve monotonically: the best one is kept
+        best = (float("inf"), bands)
+        for rnd in range(args.balance_rounds + 1):
             r.reset_accumulation()
+            r.draw_frame(algo, tile)            # the first frame of a new split sizes buffers: not measured
+            r.sync()
             r.timings_sum(reset=True)
             for _ in range(3):
                 r.draw_frame(algo, tile)
@@ -295,15 +345,23 @@ def main():
             mine = torch.tensor([ts["total_ms"] / max(1, nf)], dtype=torch.float64, device="cuda")
             allms = [torch.zeros_like(mine) for _ in range(world)]
             dist.all_gather(allms, mine)
-            cost = tiles.refine_row_costs(cost, bands, [float(x) for x in allms])
+            ms = [float(x) for x in allms]
+            if max(ms) < best[0]:
+                best = (max(ms), bands)
+            if rnd == args.balance_rounds:
+                break
+            cost = tiles.refine_row_costs(cost, bands, ms)
             set_bands(tiles.balanced_row_bands(cost, world))
+        set_bands(best[1])
         r.reset_accumulation()
 
     # N>1: the rank's band goes to every GPU straight from the resolve kernel (peer stores over NVLink into torch
     # symmetric memory) when that is available, else as one grouped NCCL send/recv of the 4 B/pixel frame colours
     peer_fc = None
     exchange = "none"
-    if world > 1:
+    if world > 1 and args.exchange == "none":
+        exchange = "none (pixels are independent: every GPU keeps the progressive accumulator of its band; bands meet in host memory)"
+    elif world > 1:
         exchange = "nccl grouped send/recv of frame colours"
         if args.exchange in ("auto", "peer"):
             try:
@@ -327,7 +385,7 @@ def main():
         # own band: light generation + gather + progressive average; the other ranks' rows arrive as frame colours
         # (4 B/pixel, one grouped NCCL send/recv on the kernels' stream) and are averaged in locally
         r.draw_frame(algo, tile)
-        if world > 1:
+        if world > 1 and args.exchange != "none":
             tiles.exchange_rows_p2p(fc_t, bands)
             for t in others:
                 r.accumulate_frame_color(t)
@@ -400,9 +458,11 @@ def main():
     e2e_frames = [0]
 
     # N > 1: the volume crosses PCIe once per node (rank 0), an NCCL broadcast replicates it over NVLink and every rank
-    # installs it from device memory (tiles.ReplicatedGrid / vr_set_grid_device); the image comes back on rank 0
+    # installs it from device memory (tiles.ReplicatedGrid / vr_set_grid_device); every rank returns the rows it rendered
+    # over its own PCIe link into one host image that all ranks map (shared, page-locked memory)
     replicated = tiles.ReplicatedGrid(r, grid.nbytes) if world > 1 else None
     grid_header = grid_host[:4096].copy()
+    shared = SharedHostImages(2, H, W, rank, dist) if world > 1 else None
 
     def e2e_step():
         if replicated is not None:
@@ -411,9 +471,11 @@ def main():
             r.set_grid(grid_host)                   # H2D: the NanoVDB buffer (binding 2)
         r.ubo = r.ubo                               # H2D: the 96-byte UBO (kernel parameter)
         step()
-        if rank == 0:
-            r.read_accum_async(out_host[e2e_frames[0] & 1])   # D2H: linear float image (waits for the previous frame's copy)
-            e2e_frames[0] += 1
+        if shared is not None:   # D2H: this rank's rows of the linear float image (waits for the previous frame's copy)
+            r.read_accum_tile_async(tile, shared.images[e2e_frames[0] & 1])
+        else:
+            r.read_accum_async(out_host[e2e_frames[0] & 1])
+        e2e_frames[0] += 1
 
     for _ in range(2):
         e2e_step()
@@ -437,27 +499,36 @@ def main():
         e2e_s, e2e_ceff = float(tmax[0]), float(tsum[1])
     e2e_value = e2e_ceff / e2e_s
 
-    # ---- N>1: the tiled, exchanged result must equal a whole-frame render of the same frames (untimed check)
+    # ---- N>1: the bands, gathered in host memory by the ranks' own read-backs, must equal a whole-frame render of the
+    # same frames bit for bit (untimed check); with an all-gather exchange every rank's device image must as well
     verified = None
     if world > 1:
-        def render(n_frames, tiled):
-            r.reset_accumulation()
-            for _ in range(n_frames):
-                if tiled:
-                    step()
-                else:
-                    if peer_fc is not None:
-                        r.set_frame_color_peers(None, [])
-                    r.draw_frame(algo)
-            r.sync()
-            return r.read_accum(), r.read_image_rgba8()
-        a_t, i_t = render(3, True)
+        nfr = 3
+        r.reset_accumulation()
+        for _ in range(nfr):
+            step()
+        r.read_accum_tile_async(tile, shared.images[0])
+        r.read_wait()
+        band_i = r.read_image_rgba8()[bands[rank][0]:bands[rank][0] + bands[rank][1]]
+        full_t = (r.read_accum(), r.read_image_rgba8()) if args.exchange != "none" else None
         barrier()
-        a_f, i_f = render(3, False)
-        ok = torch.tensor([1 if (np.array_equal(a_t, a_f) and np.array_equal(i_t, i_f)) else 0], device="cuda")
+        if peer_fc is not None:
+            r.set_frame_color_peers(None, [])
+        r.reset_accumulation()
+        for _ in range(nfr):
+            r.draw_frame(algo)
+        r.sync()
+        a_f, i_f = r.read_accum(), r.read_image_rgba8()
+        good = np.array_equal(i_f[bands[rank][0]:bands[rank][0] + bands[rank][1]], band_i)
+        if rank == 0:
+            good = good and np.array_equal(shared.images[0], a_f)     # the image the N read-backs assembled on the host
+        if full_t is not None:
+            good = good and np.array_equal(full_t[0], a_f) and np.array_equal(full_t[1], i_f)
+        ok = torch.tensor([1 if good else 0], device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         verified = bool(int(ok))
         barrier()
+        shared.close(dist)
 
     if rank == 0:
         # ---- roofline of the dominant kernel (k_eval): FP32-issue bound, measured live with CUDA events
@@ -473,13 +544,22 @@ def main():
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         samples_per_step = evals / max(1, c["eval_lights"]) / args.steps
         alg_bytes = samples_per_step * 20.0 + c["eval_lights"] * 16.0   # 16 B sample in + 4 B out, 16 B per light
-        traffic = None
+        # measured DRAM traffic of one launch of the dominant kernel, from a committed ncu --set full capture. The entry is
+        # stamped with the library version it was captured on: after a kernel change the stamp no longer matches the built
+        # library and the figure is dropped (null + reason) instead of silently going stale.
+        traffic, traffic_note = None, None
         try:
             with open(os.path.join(ROOT, "profiles", "eval_traffic.json")) as f:
                 tj = json.load(f)
-                traffic = tj.get(args.workload if args.eval_variant == 8 else f"{args.workload}@{args.eval_variant}")
-        except Exception:
-            pass
+            ent = tj.get(args.workload if args.eval_variant == 8 else f"{args.workload}@{args.eval_variant}")
+            built = vr.load().vr_version().decode()
+            if isinstance(ent, dict) and ent.get("version") == built:
+                traffic, traffic_note = ent["traffic"], f"{ent.get('source', '')} (captured on {ent.get('commit', '?')}, {built})"
+            elif ent is not None:
+                cap = ent.get("version") if isinstance(ent, dict) else "an unstamped round-1 build"
+                traffic_note = f"dropped: captured on {cap}, the built library is {built}"
+        except Exception as e:  # noqa: BLE001
+            traffic_note = f"unavailable: {type(e).__name__}"
         point_kernels = {0: "k_eval<point,8>", 1: "k_eval_point2<8>", 2: "k_eval_point3<8,3,2>", 3: "k_eval_point3<6,4,2>",
                          8: "k_eval_seg<2,point,16> (+ k_eval_seg<2,point,8> on odd segments, k_eval_point3<8,3,2,list> on leftovers and near-light segments)"}
         kernel_name = point_kernels[args.eval_variant] if algo in ("point", "ray") else {0: "k_eval<sphere,8>", 8: "k_eval_seg<2,sphere,8> (+ k_eval_sphere2<8,list> on leftovers and near-light segments)"}.get(args.eval_variant, "k_eval_sphere2<8>")
@@ -493,7 +573,7 @@ def main():
             "flop_per_eval": flop, "evals_per_s": evals / eval_s if eval_s > 0 else 0.0,
             "mufu_rcp_peak_per_s": peak_rcp * 1e12, "mufu_per_eval": mufu_per_eval,
             "mufu_frac": (evals / eval_s) * mufu_per_eval / (peak_rcp * 1e12) if peak_rcp and eval_s > 0 else None,
-            "traffic": traffic,
+            "traffic": traffic, "traffic_source": traffic_note,
             "hbm": {"bound": "hbm", "achieved": alg_bytes / (eval_s / args.steps) / 1e9 if eval_s > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "frac": (alg_bytes / (eval_s / args.steps) / 1e9) / hbm_peak if eval_s > 0 else None,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (of fallback)",
@@ -521,6 +601,7 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "contributions/s", "ms_per_step": e2e_s * 1e3 / args.steps,
                     "h2d_bytes_per_step": int(grid.nbytes) + 96 * world, "d2h_bytes_per_step": int(W * H * 16),
+                    "d2h": "every rank copies the rows it rendered into one shared, page-locked host image" if world > 1 else "rank 0",
                     "nvlink_broadcast_bytes_per_step": int(grid.nbytes) * (world - 1) if world > 1 else 0},
             "gpu_launches": int(launches),
             "roofline": roofline,

@@ -147,7 +147,7 @@ struct vr_ctx {
     DevBuf<VrSample> samples;
     DevBuf<float> contrib;
     // ray-segment evaluation (eval_variant 8): segment table + index list of the exact kernel, rebuilt with the march
-    DevBuf<uint32_t> seg_first, seg_pix, seg_flag, seg16_first, seg16_pix, seg16_flag, seg_list, seg_base;
+    DevBuf<uint32_t> seg_first, seg_pix, seg_flag, seg16_first, seg16_pix, seg16_flag, seg_list, seg_list2, seg_base, seg_sched;
     DevBuf<uint8_t> seg_flags;
     unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
     bool seg_valid = false;                    // tables match the cached march
@@ -168,6 +168,7 @@ struct vr_ctx {
     struct Scalars {
         unsigned long long nsamples, neval, S_ref, S_eff;
         uint32_t light_count, overflow;
+        unsigned long long seg_stalled;
     };
     Scalars* scalars_host = nullptr;
     cudaEvent_t ev_scalars = nullptr;
@@ -380,6 +381,7 @@ int enqueue_scalars(vr_ctx* c, cudaStream_t st, bool have_march) {
     if (have_march) VR_CUDA(c, cudaMemcpyAsync(&h->S_ref, c->wc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaMemcpyAsync(&h->light_count, &c->counter->lightCount, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaMemcpyAsync(&h->overflow, c->expand_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    VR_CUDA(c, cudaMemcpyAsync(&h->seg_stalled, c->seg_counts + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaEventRecord(c->ev_scalars, st));
     c->counters_pending = true;
     c->counters_have_march = have_march;
@@ -395,6 +397,7 @@ int finalize_counters(vr_ctx* c) {
         c->last_counters.S_eff = c->cached_S[1] = h.S_eff;
     }
     if (h.overflow) return fail(c, VR_E_STATE, "internal: the expanded light list overflowed its buffer");
+    if (h.seg_stalled) return fail(c, VR_E_STATE, "internal: a slice-order wait of the segment kernel gave up in an earlier frame");
     if (c->last_algo == VR_ALGO_PATH) {
         c->last_counters.E = h.S_eff;
         return VR_OK;
@@ -414,7 +417,8 @@ int finalize_counters(vr_ctx* c) {
 
 extern "C" {
 
-const char* vr_version(void) { return "libvr 0.1 (sm_100a)"; }
+// bump the kernel revision (kN) whenever an evaluation kernel changes: profiles/eval_traffic.json entries are stamped with it
+const char* vr_version(void) { return "libvr 0.2-k1 (sm_100a)"; }
 
 const char* vr_last_error(const vr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
@@ -550,6 +554,8 @@ int vr_destroy(vr_ctx* c) {
     c->seg_first.release();
     c->seg_pix.release();
     c->seg_list.release();
+    c->seg_list2.release();
+    c->seg_sched.release();
     c->seg_base.release();
     c->seg_flag.release();
     c->seg16_first.release();
@@ -1087,11 +1093,17 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             VR_CUDA(c, c->seg16_flag.reserve(nreal / 16 + 1));
             VR_CUDA(c, c->seg_flags.reserve(nreal / 8 + 2));
             VR_CUDA(c, c->seg_list.reserve(nreal + 1));
+            VR_CUDA(c, c->seg_list2.reserve(nreal + 1));
+            VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 512 + 4)));  // per kernel instance: ticket + one word per chunk
             VR_CUDA(c, c->seg_base.reserve(npix + 1));
         }
         sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
         sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
-        sl.list = c->seg_list.p, sl.counts = c->seg_counts;
+        sl.list = c->seg_list.p, sl.list2 = c->seg_list2.p, sl.counts = c->seg_counts;
+        {
+            const uint64_t per = nreal / 8 / 512 + 4;  // chunks of SEG_PER_CTA = 512 entries, at most nreal / 8 entries
+            sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
+        }
         sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
         sl.list_capacity = (uint32_t)nreal;
         if (!c->seg_valid) {
@@ -1575,10 +1587,10 @@ int vr_set_eval_near_distance(vr_ctx* c, float distance) {
 int vr_get_eval_segment_counts(vr_ctx* c, uint64_t out[3]) {
     if (!c || !out) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
-    unsigned long long h[6] = {0, 0, 0, 0, 0, 0};
+    unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     VR_CUDA(c, cudaMemcpyAsync(h, c->seg_counts, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    out[0] = h[5], out[1] = h[1], out[2] = h[2];  // h[5] = 2 * (16-sample entries) + (8-sample entries)
+    out[0] = h[5], out[1] = h[1], out[2] = h[2] + h[7];  // h[5] = 2 * (16-sample entries) + (8-sample entries); h[7]: handed over
     return check_stream(c);
 }
 

@@ -106,6 +106,11 @@ struct vr_group {
     VrPeerFlags peer_flags{};
     uint32_t epoch = 0, parity = 0;
     int exchange = VR_EXCHANGE_NONE;
+    // A device listed more than once (bands on one GPU): its contexts' streams may share a hardware queue, where a
+    // spinning barrier kernel would block the very peer it waits for. Such groups order the exchange with CUDA events
+    // (recorded after each GPU's resolve, waited for by every other GPU's stream) in two host phases instead.
+    bool shared_device = false;
+    std::vector<cudaEvent_t> stored[2];        // per parity, per GPU: its band's frame colours are stored everywhere
     uint8_t* staging[2] = {nullptr, nullptr};  // the volume on GPU 0, source of the GPU-to-GPU replication
     uint64_t staging_cap[2] = {0, 0};
     std::vector<cudaEvent_t> staged_read[2];   // per GPU: its copy out of staging[k] is done
@@ -209,6 +214,15 @@ void complement(const vr_group* g, uint32_t i, vr_tile out[2], int* n) {
     if (b.y0 + b.h < g->height) out[(*n)++] = vr_tile{0, b.y0 + b.h, g->width, g->height - (b.y0 + b.h)};
 }
 
+// the rows GPU i received: progressive average from its local copy of the frame colours
+int accumulate_rest(vr_group* g, uint32_t i) {
+    vr_tile rest[2];
+    int nrest = 0, rc = VR_OK;
+    complement(g, i, rest, &nrest);
+    for (int k = 0; k < nrest && rc == VR_OK; k++) rc = vr_accumulate_frame_color(g->ctx[i], &rest[k]);
+    return rc;
+}
+
 // one tiled frame on GPU i (worker thread i): own band with peer stores, barrier, the rest of the image from the local copy
 int frame_on(vr_group* g, uint32_t i, vr_algo algo, uint32_t parity, uint32_t epoch) {
     vr_ctx* c = g->ctx[i];
@@ -227,12 +241,12 @@ int frame_on(vr_group* g, uint32_t i, vr_algo algo, uint32_t parity, uint32_t ep
     }
     rc = vr_render_frame(c, algo, g->n > 1 ? &g->band[i] : nullptr);
     if (rc != VR_OK || g->n == 1) return rc;
+    if (g->shared_device) {  // second phase (after every GPU recorded its event): vr_group_render_frame
+        cudaSetDevice(g->dev[i]);
+        return cudaEventRecord(g->stored[parity][i], g->stream[i]) == cudaSuccess ? VR_OK : VR_E_CUDA;
+    }
     vrk_peer_barrier(g->stream[i], g->peer_flags, i, g->n, epoch);
-    vr_tile rest[2];
-    int nrest = 0;
-    complement(g, i, rest, &nrest);
-    for (int k = 0; k < nrest && rc == VR_OK; k++) rc = vr_accumulate_frame_color(c, &rest[k]);
-    return rc;
+    return accumulate_rest(g, i);
 }
 
 }  // namespace
@@ -259,6 +273,9 @@ int vr_group_destroy(vr_group* g) {
             cudaFree(g->flags[i]);
         }
     if (!g->dev.empty()) cudaSetDevice(g->dev[0]);
+    for (int p = 0; p < 2; p++)
+        for (cudaEvent_t e : g->stored[p])
+            if (e) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) {
         if (g->staging[k]) cudaFree(g->staging[k]);
         for (cudaEvent_t e : g->staged_read[k])
@@ -330,10 +347,14 @@ int vr_group_create(const int* cuda_devices, uint32_t n, vr_group** out) {
         }
         g->peer_flags.flags[i] = g->flags[i];
     }
-    for (int k = 0; k < 2; k++) g->staged_read[k].assign(n, nullptr);
+    for (int k = 0; k < 2; k++) g->staged_read[k].assign(n, nullptr), g->stored[k].assign(n, nullptr);
     for (uint32_t i = 0; i < n; i++) {
         cudaSetDevice(g->dev[i]);
-        for (int k = 0; k < 2; k++) cudaEventCreateWithFlags(&g->staged_read[k][i], cudaEventDisableTiming);
+        for (int k = 0; k < 2; k++) {
+            cudaEventCreateWithFlags(&g->staged_read[k][i], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&g->stored[k][i], cudaEventDisableTiming);
+        }
+        for (uint32_t j = 0; j < i; j++) g->shared_device = g->shared_device || g->dev[i] == g->dev[j];
     }
     for (uint32_t i = 0; i < n; i++) {
         Worker* w = new (std::nothrow) Worker();
@@ -462,7 +483,14 @@ int vr_group_render_frame(vr_group* g, vr_algo algo) {
     if (rc != VR_OK) return rc;
     const uint32_t parity = g->parity, epoch = ++g->epoch;
     g->parity ^= 1u;
-    return on_all(g, [=](uint32_t i) { return frame_on(g, i, algo, parity, epoch); });
+    rc = on_all(g, [=](uint32_t i) { return frame_on(g, i, algo, parity, epoch); });
+    if (rc != VR_OK || g->n == 1 || g->exchange != VR_EXCHANGE_ALLGATHER || !g->shared_device) return rc;
+    return on_all(g, [=](uint32_t i) {
+        cudaSetDevice(g->dev[i]);
+        for (uint32_t j = 0; j < g->n; j++)
+            if (j != i && cudaStreamWaitEvent(g->stream[i], g->stored[parity][j], 0) != cudaSuccess) return (int)VR_E_CUDA;
+        return accumulate_rest(g, i);
+    });
 }
 
 int vr_group_sync(vr_group* g) {

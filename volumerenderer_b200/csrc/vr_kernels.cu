@@ -595,7 +595,8 @@ __global__ void __launch_bounds__(EVAL_THREADS) k_eval_point2(const VrSample* __
 // evaluations: FMA pipe 17 cycles, XU pipe 16 cycles per evaluation.
 // LIST: the kernel evaluates samples[list[i]], i < *nlist_dev (the leftovers and near-light segments of the ray-segment
 // kernel); the launch is sized by an upper bound of the list length and CTAs beyond it leave at once.
-template <int S, bool LIST>
+// STRIDE (LIST only): the CTAs of a fixed small grid walk the list in strides (the hand-over list, normally empty)
+template <int S, bool LIST, bool STRIDE = false>
 __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample* __restrict__ samples, uint64_t nsamples,
                                                                    const uint32_t* __restrict__ list,
                                                                    const unsigned long long* __restrict__ nlist_begin_dev,
@@ -614,7 +615,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
-    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
     const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -622,10 +622,13 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    uint32_t it = 0;  // tiles consumed so far by this CTA: stage = it & 1, mbarrier phase parity = (it >> 1) & 1
+    uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    do {
     if (tid == 0 && ntiles > 0) {
         const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
-        mbar_expect_tx(&bar[0], cnt * 32u);
-        tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
+        mbar_expect_tx(&bar[it & 1], cnt * 32u);
+        tma_bulk_g2s(&stage[it & 1][0], lights2, cnt * 32u, &bar[it & 1]);
     }
     float2 nsx[P], nsy[P], nsz[P], acc[P];
     float sw[S];
@@ -640,15 +643,15 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
         acc[p] = make_float2(0.f, 0.f);
     }
     const float2 nR = make_float2(-radius, -radius);
-    for (uint64_t tl = 0; tl < ntiles; tl++) {
-        const uint32_t buf = (uint32_t)(tl & 1);
+    for (uint64_t tl = 0; tl < ntiles; tl++, it++) {
+        const uint32_t buf = it & 1;
         if (tid == 0 && tl + 1 < ntiles) {
             const uint64_t first = (tl + 1) * EVAL2_TILE;
             const uint32_t cnt = (uint32_t)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
             mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
             tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * first, cnt * 32u, &bar[buf ^ 1]);
         }
-        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
+        mbar_wait(&bar[buf], (it >> 1) & 1);
         const uint64_t first = tl * EVAL2_TILE;
         const int cnt = (int)((nlights - first) < EVAL2_TILE ? (nlights - first) : EVAL2_TILE);
         const float4* __restrict__ L = stage[buf];
@@ -685,6 +688,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, 3) k_eval_sphere2(const VrSample
         if (i0 < nsamples) out[LIST ? (uint64_t)list[i0] : i0] = sw[2 * p] * acc[p].x;
         if (i1 < nsamples) out[LIST ? (uint64_t)list[i1] : i1] = sw[2 * p + 1] * acc[p].y;
     }
+    base += (uint64_t)gridDim.x * (EVAL_THREADS * S);
+    } while (STRIDE && base < nsamples);
 }
 
 // ---- speculative variant: no per-evaluation guard in the main pass -------------------------------------------------
@@ -759,7 +764,8 @@ __device__ __forceinline__ void eval_pass_packed(float4 (&stage)[2][2 * EVAL2_TI
 }
 
 // LIST: samples[list[i]], i < *nlist_dev, as in k_eval_sphere2
-template <int S, int MINB, int UNROLL, bool LIST = false>  // S samples per thread (even), MINB resident CTAs per SM
+// STRIDE (LIST only): the CTAs of a fixed small grid walk the list in strides (the hand-over list, normally empty)
+template <int S, int MINB, int UNROLL, bool LIST = false, bool STRIDE = false>  // S samples per thread (even), MINB resident CTAs per SM
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSample* __restrict__ samples, uint64_t nsamples,
                                                               const uint32_t* __restrict__ list,
                                                               const unsigned long long* __restrict__ nlist_begin_dev,
@@ -778,13 +784,15 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     const uint32_t tid = threadIdx.x;
-    const uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
+    uint64_t base = (uint64_t)blockIdx.x * (EVAL_THREADS * S);
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    uint32_t it = 0;
+    do {
     float2 nsx[P], nsy[P], nsz[P], acc[P];
     float sw[S];
 #pragma unroll
@@ -798,7 +806,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
         sw[2 * p] = a.w, sw[2 * p + 1] = b.w;
         acc[p] = make_float2(0.f, 0.f);
     }
-    uint32_t it = 0;
     float dmin = 3.0e38f;
     eval_pass_packed<P, false, UNROLL>(stage, bar, lights2, nlights, it, nsx, nsy, nsz, acc, dmin);
     if (__syncthreads_or(!(dmin >= 0.0001f))) {  // also true for a NaN d2 (non-finite input)
@@ -813,6 +820,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
         if (i0 < nsamples) out[LIST ? (uint64_t)list[i0] : i0] = sw[2 * p] * acc[p].x;
         if (i1 < nsamples) out[LIST ? (uint64_t)list[i1] : i1] = sw[2 * p + 1] * acc[p].y;
     }
+    base += (uint64_t)gridDim.x * (EVAL_THREADS * S);
+    } while (STRIDE && base < nsamples);
 }
 
 // ---- ray-segment variant: eight samples of one camera ray share the per-light geometry ----------------------------------
@@ -951,19 +960,27 @@ __global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* _
     }
 }
 
-// the flagged entries of a segment table go onto the exact kernel's list (behind the leftovers), before the evaluation
-// starts: the exact kernel can then run next to the segment kernel instead of after it
-template <int LEN>
-__global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl) {
-    const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
-    const uint64_t e = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+// the flagged entries of the segment tables go onto the exact kernel's list (behind the leftovers), before the evaluation
+// starts: the exact kernel can then run next to the segment kernel instead of after it. One launch for both tables: the
+// first blocks16 thread blocks walk the 16-sample table, the rest the 8-sample table.
+__global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl, uint32_t blocks16) {
+    const bool t16 = blockIdx.x < blocks16;
+    const uint64_t nseg = t16 ? sl.counts[4] : sl.counts[0];
+    const uint64_t e = (uint64_t)(t16 ? blockIdx.x : blockIdx.x - blocks16) * 256 + threadIdx.x;
     if (e >= nseg) return;
-    const uint32_t fi = (LEN == 16 ? sl.seg16_flag : sl.seg_flag)[e];
-    if (!(*sl.flag_all != 0u || sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0))) return;
-    const uint32_t first = (LEN == 16 ? sl.seg16_first : sl.seg_first)[e];
-    const unsigned long long slot = atomicAdd(&sl.counts[2], (unsigned long long)LEN);
-    for (int k = 0; k < LEN; k++)
+    const uint32_t fi = (t16 ? sl.seg16_flag : sl.seg_flag)[e];
+    if (!(*sl.flag_all != 0u || sl.flags[fi] != 0 || (t16 && sl.flags[fi + 1] != 0))) return;
+    const uint32_t first = (t16 ? sl.seg16_first : sl.seg_first)[e];
+    const uint32_t len = t16 ? 16u : 8u;
+    const unsigned long long slot = atomicAdd(&sl.counts[2], (unsigned long long)len);
+    for (uint32_t k = 0; k < len; k++)
         if (slot + k < sl.list_capacity) sl.list[slot + k] = first + k;
+}
+// start of an evaluation pass: the exact kernel's list restarts from the leftovers, nothing handed over yet, no give-up flag
+__global__ void k_seg_begin(VrSegLists sl) {
+    sl.counts[2] = sl.counts[1];
+    sl.counts[7] = 0;  // (counts[6], the stall mark of k_eval_seg, is never cleared: it is a bug report)
+    *sl.flag_all = 0u;
 }
 
 __device__ __forceinline__ float2 neg2(const float2 v) { return make_float2(-v.x, -v.y); }  // folds into the operand modifier
@@ -1001,22 +1018,75 @@ __device__ __forceinline__ float2 seg_dist2(const float2 l2, const float2 nR) {
 
 // LEN = 8: one segment per half; LEN = 16: two consecutive segments of the same pixel per half (table sl.seg16_*), so the
 // per-light geometry is shared by 16 samples; their weights are read again at the end instead of held in registers.
+//
+// Work distribution. A chunk is SEG_PER_CTA table entries, and every sample's light sum is DEFINED as the sum over
+// SEG_SPLIT consecutive slices of the light list, added in slice order: out = (((w*S0) + w*S1) + w*S2) + w*S3. A "full"
+// unit is one CTA that walks all slices of a chunk one after the other (entries stay in registers, the partial result is
+// accumulated in `out`); a "slice" unit is one CTA per (chunk, slice). CTAs take units from a ticket counter in the order
+// they start: first the full units of all chunks but the last `slots` (one resident wave), then the slice units of those
+// last chunks, slice 0 first. So the end of the kernel is made of units a quarter as long, and the GPU drains evenly: the
+// tail of a launch whose chunks fill 3.4 waves (one of eight GPUs' bands) costs a quarter of a CTA time instead of a
+// whole one. Slice units of a chunk add to `out` in slice order (a per-chunk counter; a unit's predecessor always holds
+// an earlier ticket, i.e. is running or done: no deadlock), so the result does not depend on which kind of unit
+// produced it -- a tiled render equals the whole frame bit for bit (tests/test_gpu_configs.py).
+constexpr int SEG_SPLIT = 4;
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// wait until *p >= want. The unit waited for always holds an earlier ticket (it is running or done), so this ends; the
+// bound only keeps a bug from hanging the GPU: it leaves a mark (counts[6]) that the host reports.
+__device__ __forceinline__ void wait_slices(const uint32_t* p, uint32_t want, unsigned long long* stalled) {
+    for (uint32_t spin = 0; ld_acquire_u32(p) < want; spin++) {
+        __nanosleep(100);
+        if (spin > (1u << 24)) {
+            atomicExch(stalled, 1ull);
+            break;
+        }
+    }
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// lights per slice: a quarter of the list rounded up to whole pairs (the loop shares one reciprocal between two lights, so
+// slice boundaries must not split the pairs the unsliced list would form), at least 64
+__device__ __forceinline__ uint64_t seg_slice_len(uint64_t nlights) {
+    const uint64_t q = ((nlights + SEG_SPLIT - 1) / SEG_SPLIT + 1) & ~1ull;
+    return q < 64 ? 64 : q;
+}
+
 template <int MINB, bool SPHERE, int LEN>
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                                   const VrSample* __restrict__ samples, VrSegLists sl,
                                                                   const float4* __restrict__ lights2,
                                                                   const unsigned long long* __restrict__ nlights_dev, float rho,
-                                                                  float radius, float* __restrict__ out) {
+                                                                  float radius, float* __restrict__ out, uint32_t slots) {
     const float2 nR = make_float2(-radius, -radius);
     constexpr bool KEEP_W = LEN <= 8;
     const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
     const uint32_t* __restrict__ tab_first = LEN == 16 ? sl.seg16_first : sl.seg_first;
     const uint32_t* __restrict__ tab_pix = LEN == 16 ? sl.seg16_pix : sl.seg_pix;
     const uint32_t* __restrict__ tab_flag = LEN == 16 ? sl.seg16_flag : sl.seg_flag;
-    const uint64_t seg_base = (uint64_t)blockIdx.x * SEG_PER_CTA;
-    if (seg_base >= nseg) return;  // the launch is sized by the capacity, the segment count lives on the device
+    uint32_t* __restrict__ sched = LEN == 16 ? sl.sched16 : sl.sched8;  // [0] ticket counter, [1 + c] slices of chunk c done
     const uint32_t tid = threadIdx.x;
+    __shared__ uint32_t s_unit;
+    if (tid == 0) s_unit = atomicAdd(sched, 1u);
+    __syncthreads();
+    const uint32_t unit = s_unit;
+    const uint32_t nchunks = (uint32_t)((nseg + SEG_PER_CTA - 1) / SEG_PER_CTA);
+    const uint32_t nsliced = nchunks < slots ? nchunks : slots, nfull = nchunks - nsliced;
+    uint32_t chunk = unit, q0 = 0, q1 = SEG_SPLIT;
+    if (unit >= nfull) {
+        const uint32_t r = unit - nfull;
+        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT, q1 = q0 + 1;
+        if (chunk >= nchunks) return;  // the launch is sized by the capacity, the segment count lives on the device
+    }
+    const bool sliced = q1 - q0 == 1;
+    uint32_t* __restrict__ done = sched + 1 + chunk;
+    const uint64_t seg_base = (uint64_t)chunk * SEG_PER_CTA;
     const bool redo_all = *sl.flag_all != 0u;
+    bool idle;
     {
         // a CTA whose entries are all on the exact kernel's list already (near a light, or flag_all) has nothing to evaluate
         bool listed = true;
@@ -1028,9 +1098,17 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 listed = listed && (sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0));
             }
         }
-        if (__syncthreads_and(listed)) return;
+        idle = __syncthreads_and(listed) != 0;
+    }
+    if (idle) {
+        if (sliced && tid == 0) {  // keep the chunk's slice order going for the units behind this one
+            wait_slices(done, q0, &sl.counts[6]);
+            st_release_u32(done, q0 + 1);
+        }
+        return;
     }
     const uint64_t nlights = *nlights_dev;
+    const uint64_t slice_len = seg_slice_len(nlights);
     __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
     __shared__ __align__(8) uint64_t bar[2];
     if (tid == 0) {
@@ -1039,11 +1117,15 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    const uint64_t ntiles = (nlights + EVAL2_TILE - 1) / EVAL2_TILE;
-    if (tid == 0 && ntiles > 0) {
-        const uint32_t cnt = (uint32_t)(nlights < EVAL2_TILE ? nlights : EVAL2_TILE);
-        mbar_expect_tx(&bar[0], cnt * 32u);
-        tma_bulk_g2s(&stage[0][0], lights2, cnt * 32u, &bar[0]);
+    uint32_t it = 0;  // tiles consumed so far: stage = it & 1, mbarrier phase parity = (it >> 1) & 1
+    {
+        const uint64_t lo = (uint64_t)q0 * slice_len;
+        if (tid == 0 && lo < nlights) {  // the first tile of the first slice travels while the entries are loaded
+            const uint64_t left = (nlights - lo < slice_len ? nlights - lo : slice_len);
+            const uint32_t cnt = (uint32_t)(left < EVAL2_TILE ? left : EVAL2_TILE);
+            mbar_expect_tx(&bar[0], cnt * 32u);
+            tma_bulk_g2s(&stage[0][0], lights2 + 2 * lo, cnt * 32u, &bar[0]);
+        }
     }
 
     float2 s[LEN], acc[LEN], A[3], D[3];
@@ -1085,7 +1167,6 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 sv[k] = sk;
                 if (KEEP_W) sw[h][k] = q.w;
             }
-            // near a light (decided by k_flag_near_segments), or samples too far off their line for the bound to hold
             // Segments near a light were put on the exact kernel's list by k_list_flagged already. What is decided here: samples
             // too far off their line for the bound to hold -> hand the entry over as well (rare: a safety net for grid scales
             // where FP32 positions are coarse).
@@ -1096,7 +1177,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         }
 #pragma unroll
         for (int k = 0; k < LEN; k++) {
-            if (h == 0) s[k].x = sv[k], acc[k] = make_float2(0.f, 0.f);
+            if (h == 0) s[k].x = sv[k];
             else s[k].y = sv[k];
         }
 #pragma unroll
@@ -1105,65 +1186,99 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
             else A[c].y = a[c], D[c].y = d[c];
         }
     }
-    for (uint64_t tl = 0; tl < ntiles; tl++) {
-        const uint32_t buf = (uint32_t)(tl & 1);
-        if (tid == 0 && tl + 1 < ntiles) {
-            const uint64_t nxt = (tl + 1) * EVAL2_TILE;
-            const uint32_t cnt = (uint32_t)((nlights - nxt) < EVAL2_TILE ? (nlights - nxt) : EVAL2_TILE);
-            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
-            tma_bulk_g2s(&stage[buf ^ 1][0], lights2 + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
+
+    for (uint32_t q = q0; q < q1; q++) {
+        const uint64_t lo = (uint64_t)q * slice_len;
+        const uint64_t nl = lo < nlights ? (nlights - lo < slice_len ? nlights - lo : slice_len) : 0;  // lights of this slice
+        const float4* __restrict__ src = lights2 + 2 * lo;
+        const uint64_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
+#pragma unroll
+        for (int k = 0; k < LEN; k++) acc[k] = make_float2(0.f, 0.f);
+        if (q != q0 && tid == 0 && ntiles > 0) {  // (the first slice's first tile is already in flight)
+            const uint32_t cnt = (uint32_t)(nl < EVAL2_TILE ? nl : EVAL2_TILE);
+            mbar_expect_tx(&bar[it & 1], cnt * 32u);
+            tma_bulk_g2s(&stage[it & 1][0], src, cnt * 32u, &bar[it & 1]);
         }
-        mbar_wait(&bar[buf], (uint32_t)((tl >> 1) & 1));
-        const uint64_t lo = tl * EVAL2_TILE;
-        const int cnt = (int)((nlights - lo) < EVAL2_TILE ? (nlights - lo) : EVAL2_TILE);
-        const float4* __restrict__ L = stage[buf];
-        int l = 0;
+        for (uint64_t tl = 0; tl < ntiles; tl++, it++) {
+            const uint32_t buf = it & 1;
+            if (tid == 0 && tl + 1 < ntiles) {
+                const uint64_t nxt = (tl + 1) * EVAL2_TILE;
+                const uint32_t cnt = (uint32_t)((nl - nxt) < EVAL2_TILE ? (nl - nxt) : EVAL2_TILE);
+                mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+                tma_bulk_g2s(&stage[buf ^ 1][0], src + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
+            }
+            mbar_wait(&bar[buf], (it >> 1) & 1);
+            const uint64_t tlo = tl * EVAL2_TILE;
+            const int cnt = (int)((nl - tlo) < EVAL2_TILE ? (nl - tlo) : EVAL2_TILE);
+            const float4* __restrict__ L = stage[buf];
+            int l = 0;
 #pragma unroll 1
-        for (; l + 2 <= cnt; l += 2) {
-            const float4 qa = L[2 * l], qb = L[2 * l + 1], ra = L[2 * l + 2], rb = L[2 * l + 3];
-            float2 nb0, h0, nb1, h1;
-            seg_light_geometry(qa, qb, A, D, nb0, h0);
-            seg_light_geometry(ra, rb, A, D, nb1, h1);
-            const float2 W0 = make_float2(qb.z, qb.w), W1 = make_float2(rb.z, rb.w);
+            for (; l + 2 <= cnt; l += 2) {
+                const float4 qa = L[2 * l], qb = L[2 * l + 1], ra = L[2 * l + 2], rb = L[2 * l + 3];
+                float2 nb0, h0, nb1, h1;
+                seg_light_geometry(qa, qb, A, D, nb0, h0);
+                seg_light_geometry(ra, rb, A, D, nb1, h1);
+                const float2 W0 = make_float2(qb.z, qb.w), W1 = make_float2(rb.z, rb.w);
 #pragma unroll
-            for (int k = 0; k < LEN; k++) {
-                const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
-                const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
-                const float2 ab = __fmul2_rn(a, b);
-                const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
-                acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
+                for (int k = 0; k < LEN; k++) {
+                    const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
+                    const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
+                    const float2 ab = __fmul2_rn(a, b);
+                    const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
+                    acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
+                }
+            }
+            if (l < cnt) {  // odd tail of the list (its last slice only: slices are whole pairs)
+                const float4 qa = L[2 * l], qb = L[2 * l + 1];
+                float2 nb0, h0;
+                seg_light_geometry(qa, qb, A, D, nb0, h0);
+                const float2 W0 = make_float2(qb.z, qb.w);
+#pragma unroll
+                for (int k = 0; k < LEN; k++) {
+                    const float2 u0 = __fadd2_rn(s[k], nb0);
+                    const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR);
+                    acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
+                }
+            }
+            __syncthreads();  // everyone is done with stage[buf] before it is refilled two tiles later
+        }
+        // ---- out (+)= w * (this slice's sum), in slice order
+        if (sliced && q > 0) {
+            if (tid == 0) wait_slices(done, q, &sl.counts[6]);
+            __syncthreads();
+        }
+        if (q == 0 || nl > 0) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                if (first[h] == 0xffffffffu || skip[h]) continue;
+#pragma unroll
+                for (int k = 0; k < LEN; k++) {
+                    const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
+                    const float v = w * (h == 0 ? acc[k].x : acc[k].y);
+                    float* o = out + first[h] + k;
+                    *o = q == 0 ? v : __fadd_rn(__ldcg(o), v);
+                }
             }
         }
-        if (l < cnt) {  // odd tail of the list
-            const float4 qa = L[2 * l], qb = L[2 * l + 1];
-            float2 nb0, h0;
-            seg_light_geometry(qa, qb, A, D, nb0, h0);
-            const float2 W0 = make_float2(qb.z, qb.w);
-#pragma unroll
-            for (int k = 0; k < LEN; k++) {
-                const float2 u0 = __fadd2_rn(s[k], nb0);
-                const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR);
-                acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
-            }
+        if (sliced) {
+            __threadfence();
+            __syncthreads();
+            if (tid == 0) st_release_u32(done, q + 1);
         }
-        __syncthreads();
     }
 
-    const uint32_t npush = (redo[0] ? LEN : 0) + (redo[1] ? LEN : 0);
-    unsigned long long slot = 0;
-    if (npush) slot = atomicAdd(&sl.counts[2], (unsigned long long)npush);
+    if (q0 == 0) {  // entries handed over to the exact kernel (second list): announced once per chunk
+        const uint32_t npush = (redo[0] ? LEN : 0) + (redo[1] ? LEN : 0);
+        unsigned long long slot = 0;
+        if (npush) slot = atomicAdd(&sl.counts[7], (unsigned long long)npush);
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-        if (first[h] == 0xffffffffu) continue;
+        for (int h = 0; h < 2; h++) {
+            if (!redo[h]) continue;
 #pragma unroll
-        for (int k = 0; k < LEN; k++) {
-            if (!skip[h]) {
-                const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
-                out[first[h] + k] = w * (h == 0 ? acc[k].x : acc[k].y);
-            }
-            if (redo[h] && slot + k < sl.list_capacity) sl.list[slot + k] = first[h] + k;
+            for (int k = 0; k < LEN; k++)
+                if (slot + k < sl.list_capacity) sl.list2[slot + k] = first[h] + k;
+            slot += LEN;
         }
-        if (redo[h]) slot += LEN;
     }
 }
 
@@ -1762,32 +1877,49 @@ void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned 
     VR_COUNT(1);
     k_build_segments<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(counts, offsets, npix, sl, pairs);
 }
-// the exact kernels over entries [*begin_dev (0 if NULL), *end_dev) of the list; launched over `bound` entries, CTAs beyond
-// the real length leave at once. Small launches use 4 samples per thread: twice the CTAs at half the duration.
-static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* samples, uint64_t bound, bool small, const VrSegLists& sl,
-                              const unsigned long long* begin_dev, const unsigned long long* end_dev, const float4* lights2,
+// the exact kernels over `list[0 .. *end_dev)`; launched over `bound` entries, CTAs beyond the real length leave at once.
+// Small launches use 4 samples per thread: twice the CTAs at half the duration. strided: a fixed small grid whose CTAs
+// walk the list in strides (for the hand-over list, which is normally empty: a launch over its capacity would be
+// thousands of CTAs that only read the length).
+static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* samples, uint64_t bound, bool small, bool strided,
+                              const uint32_t* list, const unsigned long long* end_dev, const float4* lights2,
                               const unsigned long long* nlights_dev, float radius, float* out, unsigned long long* redo_count) {
     if (!bound) return;
     VR_COUNT(1);
     const uint64_t per_cta = (uint64_t)EVAL_THREADS * (small ? 4 : 8);
-    const unsigned grid = (unsigned)((bound + per_cta - 1) / per_cta);
+    unsigned grid = (unsigned)((bound + per_cta - 1) / per_cta);
+    if (strided) {  // (small implied)
+        if (grid > 296u) grid = 296u;
+        if (sphere) k_eval_sphere2<4, true, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, radius, out);
+        else k_eval_point3<4, 3, 2, true, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, out, redo_count);
+        return;
+    }
     if (sphere) {
         if (small)
-            k_eval_sphere2<4, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, radius, out);
+            k_eval_sphere2<4, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, radius, out);
         else
-            k_eval_sphere2<8, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, radius, out);
+            k_eval_sphere2<8, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, radius, out);
     } else if (small) {
-        k_eval_point3<4, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, out, redo_count);
+        k_eval_point3<4, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, out, redo_count);
     } else {
-        k_eval_point3<8, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, sl.list, begin_dev, end_dev, lights2, nlights_dev, out, redo_count);
+        k_eval_point3<8, 3, 2, true><<<grid, EVAL_THREADS, 0, st>>>(samples, 0, list, nullptr, end_dev, lights2, nlights_dev, out, redo_count);
     }
 }
 
+// resident CTAs of a segment kernel on this GPU (the "wave" its tail distribution is planned for)
+template <class K>
+static uint32_t seg_slots(K kernel) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EVAL_THREADS, 0);
+    return (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
+}
 // Evaluation pass of the ray-segment path. Main stream: near-light flags, the flagged entries onto the exact kernel's list,
 // then the big segment kernel. Side stream (lower priority, forked once the list is complete): the odd 8-sample segments and
 // the exact kernel over the list (leftovers + near-light segments) -- independent work whose CTAs fill the SMs that the big
-// kernel's last wave leaves idle. After the join: the exact kernel on whatever the segment kernels handed over themselves
-// (entries whose samples deviate too much from their line; normally none, then every CTA of that launch leaves at once).
+// kernel's end leaves idle. After the join: the exact kernel on whatever the segment kernels handed over themselves
+// (entries whose samples deviate too much from their line; normally none: a small grid-stride launch over the second list).
 void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join, const VrGridDev& g,
                         const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
@@ -1796,16 +1928,24 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
                         unsigned long long* redo_count) {
     if (nsamples == 0) return;
     if (!side) side = st;
-    // the exact kernel's list restarts from the leftovers every frame
-    cudaMemcpyAsync(sl.counts + 2, sl.counts + 1, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
+    static const uint32_t slots16 = seg_slots(k_eval_seg<2, false, 16>), slots8 = seg_slots(k_eval_seg<2, false, 8>),
+                          slots8s = seg_slots(k_eval_seg<2, true, 8>);
     const uint64_t seg_cap = nsamples / SEG_LEN;
     const bool small = nsamples < 40ull * 1000 * 1000;  // short lists: 4 samples per thread, twice the CTAs at half the duration
-    const unsigned grid16 = (unsigned)((seg_cap / 2 + SEG_PER_CTA - 1) / SEG_PER_CTA);
+    const uint64_t cap16 = sphere ? 0 : seg_cap / 2;
     const uint64_t cap8 = sphere ? seg_cap : (seg_cap < npix ? seg_cap : npix);  // point-type: at most one odd segment per pixel
-    const unsigned grid8 = (unsigned)((cap8 + SEG_PER_CTA - 1) / SEG_PER_CTA);
+    // launches are sized by the tables' upper bounds (the lengths live on the device): all full units, or up to `slots`
+    // chunks in SEG_SPLIT slice units each; CTAs whose ticket is beyond the work leave at once
+    auto grid_of = [](uint64_t cap, uint32_t slots) {
+        const uint64_t chunks = (cap + SEG_PER_CTA - 1) / SEG_PER_CTA;
+        const uint64_t sliced = chunks < slots ? chunks : slots;
+        return (unsigned)(chunks - sliced + sliced * SEG_SPLIT);
+    };
+    cudaMemsetAsync(sl.sched16, 0, sl.sched_bytes, st);  // ticket counters and per-chunk slice counters of both kernels
+    VR_COUNT(1);
+    k_seg_begin<<<1, 1, 0, st>>>(sl);
     if (seg_cap) {
         cudaMemsetAsync(sl.flags, 0, seg_cap, st);
-        cudaMemsetAsync(sl.flag_all, 0, sizeof(uint32_t), st);
         // sphere-type lists: distances are measured from the sphere's surface, the flags from its centre
         const float margin = 1.02f * (rho + (sphere ? radius : 0.0f)) + 1.0e-3f;
         if (nlights_capacity) {
@@ -1813,37 +1953,31 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
             k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 128, 0, st>>>(
                 lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples, sl, margin);
         }
-        if (!sphere && seg_cap / 2) {
-            VR_COUNT(1);
-            k_list_flagged<16><<<(unsigned)((seg_cap / 2 + 255) / 256), 256, 0, st>>>(sl);
-        }
         VR_COUNT(1);
-        k_list_flagged<8><<<(unsigned)((cap8 + 255) / 256), 256, 0, st>>>(sl);
+        const unsigned b16 = (unsigned)((cap16 + 255) / 256), b8 = (unsigned)((cap8 + 255) / 256);
+        k_list_flagged<<<b16 + b8, 256, 0, st>>>(sl, b16);
     }
-    // counts[6] = the list length now (leftovers + near-light segments); the segment kernels append behind it
-    cudaMemcpyAsync(sl.counts + 6, sl.counts + 2, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st);
     if (side != st) {
         cudaEventRecord(ev_fork, st);
         cudaStreamWaitEvent(side, ev_fork, 0);
     }
     if (seg_cap) {
-        // launches are sized by the tables' upper bounds; CTAs beyond their lengths leave at once
         VR_COUNT(1);
         if (sphere) {
-            k_eval_seg<2, true, 8><<<grid8, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+            k_eval_seg<2, true, 8><<<grid_of(cap8, slots8s), EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out, slots8s);
         } else {
-            k_eval_seg<2, false, 16><<<grid16, EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            if (cap16) k_eval_seg<2, false, 16><<<grid_of(cap16, slots16), EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots16);
             VR_COUNT(1);
-            k_eval_seg<2, false, 8><<<grid8, EVAL_THREADS, 0, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            k_eval_seg<2, false, 8><<<grid_of(cap8, slots8), EVAL_THREADS, 0, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots8);
         }
     }
-    launch_exact_list(side, sphere, samples, nsamples, small, sl, nullptr, sl.counts + 6, lights2, nlights_dev, radius, out, redo_count);
+    // the list is complete since k_list_flagged (the segment kernels hand over into the second list)
+    launch_exact_list(side, sphere, samples, nsamples, small, false, sl.list, sl.counts + 2, lights2, nlights_dev, radius, out, redo_count);
     if (side != st) {
         cudaEventRecord(ev_join, side);
         cudaStreamWaitEvent(st, ev_join, 0);
     }
-    launch_exact_list(st, sphere, samples, seg_cap * SEG_LEN, small, sl, sl.counts + 6, sl.counts + 2, lights2, nlights_dev, radius, out,
-                      redo_count);
+    launch_exact_list(st, sphere, samples, seg_cap * SEG_LEN, true, true, sl.list2, sl.counts + 7, lights2, nlights_dev, radius, out, redo_count);
 }
 void vrk_eval_sphere_packed(cudaStream_t st, const VrSample* samples, uint64_t nsamples, const float4* lights2,
                             const unsigned long long* nlights_dev, float radius, float* out) {

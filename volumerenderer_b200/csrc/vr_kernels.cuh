@@ -92,10 +92,16 @@ struct VrSegLists {
     uint32_t* seg_base;           // per pixel: flag number of its first segment
     uint8_t* flags;               // per segment: 1 = comes near a light, evaluate exactly (k_flag_near_segments)
     uint32_t* flag_all;           // 1 = a light sits next to the camera plane: every segment goes to the exact kernel
-    uint32_t* list;               // samples for the exact kernel: leftovers, then the fix-ups appended by k_eval_seg
-    unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + fix-ups), [3] flag_all,
-                                  // [4] seg16 entries, [5] segments (flag numbers), [6] list length before the segment kernels
-    uint32_t list_capacity;
+    uint32_t* list;               // samples for the exact kernel: leftovers, then the near-light entries (k_list_flagged)
+    uint32_t* list2;              // samples the segment kernels hand over themselves (residual check): evaluated after the join
+    unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + near-light), [3] flag_all,
+                                  // [4] seg16 entries, [5] segments (flag numbers), [6] set if a slice-order wait of
+                                  // k_eval_seg ever gave up (must stay 0), [7] list2 length
+    uint32_t list_capacity;       // of list and of list2
+    // work distribution of k_eval_seg: [0] ticket counter, [1 + c] slices of chunk c accumulated; one array per kernel
+    // instance (16- and 8-sample tables run concurrently), allocated back to back (sched_bytes from sched16), zeroed per pass
+    uint32_t *sched16, *sched8;
+    uint64_t sched_bytes;
 };
 // builds seg_first / seg_pix / the leftover part of list from the per-pixel sample counts and offsets (nsamples < 2^32)
 // pairs != 0: pairs of segments go to the 16-sample table (point-type lists); 0: every segment to the 8-sample table
