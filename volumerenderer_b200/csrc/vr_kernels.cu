@@ -1020,15 +1020,17 @@ __device__ __forceinline__ float2 seg_dist2(const float2 l2, const float2 nR) {
 // per-light geometry is shared by 16 samples; their weights are read again at the end instead of held in registers.
 //
 // Work distribution. A chunk is SEG_PER_CTA table entries, and every sample's light sum is DEFINED as the sum over
-// SEG_SPLIT consecutive slices of the light list, added in slice order: out = (((w*S0) + w*S1) + w*S2) + w*S3. A "full"
-// unit is one CTA that walks all slices of a chunk one after the other (entries stay in registers, the partial result is
-// accumulated in `out`); a "slice" unit is one CTA per (chunk, slice). CTAs take units from a ticket counter in the order
-// they start: first the full units of all chunks but the last `slots` (one resident wave), then the slice units of those
-// last chunks, slice 0 first. So the end of the kernel is made of units a quarter as long, and the GPU drains evenly: the
-// tail of a launch whose chunks fill 3.4 waves (one of eight GPUs' bands) costs a quarter of a CTA time instead of a
-// whole one. Slice units of a chunk add to `out` in slice order (a per-chunk counter; a unit's predecessor always holds
-// an earlier ticket, i.e. is running or done: no deadlock), so the result does not depend on which kind of unit
-// produced it -- a tiled render equals the whole frame bit for bit (tests/test_gpu_configs.py).
+// SEG_SPLIT consecutive slices of the light list, added in slice order and weighted once: out = w*(((S0 + S1) + S2) + S3).
+// A "full" unit is one CTA that walks the whole list for a chunk in one uninterrupted loop (entries stay in registers); at
+// a slice boundary it moves its accumulators into a running total in shared memory (3 x 16 LDS/STS per thread per chunk,
+// no global traffic, no pipeline restart). A "slice" unit is one CTA per (chunk, slice); it keeps the running total in
+// `out`. CTAs take units from a ticket counter in the order they start: first the full units of all chunks but the last
+// `slots` (one resident wave), then the slice units of those last chunks, slice 0 first. So the end of the kernel is made
+// of units a quarter as long, and the GPU drains evenly: the tail of a launch whose chunks fill 3.4 waves (one of eight
+// GPUs' bands) costs a quarter of a CTA time instead of a whole one. Slice units of a chunk add to `out` in slice order
+// (a per-chunk counter; a unit's predecessor always holds an earlier ticket, i.e. is running or done: no deadlock), so
+// the result does not depend on which kind of unit produced it -- a tiled render equals the whole frame bit for bit
+// (tests/test_gpu_configs.py).
 constexpr int SEG_SPLIT = 4;
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
     uint32_t v;
@@ -1051,10 +1053,13 @@ __device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
 }
 // lights per slice: a quarter of the list rounded up to whole pairs (the loop shares one reciprocal between two lights, so
 // slice boundaries must not split the pairs the unsliced list would form), at least 64
-__device__ __forceinline__ uint64_t seg_slice_len(uint64_t nlights) {
+__host__ __device__ __forceinline__ uint64_t seg_slice_len(uint64_t nlights) {
     const uint64_t q = ((nlights + SEG_SPLIT - 1) / SEG_SPLIT + 1) & ~1ull;
     return q < 64 ? 64 : q;
 }
+// dynamic shared memory of k_eval_seg: the two light stages, the two mbarriers, the running totals of a full unit
+constexpr uint32_t SEG_STAGE_BYTES = 2u * 2u * EVAL2_TILE * 16u;
+constexpr uint32_t seg_smem_bytes(int len) { return SEG_STAGE_BYTES + 128u + (uint32_t)len * EVAL_THREADS * 8u; }
 
 template <int MINB, bool SPHERE, int LEN>
 __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
@@ -1062,6 +1067,10 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                                                                   const float4* __restrict__ lights2,
                                                                   const unsigned long long* __restrict__ nlights_dev, float rho,
                                                                   float radius, float* __restrict__ out, uint32_t slots) {
+    extern __shared__ __align__(128) unsigned char seg_smem[];
+    float4 (*stage)[2 * EVAL2_TILE] = reinterpret_cast<float4 (*)[2 * EVAL2_TILE]>(seg_smem);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(seg_smem + SEG_STAGE_BYTES);
+    float2* part = reinterpret_cast<float2*>(seg_smem + SEG_STAGE_BYTES + 128u);  // [k][tid]: conflict-free 8-byte accesses
     const float2 nR = make_float2(-radius, -radius);
     constexpr bool KEEP_W = LEN <= 8;
     const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
@@ -1076,13 +1085,13 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     const uint32_t unit = s_unit;
     const uint32_t nchunks = (uint32_t)((nseg + SEG_PER_CTA - 1) / SEG_PER_CTA);
     const uint32_t nsliced = nchunks < slots ? nchunks : slots, nfull = nchunks - nsliced;
-    uint32_t chunk = unit, q0 = 0, q1 = SEG_SPLIT;
+    uint32_t chunk = unit, q0 = 0;
+    bool sliced = false;
     if (unit >= nfull) {
         const uint32_t r = unit - nfull;
-        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT, q1 = q0 + 1;
+        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT, sliced = true;
         if (chunk >= nchunks) return;  // the launch is sized by the capacity, the segment count lives on the device
     }
-    const bool sliced = q1 - q0 == 1;
     uint32_t* __restrict__ done = sched + 1 + chunk;
     const uint64_t seg_base = (uint64_t)chunk * SEG_PER_CTA;
     const bool redo_all = *sl.flag_all != 0u;
@@ -1109,24 +1118,22 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     }
     const uint64_t nlights = *nlights_dev;
     const uint64_t slice_len = seg_slice_len(nlights);
-    __shared__ __align__(128) float4 stage[2][2 * EVAL2_TILE];
-    __shared__ __align__(8) uint64_t bar[2];
+    // the lights this unit walks: the whole list, or slice q0 of it
+    const uint64_t lo = sliced ? (uint64_t)q0 * slice_len : 0;
+    const uint64_t nl = !sliced ? nlights : (lo < nlights ? (nlights - lo < slice_len ? nlights - lo : slice_len) : 0);
+    const float4* __restrict__ src = lights2 + 2 * lo;
+    const uint64_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    uint32_t it = 0;  // tiles consumed so far: stage = it & 1, mbarrier phase parity = (it >> 1) & 1
-    {
-        const uint64_t lo = (uint64_t)q0 * slice_len;
-        if (tid == 0 && lo < nlights) {  // the first tile of the first slice travels while the entries are loaded
-            const uint64_t left = (nlights - lo < slice_len ? nlights - lo : slice_len);
-            const uint32_t cnt = (uint32_t)(left < EVAL2_TILE ? left : EVAL2_TILE);
+        if (ntiles > 0) {  // the first tile travels while the entries are loaded
+            const uint32_t cnt = (uint32_t)(nl < EVAL2_TILE ? nl : EVAL2_TILE);
             mbar_expect_tx(&bar[0], cnt * 32u);
-            tma_bulk_g2s(&stage[0][0], lights2 + 2 * lo, cnt * 32u, &bar[0]);
+            tma_bulk_g2s(&stage[0][0], src, cnt * 32u, &bar[0]);
         }
     }
+    __syncthreads();
 
     float2 s[LEN], acc[LEN], A[3], D[3];
     float sw[2][KEEP_W ? LEN : 1];
@@ -1187,33 +1194,28 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         }
     }
 
-    for (uint32_t q = q0; q < q1; q++) {
-        const uint64_t lo = (uint64_t)q * slice_len;
-        const uint64_t nl = lo < nlights ? (nlights - lo < slice_len ? nlights - lo : slice_len) : 0;  // lights of this slice
-        const float4* __restrict__ src = lights2 + 2 * lo;
-        const uint64_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
 #pragma unroll
-        for (int k = 0; k < LEN; k++) acc[k] = make_float2(0.f, 0.f);
-        if (q != q0 && tid == 0 && ntiles > 0) {  // (the first slice's first tile is already in flight)
-            const uint32_t cnt = (uint32_t)(nl < EVAL2_TILE ? nl : EVAL2_TILE);
-            mbar_expect_tx(&bar[it & 1], cnt * 32u);
-            tma_bulk_g2s(&stage[it & 1][0], src, cnt * 32u, &bar[it & 1]);
+    for (int k = 0; k < LEN; k++) acc[k] = make_float2(0.f, 0.f);
+    // a full unit moves its accumulators into the running total at every slice boundary (indices relative to `lo`)
+    uint64_t boundary = sliced ? ~0ull : slice_len;
+    bool spilled = false;
+    for (uint64_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = (uint32_t)tl & 1u;
+        if (tid == 0 && tl + 1 < ntiles) {
+            const uint64_t nxt = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (uint32_t)((nl - nxt) < EVAL2_TILE ? (nl - nxt) : EVAL2_TILE);
+            mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
+            tma_bulk_g2s(&stage[buf ^ 1][0], src + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
         }
-        for (uint64_t tl = 0; tl < ntiles; tl++, it++) {
-            const uint32_t buf = it & 1;
-            if (tid == 0 && tl + 1 < ntiles) {
-                const uint64_t nxt = (tl + 1) * EVAL2_TILE;
-                const uint32_t cnt = (uint32_t)((nl - nxt) < EVAL2_TILE ? (nl - nxt) : EVAL2_TILE);
-                mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
-                tma_bulk_g2s(&stage[buf ^ 1][0], src + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
-            }
-            mbar_wait(&bar[buf], (it >> 1) & 1);
-            const uint64_t tlo = tl * EVAL2_TILE;
-            const int cnt = (int)((nl - tlo) < EVAL2_TILE ? (nl - tlo) : EVAL2_TILE);
-            const float4* __restrict__ L = stage[buf];
-            int l = 0;
+        mbar_wait(&bar[buf], (uint32_t)(tl >> 1) & 1u);
+        const uint64_t tlo = tl * EVAL2_TILE;
+        const int cnt = (int)((nl - tlo) < EVAL2_TILE ? (nl - tlo) : EVAL2_TILE);
+        const float4* __restrict__ L = stage[buf];
+        int l = 0;
+        while (l < cnt) {
+            const int end = boundary - tlo < (uint64_t)cnt ? (int)(boundary - tlo) : cnt;  // (boundary > tlo + l always)
 #pragma unroll 1
-            for (; l + 2 <= cnt; l += 2) {
+            for (; l + 2 <= end; l += 2) {
                 const float4 qa = L[2 * l], qb = L[2 * l + 1], ra = L[2 * l + 2], rb = L[2 * l + 3];
                 float2 nb0, h0, nb1, h1;
                 seg_light_geometry(qa, qb, A, D, nb0, h0);
@@ -1228,7 +1230,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                     acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
                 }
             }
-            if (l < cnt) {  // odd tail of the list (its last slice only: slices are whole pairs)
+            if (l < end) {  // odd tail of the list (slices are whole pairs: this is the list's last light)
                 const float4 qa = L[2 * l], qb = L[2 * l + 1];
                 float2 nb0, h0;
                 seg_light_geometry(qa, qb, A, D, nb0, h0);
@@ -1239,32 +1241,48 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                     const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR);
                     acc[k] = __ffma2_rn(W0, make_float2(rcp_approx(a.x), rcp_approx(a.y)), acc[k]);
                 }
+                l++;
             }
-            __syncthreads();  // everyone is done with stage[buf] before it is refilled two tiles later
-        }
-        // ---- out (+)= w * (this slice's sum), in slice order
-        if (sliced && q > 0) {
-            if (tid == 0) wait_slices(done, q, &sl.counts[6]);
-            __syncthreads();
-        }
-        if (q == 0 || nl > 0) {
-#pragma unroll
-            for (int h = 0; h < 2; h++) {
-                if (first[h] == 0xffffffffu || skip[h]) continue;
+            if (tlo + (uint64_t)l == boundary && boundary < nl) {  // end of a slice with more to come: total (+)= acc
 #pragma unroll
                 for (int k = 0; k < LEN; k++) {
-                    const float w = KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w);
-                    const float v = w * (h == 0 ? acc[k].x : acc[k].y);
-                    float* o = out + first[h] + k;
-                    *o = q == 0 ? v : __fadd_rn(__ldcg(o), v);
+                    float2* pp = part + k * EVAL_THREADS + tid;
+                    *pp = spilled ? __fadd2_rn(*pp, acc[k]) : acc[k];
+                    acc[k] = make_float2(0.f, 0.f);
                 }
+                spilled = true;
+                boundary += slice_len;
             }
         }
-        if (sliced) {
-            __threadfence();
-            __syncthreads();
-            if (tid == 0) st_release_u32(done, q + 1);
+        __syncthreads();  // everyone is done with stage[buf] before it is refilled two tiles later
+    }
+    if (spilled) {
+#pragma unroll
+        for (int k = 0; k < LEN; k++) acc[k] = __fadd2_rn(part[k * EVAL_THREADS + tid], acc[k]);
+    }
+
+    // ---- full unit: out = w * total. Slice unit: the running total lives in `out`, the last slice applies the weight
+    if (sliced && q0 > 0) {
+        if (tid == 0) wait_slices(done, q0, &sl.counts[6]);
+        __syncthreads();
+    }
+    const bool last = !sliced || q0 == SEG_SPLIT - 1;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        if (first[h] == 0xffffffffu || skip[h]) continue;
+#pragma unroll
+        for (int k = 0; k < LEN; k++) {
+            float* o = out + first[h] + k;
+            float v = h == 0 ? acc[k].x : acc[k].y;
+            if (sliced && q0 > 0) v = __fadd_rn(__ldcg(o), v);
+            if (last) v = (KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w)) * v;
+            *o = v;
         }
+    }
+    if (sliced) {
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) st_release_u32(done, q0 + 1);
     }
 
     if (q0 == 0) {  // entries handed over to the exact kernel (second list): announced once per chunk
@@ -1906,14 +1924,19 @@ static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* sampl
     }
 }
 
-// resident CTAs of a segment kernel on this GPU (the "wave" its tail distribution is planned for)
+// resident CTAs of a segment kernel on this GPU (the "wave" its tail distribution is planned for); also opts the kernel
+// into its dynamic shared memory on the current device (function attributes are per device: vr_group drives several)
 template <class K>
-static uint32_t seg_slots(K kernel) {
+static uint32_t seg_slots(K kernel, uint32_t smem, uint32_t (&cache)[64]) {
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && cache[dev]) return cache[dev];
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EVAL_THREADS, 0);
-    return (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EVAL_THREADS, smem);
+    const uint32_t slots = (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
+    if (dev >= 0 && dev < 64) cache[dev] = slots;
+    return slots;
 }
 // Evaluation pass of the ray-segment path. Main stream: near-light flags, the flagged entries onto the exact kernel's list,
 // then the big segment kernel. Side stream (lower priority, forked once the list is complete): the odd 8-sample segments and
@@ -1928,8 +1951,11 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
                         unsigned long long* redo_count) {
     if (nsamples == 0) return;
     if (!side) side = st;
-    static const uint32_t slots16 = seg_slots(k_eval_seg<2, false, 16>), slots8 = seg_slots(k_eval_seg<2, false, 8>),
-                          slots8s = seg_slots(k_eval_seg<2, true, 8>);
+    static uint32_t cache16[64], cache8[64], cache8s[64];  // (benign race: every thread computes the same values)
+    constexpr uint32_t smem16 = seg_smem_bytes(16), smem8 = seg_smem_bytes(8);
+    const uint32_t slots16 = sphere ? 0 : seg_slots(k_eval_seg<2, false, 16>, smem16, cache16);
+    const uint32_t slots8 = sphere ? 0 : seg_slots(k_eval_seg<2, false, 8>, smem8, cache8);
+    const uint32_t slots8s = sphere ? seg_slots(k_eval_seg<2, true, 8>, smem8, cache8s) : 0;
     const uint64_t seg_cap = nsamples / SEG_LEN;
     const bool small = nsamples < 40ull * 1000 * 1000;  // short lists: 4 samples per thread, twice the CTAs at half the duration
     const uint64_t cap16 = sphere ? 0 : seg_cap / 2;
@@ -1964,11 +1990,11 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
     if (seg_cap) {
         VR_COUNT(1);
         if (sphere) {
-            k_eval_seg<2, true, 8><<<grid_of(cap8, slots8s), EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out, slots8s);
+            k_eval_seg<2, true, 8><<<grid_of(cap8, slots8s), EVAL_THREADS, smem8, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out, slots8s);
         } else {
-            if (cap16) k_eval_seg<2, false, 16><<<grid_of(cap16, slots16), EVAL_THREADS, 0, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots16);
+            if (cap16) k_eval_seg<2, false, 16><<<grid_of(cap16, slots16), EVAL_THREADS, smem16, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots16);
             VR_COUNT(1);
-            k_eval_seg<2, false, 8><<<grid_of(cap8, slots8), EVAL_THREADS, 0, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots8);
+            k_eval_seg<2, false, 8><<<grid_of(cap8, slots8), EVAL_THREADS, smem8, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots8);
         }
     }
     // the list is complete since k_list_flagged (the segment kernels hand over into the second list)
