@@ -78,3 +78,18 @@ def test_product_does_not_reference_the_oracle():
 def test_grid_fixture_entry_points_run_without_gpu(vr):
     g = vr.build_cloud_grid(16)
     assert isinstance(g, np.ndarray) and g.nbytes > 672
+
+
+def test_nvtx_build_flag_compiles(tmp_path):
+    """The profiling build (-DVR_NVTX: one NVTX range per pass) must keep compiling."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("no nvcc")
+    obj = str(tmp_path / "vr_api_nvtx.o")
+    src = os.path.join(ROOT, "volumerenderer_b200", "csrc", "vr_api.cu")
+    subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-Xcompiler", "-fPIC,-ffp-contract=off",
+                           "-DVR_NVTX", "-c", src, "-o", obj])
+    syms = subprocess.run(["nm", obj], capture_output=True, text=True).stdout
+    assert "nvtx" in syms.lower()

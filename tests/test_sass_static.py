@@ -61,9 +61,12 @@ def _find(funcs, *parts):
 
 
 @pytest.mark.parametrize("mangled, evals, packed_max, mufu", [
-    ("k_eval_segILi2ELb0ELi16", 64, 152, 32),   # point, 16-sample entries: 4.75 FMA-pipe cycles, 0.5 MUFU per evaluation
-    ("k_eval_segILi2ELb0ELi8", 32, 88, 16),     # point, 8-sample entries: 5.5 cycles
-    ("k_eval_segILi2ELb1ELi8", 32, 120, 48),    # sphere: 1.5 MUFU per evaluation
+    # (threads, CTAs/SM, sphere, entry length, slice units)
+    ("k_eval_segILi256ELi2ELb0ELi16ELb0", 64, 152, 32),   # point, 16-sample entries, full units: 4.75 FMA-pipe cycles, 0.5 MUFU per evaluation
+    ("k_eval_segILi256ELi2ELb0ELi16ELb1", 64, 152, 32),   # ... slice units (the last wave)
+    ("k_eval_segILi256ELi2ELb0ELi8ELb1", 32, 88, 16),     # point, 8-sample entries (odd segments, all as slice units): 5.5 cycles
+    ("k_eval_segILi256ELi2ELb1ELi8ELb0", 32, 120, 48),    # sphere: 1.5 MUFU per evaluation
+    ("k_eval_segILi256ELi2ELb1ELi8ELb1", 32, 120, 48),
 ])
 def test_segment_kernel_hot_loop_mix(funcs, mangled, evals, packed_max, mufu):
     body = _inner_mufu_loop(_find(funcs, mangled))
@@ -77,6 +80,36 @@ def test_segment_kernel_hot_loop_mix(funcs, mangled, evals, packed_max, mufu):
     assert _count(body, r"STL|LDL") == 0, "spills in the hot loop"
 
 
+def _mufu_use_distances(body):
+    """Instructions between every MUFU of the loop body and the first instruction that reads its result."""
+    out = []
+    for i, t in enumerate(body):
+        m = re.match(r"MUFU\.\w+ (R\d+),", t)
+        if not m:
+            continue
+        r = m.group(1)
+        n = int(r[1:])
+        pair = "R%d" % (n - n % 2)
+        for j in range(i + 1, len(body)):
+            ops = body[j].split(" ", 1)[1] if " " in body[j] else ""
+            srcs = ops.split(",")[1:]
+            if any(re.search(r"\b%s\b" % r, s_) or ("F32x2" in s_ and re.search(r"\b%s\b" % pair, s_)) for s_ in srcs):
+                out.append(j - i)
+                break
+    return out
+
+
+@pytest.mark.parametrize("mangled", ["k_eval_segILi256ELi2ELb0ELi16ELb0", "k_eval_segILi256ELi2ELb0ELi16ELb1"])
+def test_segment_kernel_schedule_hides_the_reciprocal_latency(funcs, mangled):
+    """Same instruction mix, 5 % slower: with one register too many ptxas serialises the samples of an entry (every
+    reciprocal consumed 2-5 instructions after its MUFU; measured 10.28 vs 9.76 ms on C2, `wait` stalls 2.0 vs 1.1 per
+    issue). The full units keep their bookkeeping uniform (chunk = blockIdx.x) so that the loop has the registers to
+    interleave two or three samples: the typical reciprocal is consumed ten or more instructions later."""
+    d = sorted(_mufu_use_distances(_inner_mufu_loop(_find(funcs, mangled))))
+    assert len(d) == 32
+    assert d[len(d) // 2] >= 9, d
+
+
 def test_exact_list_kernel_hot_loop(funcs):
     body = _inner_mufu_loop(_find(funcs, "k_eval_point3ILi8ELi3ELi2ELb1"))
     assert _count(body, r"FFMA2|FMUL2|FADD2") == 56 and _count(body, "MUFU") == 16   # 16 evaluations of 8 samples x 2 lights
@@ -84,7 +117,8 @@ def test_exact_list_kernel_hot_loop(funcs):
 
 
 def test_light_list_is_staged_by_tma(funcs):
-    for part in ("k_eval_segILi2ELb0ELi16", "k_eval_segILi2ELb1ELi8", "k_eval_point3ILi8ELi3ELi2ELb0", "k_eval_sphere2ILi8ELb0"):
+    for part in ("k_eval_segILi256ELi2ELb0ELi16ELb0", "k_eval_segILi256ELi2ELb0ELi16ELb1", "k_eval_segILi256ELi2ELb1ELi8ELb0",
+                 "k_eval_point3ILi8ELi3ELi2ELb0", "k_eval_sphere2ILi8ELb0"):
         ins = _find(funcs, part)
         assert any("UBLKCP" in t for _, t in ins), part          # cp.async.bulk global -> shared
         assert any("SYNCS" in t for _, t in ins), part           # mbarrier arrive / try_wait

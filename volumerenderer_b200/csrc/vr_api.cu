@@ -13,6 +13,31 @@
 #include "../../include/vr.h"
 #include "vr_kernels.cuh"
 
+// NVTX ranges per pass of a frame (tracing row), compiled in with -DVR_NVTX (VR_NVTX=1 in the
+// environment of __graft_entry__.build(); header-only NVTX 3, no link dependency). A VrPassRange names the pass that
+// is being ENQUEUED; profilers project the range onto the stream's kernels. Off by default: the product build carries
+// no profiler hooks.
+#ifdef VR_NVTX
+#include <nvtx3/nvToolsExt.h>
+struct VrPassRange {
+    bool open = false;
+    explicit VrPassRange(const char* name) { next(name); }
+    void next(const char* name) {
+        if (open) nvtxRangePop();
+        nvtxRangePushA(name);
+        open = true;
+    }
+    ~VrPassRange() {
+        if (open) nvtxRangePop();
+    }
+};
+#else
+struct VrPassRange {
+    explicit VrPassRange(const char*) {}
+    void next(const char*) {}
+};
+#endif
+
 static_assert(sizeof(vr_ubo) == 96, "UBO must match the std140 block of shaders/common_bindings.h:19-34");
 static_assert(sizeof(vr_ray_light) == 32, "RayLight std430 stride (shaders/common_bindings.h:10-12)");
 
@@ -128,8 +153,9 @@ struct vr_ctx {
     cudaEvent_t ev_copy_ready = nullptr, ev_copy_done = nullptr;
     DevBuf<float> accum_snapshot;
     bool copy_pending = false;
+    cudaStream_t seg_stream2 = nullptr;
     cudaStream_t seg_stream = nullptr;  // low priority: the small evaluation kernels that fill the big kernel's tail
-    cudaEvent_t ev_seg_fork = nullptr, ev_seg_join = nullptr;
+    cudaEvent_t ev_seg_fork = nullptr, ev_seg_join = nullptr, ev_seg_join2 = nullptr;
     bool lg_in_flight = false;
     uint32_t lg_groups[3] = {1, 1, 1};
     vr_lightgen_variant lg_variant = VR_LG_RESET_ORIGIN;
@@ -351,6 +377,7 @@ void note_generation(vr_ctx* c, const vr_ubo& u, vr_algo algo) {
 // light generation on stream `st` (shaders/light_gen.comp) with parameters `u` into (lights, counter), timed into `t`
 int enqueue_light_gen(vr_ctx* c, cudaStream_t st, vr_ctx::TimingSet* t, const vr_ubo& u, vr_algo algo, uint32_t gx, uint32_t gy,
                       uint32_t gz, vr_lightgen_variant variant, vr_ray_light* lights, VrLightCounter* counter) {
+    VrPassRange range_fn("vr:light_gen");
     const uint64_t nphot = (uint64_t)gx * 4 * gy * 4 * gz;
     cudaEventRecord(t->ev[0], st);
     t->lg_timed = true;
@@ -443,7 +470,13 @@ int vr_create(int cuda_device, vr_ctx** out) {
         }                                                                                       \
     } while (0)
     VR_CREATE_CUDA(cudaSetDevice(cuda_device));
-    VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    {
+        // one step above the lowest priority: the side streams of the evaluation pass (lowest) only get the SM slots that the
+        // main stream's kernels leave free
+        int lo = 0, hi = 0;
+        VR_CREATE_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));  // lo = numerically largest = lowest priority
+        VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->own_stream, cudaStreamNonBlocking, lo - 1 >= hi ? lo - 1 : lo));
+    }
     c->stream = c->own_stream;
     c->launch_base = vrk_launch_count();
     VR_CREATE_CUDA(cudaMalloc(&c->counter, sizeof(VrLightCounter)));
@@ -472,6 +505,7 @@ int vr_create(int cuda_device, vr_ctx** out) {
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);  // lo = the numerically largest = lowest priority
         VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->seg_stream, cudaStreamNonBlocking, lo));
+        VR_CREATE_CUDA(cudaStreamCreateWithPriority(&c->seg_stream2, cudaStreamNonBlocking, lo));
     }
     VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->upload_stream, cudaStreamNonBlocking));
@@ -480,6 +514,7 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_fork, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join2, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 8 * sizeof(unsigned long long)));  // layout: VrSegLists::counts
@@ -546,7 +581,9 @@ int vr_destroy(vr_ctx* c) {
     c->accum_snapshot.release();
     if (c->ev_seg_fork) cudaEventDestroy(c->ev_seg_fork);
     if (c->ev_seg_join) cudaEventDestroy(c->ev_seg_join);
+    if (c->ev_seg_join2) cudaEventDestroy(c->ev_seg_join2);
     if (c->seg_stream) cudaStreamDestroy(c->seg_stream);
+    if (c->seg_stream2) cudaStreamDestroy(c->seg_stream2);
     if (c->ev_lg_done) cudaEventDestroy(c->ev_lg_done);
     if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     if (c->eval_redo) cudaFree(c->eval_redo);
@@ -663,6 +700,7 @@ static void grid_alt_install(vr_ctx* c, const uint8_t* b, uint64_t size, uint64_
 }
 
 int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
+    VrPassRange range_fn("vr:set_grid");
     if (!c) return VR_E_ARG;
     if (!bytes) return fail(c, VR_E_ARG, "vr_set_grid: NULL buffer");
     const uint8_t* b = (const uint8_t*)bytes;
@@ -888,6 +926,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     memset(&c->last_counters, 0, sizeof(c->last_counters));
     c->last_algo = algo;
 
+    VrPassRange range(algo == VR_ALGO_PATH ? "vr:path" : "vr:march");
     if (algo == VR_ALGO_PATH) {
         cudaEventRecord(t->ev[2], st);
         cudaEventRecord(t->ev[3], st);
@@ -935,7 +974,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     // Single-pass march (default with the ray-segment evaluation, which addresses samples through tables): slots sized by
     // a lookup-free bound of each pixel's step count, so the count pass of the two-pass march (40 % of it) is not needed.
     // The exact kernels (variants 0-3) and the opt-in physics walk a compact sample array: two passes for them.
-    key.gaps = (c->march_single && c->eval_variant == 8 && !(c->phys.phase_hg || c->phys.light_transmittance)) ? 1u : 0u;
+    key.gaps = (c->march_single && c->eval_variant >= 8 && !(c->phys.phase_hg || c->phys.light_transmittance)) ? 1u : 0u;
     if (key.gaps && key == c->gaps_refused) key.gaps = 0;
     bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
     const bool reuse = c->march_cache && same_key;
@@ -1014,6 +1053,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     cudaEventRecord(t->ev[3], st);
 
     // ---- light list for the evaluation kernels (needs the lights: join the light-generation stream)
+    range.next("vr:light_list");
     if (c->lg_in_flight) {
         VR_CUDA(c, cudaStreamWaitEvent(st, c->ev_lg_done, 0));
         c->lg_in_flight = false;
@@ -1062,6 +1102,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         nt->open = true;
         vr_ubo nu = c->ubo;
         nu.frameCount += c->frame_step;
+        VrPassRange prefetch("vr:light_gen(prefetch)");
         VR_CUDA(c, cudaEventRecord(c->ev_fork, st));
         VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
         VR_CUDA(c, cudaMemsetAsync(c->counter_alt, 0, sizeof(VrLightCounter), c->aux_stream));
@@ -1075,12 +1116,13 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     }
 
     // ---- evaluation (hot) + resolve
+    range.next("vr:evaluate");
     const int sphere = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 1 : 0;
     if (c->phys.phase_hg || c->phys.light_transmittance)  // opt-in physics: its own (slow, every-rounding) kernel
         vrk_eval_phys(st, sphere, c->gdev, c->ubo, c->phys, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->contrib.p);
     else if (c->eval_variant == 0)
         vrk_eval(st, sphere, c->samples.p, nsamples, c->eval_lights.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
-    else if (c->eval_variant == 8 && nsamples < 0xffffffffull) {
+    else if (c->eval_variant >= 8 && nsamples < 0xffffffffull) {
         VrSegLists sl;
         if (c->seg_pairs != (sphere ? 0 : 1)) c->seg_valid = false;
         if (!c->seg_valid) {
@@ -1094,14 +1136,14 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             VR_CUDA(c, c->seg_flags.reserve(nreal / 8 + 2));
             VR_CUDA(c, c->seg_list.reserve(nreal + 1));
             VR_CUDA(c, c->seg_list2.reserve(nreal + 1));
-            VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 512 + 4)));  // per kernel instance: ticket + one word per chunk
+            VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 128 + 4)));  // per kernel instance: ticket + one word per chunk
             VR_CUDA(c, c->seg_base.reserve(npix + 1));
         }
         sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
         sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
         sl.list = c->seg_list.p, sl.list2 = c->seg_list2.p, sl.counts = c->seg_counts;
         {
-            const uint64_t per = nreal / 8 / 512 + 4;  // chunks of SEG_PER_CTA = 512 entries, at most nreal / 8 entries
+            const uint64_t per = nreal / 8 / 128 + 4;  // chunks of at least 128 entries (two per thread), at most nreal / 8 entries
             sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
         }
         sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
@@ -1118,15 +1160,16 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             rho *= sqrtf(1000.0f / (float)eval_list_cap);
             if (rho < 0.1f) rho = 0.1f;
         }
-        vrk_eval_point_seg(st, c->eval_side_stream ? c->seg_stream : nullptr, c->ev_seg_fork, c->ev_seg_join, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nreal, npix, c->px_counts.p, c->px_offsets.p, sl,
+        vrk_eval_point_seg(st, c->eval_side_stream ? c->seg_stream : nullptr, c->eval_side_stream ? c->seg_stream2 : nullptr, c->ev_seg_fork, c->ev_seg_join, c->ev_seg_join2, c->gdev, c->ubo, tan_scale, tile, c->samples.p, nreal, npix, c->px_counts.p, c->px_offsets.p, sl,
                            c->eval_lights.p, c->eval_lights2.p, eval_list_cap, c->totals + 1, rho, sphere, c->ubo.beamRadius,
                            c->contrib.p, c->eval_redo);
     } else if (sphere)
         vrk_eval_sphere_packed(st, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1, c->ubo.beamRadius, c->contrib.p);
     else
-        vrk_eval_point_packed(st, c->eval_variant == 8 ? 2 : c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1,
+        vrk_eval_point_packed(st, c->eval_variant >= 8 ? 2 : c->eval_variant, c->samples.p, nsamples, c->eval_lights2.p, c->totals + 1,
                               c->contrib.p, c->eval_redo);
     cudaEventRecord(t->ev[5], st);
+    range.next("vr:resolve");
     vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8, c->accumulate_mode);
     cudaEventRecord(t->ev[6], st);
     t->pending = true, t->open = false;
@@ -1142,6 +1185,7 @@ int vr_set_light_gen_groups(vr_ctx* c, uint32_t gx, uint32_t gy, uint32_t gz, vr
 }
 
 int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
+    VrPassRange range_fn("vr:frame");
     if (!c) return VR_E_ARG;
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
@@ -1392,6 +1436,7 @@ int vr_set_frame_color_peers(vr_ctx* c, void* local, void* const* peers, uint32_
 }
 
 int vr_accumulate_frame_color(vr_ctx* c, const vr_tile* tile_or_null) {
+    VrPassRange range_fn("vr:accumulate_frame_color");
     if (!c) return VR_E_ARG;
     if (!c->accum) return fail(c, VR_E_STATE, "no image: call vr_resize first");
     if (c->ubo.frameCount == 0) return fail(c, VR_E_STATE, "vr_accumulate_frame_color: no frame rendered yet (frameCount == 0)");
@@ -1702,6 +1747,7 @@ int vr_set_march_cache(vr_ctx* c, int enabled) {
 }
 
 int vr_cpu_test_render(vr_ctx* c, uint32_t width, uint32_t height, float* density_out) {
+    VrPassRange range_fn("vr:cpu_test");
     if (!c) return VR_E_ARG;
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
     if (width == 0 || height == 0 || !density_out) return fail(c, VR_E_ARG, "vr_cpu_test_render: bad arguments");

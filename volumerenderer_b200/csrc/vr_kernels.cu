@@ -1002,7 +1002,6 @@ __device__ __forceinline__ void seg_light_geometry(const float4 qa, const float4
 }
 
 constexpr int SEG_LEN = 8;                        // samples per segment (the unit of the tables and flags)
-constexpr int SEG_PER_CTA = 2 * EVAL_THREADS;     // two segments per thread: the x and y halves of every FP32x2 register
 
 // squared distance that enters the reciprocal. Point-type lists: the distance to the light itself. Sphere-type lists
 // (sphere lights, beam sub-points; common_functions.h:182-201): the light acts from the nearest point of its sphere of
@@ -1059,10 +1058,12 @@ __host__ __device__ __forceinline__ uint64_t seg_slice_len(uint64_t nlights) {
 }
 // dynamic shared memory of k_eval_seg: the two light stages, the two mbarriers, the running totals of a full unit
 constexpr uint32_t SEG_STAGE_BYTES = 2u * 2u * EVAL2_TILE * 16u;
-constexpr uint32_t seg_smem_bytes(int len) { return SEG_STAGE_BYTES + 128u + (uint32_t)len * EVAL_THREADS * 8u; }
+constexpr uint32_t seg_smem_bytes(int len, int threads) { return SEG_STAGE_BYTES + 128u + (uint32_t)len * (uint32_t)threads * 8u; }
 
-template <int MINB, bool SPHERE, int LEN>
-__global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
+// SLICE = false: the full units (chunk = blockIdx.x, all bookkeeping uniform: the loop keeps every register it had before
+// the slicing existed); SLICE = true: the slice units of the last `slots` chunks, taken from the ticket counter.
+template <int THREADS, int MINB, bool SPHERE, int LEN, bool SLICE>
+__global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                                   const VrSample* __restrict__ samples, VrSegLists sl,
                                                                   const float4* __restrict__ lights2,
                                                                   const unsigned long long* __restrict__ nlights_dev, float rho,
@@ -1070,7 +1071,8 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     extern __shared__ __align__(128) unsigned char seg_smem[];
     float4 (*stage)[2 * EVAL2_TILE] = reinterpret_cast<float4 (*)[2 * EVAL2_TILE]>(seg_smem);
     uint64_t* bar = reinterpret_cast<uint64_t*>(seg_smem + SEG_STAGE_BYTES);
-    float2* part = reinterpret_cast<float2*>(seg_smem + SEG_STAGE_BYTES + 128u);  // [k][tid]: conflict-free 8-byte accesses
+    float2* part = reinterpret_cast<float2*>(seg_smem + SEG_STAGE_BYTES + 128u);  // [k][tid]: conflict-free 8-byte accesses (full units)
+    constexpr int SEG_PER_CTA = 2 * THREADS;  // two entries per thread: the x and y halves of every FP32x2 register
     const float2 nR = make_float2(-radius, -radius);
     constexpr bool KEEP_W = LEN <= 8;
     const uint64_t nseg = LEN == 16 ? sl.counts[4] : sl.counts[0];
@@ -1079,18 +1081,19 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     const uint32_t* __restrict__ tab_flag = LEN == 16 ? sl.seg16_flag : sl.seg_flag;
     uint32_t* __restrict__ sched = LEN == 16 ? sl.sched16 : sl.sched8;  // [0] ticket counter, [1 + c] slices of chunk c done
     const uint32_t tid = threadIdx.x;
-    __shared__ uint32_t s_unit;
-    if (tid == 0) s_unit = atomicAdd(sched, 1u);
-    __syncthreads();
-    const uint32_t unit = s_unit;
     const uint32_t nchunks = (uint32_t)((nseg + SEG_PER_CTA - 1) / SEG_PER_CTA);
     const uint32_t nsliced = nchunks < slots ? nchunks : slots, nfull = nchunks - nsliced;
-    uint32_t chunk = unit, q0 = 0;
-    bool sliced = false;
-    if (unit >= nfull) {
-        const uint32_t r = unit - nfull;
-        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT, sliced = true;
+    uint32_t chunk = blockIdx.x, q0 = 0;
+    constexpr bool sliced = SLICE;
+    if (SLICE) {
+        __shared__ uint32_t s_unit;
+        if (tid == 0) s_unit = atomicAdd(sched, 1u);
+        __syncthreads();
+        const uint32_t r = s_unit;
+        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT;
         if (chunk >= nchunks) return;  // the launch is sized by the capacity, the segment count lives on the device
+    } else if (chunk >= nfull) {
+        return;
     }
     uint32_t* __restrict__ done = sched + 1 + chunk;
     const uint64_t seg_base = (uint64_t)chunk * SEG_PER_CTA;
@@ -1101,7 +1104,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         bool listed = true;
 #pragma unroll
         for (int h = 0; h < 2; h++) {
-            const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
+            const uint64_t seg = seg_base + tid + (uint64_t)h * THREADS;
             if (seg < nseg && !redo_all) {
                 const uint32_t fi = tab_flag[seg];
                 listed = listed && (sl.flags[fi] != 0 || (LEN == 16 && sl.flags[fi + 1] != 0));
@@ -1116,19 +1119,20 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
         }
         return;
     }
-    const uint64_t nlights = *nlights_dev;
-    const uint64_t slice_len = seg_slice_len(nlights);
+    // (list lengths are below 2^32: vr_dispatch_compute_color refuses longer expansions; 32-bit counters spare registers)
+    const uint32_t nlights = (uint32_t)*nlights_dev;
+    const uint32_t slice_len = (uint32_t)seg_slice_len(nlights);
     // the lights this unit walks: the whole list, or slice q0 of it
-    const uint64_t lo = sliced ? (uint64_t)q0 * slice_len : 0;
-    const uint64_t nl = !sliced ? nlights : (lo < nlights ? (nlights - lo < slice_len ? nlights - lo : slice_len) : 0);
-    const float4* __restrict__ src = lights2 + 2 * lo;
-    const uint64_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
+    const uint32_t lo = sliced ? (q0 * slice_len < nlights ? q0 * slice_len : nlights) : 0u;
+    const uint32_t nl = !sliced ? nlights : (nlights - lo < slice_len ? nlights - lo : slice_len);
+    const float4* __restrict__ src = lights2 + 2 * (uint64_t)lo;
+    const uint32_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
     if (tid == 0) {
         mbar_init(&bar[0], 1);
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         if (ntiles > 0) {  // the first tile travels while the entries are loaded
-            const uint32_t cnt = (uint32_t)(nl < EVAL2_TILE ? nl : EVAL2_TILE);
+            const uint32_t cnt = nl < EVAL2_TILE ? nl : EVAL2_TILE;
             mbar_expect_tx(&bar[0], cnt * 32u);
             tma_bulk_g2s(&stage[0][0], src, cnt * 32u, &bar[0]);
         }
@@ -1142,7 +1146,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     bool skip[2] = {false, false};  // on the exact kernel's list already: that kernel (another stream) owns the result
 #pragma unroll
     for (int h = 0; h < 2; h++) {
-        const uint64_t seg = seg_base + tid + (uint64_t)h * EVAL_THREADS;
+        const uint64_t seg = seg_base + tid + (uint64_t)h * THREADS;
         float a[3] = {1.0e6f, 1.0e6f, 1.0e6f}, d[3] = {1.0f, 0.0f, 0.0f}, sv[LEN];
         first[h] = 0xffffffffu;
 #pragma unroll
@@ -1196,24 +1200,24 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
 
 #pragma unroll
     for (int k = 0; k < LEN; k++) acc[k] = make_float2(0.f, 0.f);
-    // a full unit moves its accumulators into the running total at every slice boundary (indices relative to `lo`)
-    uint64_t boundary = sliced ? ~0ull : slice_len;
+    // a full unit moves its accumulators into the running total at every slice boundary
+    uint32_t boundary = sliced ? 0xffffffffu : slice_len;
     bool spilled = false;
-    for (uint64_t tl = 0; tl < ntiles; tl++) {
-        const uint32_t buf = (uint32_t)tl & 1u;
+    for (uint32_t tl = 0; tl < ntiles; tl++) {
+        const uint32_t buf = tl & 1u;
         if (tid == 0 && tl + 1 < ntiles) {
-            const uint64_t nxt = (tl + 1) * EVAL2_TILE;
-            const uint32_t cnt = (uint32_t)((nl - nxt) < EVAL2_TILE ? (nl - nxt) : EVAL2_TILE);
+            const uint32_t nxt = (tl + 1) * EVAL2_TILE;
+            const uint32_t cnt = (nl - nxt) < EVAL2_TILE ? (nl - nxt) : EVAL2_TILE;
             mbar_expect_tx(&bar[buf ^ 1], cnt * 32u);
-            tma_bulk_g2s(&stage[buf ^ 1][0], src + 2 * nxt, cnt * 32u, &bar[buf ^ 1]);
+            tma_bulk_g2s(&stage[buf ^ 1][0], src + 2 * (uint64_t)nxt, cnt * 32u, &bar[buf ^ 1]);
         }
-        mbar_wait(&bar[buf], (uint32_t)(tl >> 1) & 1u);
-        const uint64_t tlo = tl * EVAL2_TILE;
+        mbar_wait(&bar[buf], (tl >> 1) & 1u);
+        const uint32_t tlo = tl * EVAL2_TILE;
         const int cnt = (int)((nl - tlo) < EVAL2_TILE ? (nl - tlo) : EVAL2_TILE);
         const float4* __restrict__ L = stage[buf];
         int l = 0;
         while (l < cnt) {
-            const int end = boundary - tlo < (uint64_t)cnt ? (int)(boundary - tlo) : cnt;  // (boundary > tlo + l always)
+            const int end = boundary - tlo < (uint32_t)cnt ? (int)(boundary - tlo) : cnt;  // (boundary > tlo + l always)
 #pragma unroll 1
             for (; l + 2 <= end; l += 2) {
                 const float4 qa = L[2 * l], qb = L[2 * l + 1], ra = L[2 * l + 2], rb = L[2 * l + 3];
@@ -1222,13 +1226,13 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 seg_light_geometry(ra, rb, A, D, nb1, h1);
                 const float2 W0 = make_float2(qb.z, qb.w), W1 = make_float2(rb.z, rb.w);
 #pragma unroll
-                for (int k = 0; k < LEN; k++) {
-                    const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
-                    const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
-                    const float2 ab = __fmul2_rn(a, b);
-                    const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
-                    acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
-                }
+                    for (int k = 0; k < LEN; k++) {
+                        const float2 u0 = __fadd2_rn(s[k], nb0), u1 = __fadd2_rn(s[k], nb1);
+                        const float2 a = seg_dist2<SPHERE>(__ffma2_rn(u0, u0, h0), nR), b = seg_dist2<SPHERE>(__ffma2_rn(u1, u1, h1), nR);
+                        const float2 ab = __fmul2_rn(a, b);
+                        const float2 num = __ffma2_rn(W1, a, __fmul2_rn(W0, b));
+                        acc[k] = __ffma2_rn(num, make_float2(rcp_approx(ab.x), rcp_approx(ab.y)), acc[k]);
+                    }
             }
             if (l < end) {  // odd tail of the list (slices are whole pairs: this is the list's last light)
                 const float4 qa = L[2 * l], qb = L[2 * l + 1];
@@ -1243,10 +1247,10 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
                 }
                 l++;
             }
-            if (tlo + (uint64_t)l == boundary && boundary < nl) {  // end of a slice with more to come: total (+)= acc
+            if (tlo + (uint32_t)l == boundary && boundary < nl) {  // end of a slice with more to come: total (+)= acc
 #pragma unroll
                 for (int k = 0; k < LEN; k++) {
-                    float2* pp = part + k * EVAL_THREADS + tid;
+                    float2* pp = part + k * THREADS + tid;
                     *pp = spilled ? __fadd2_rn(*pp, acc[k]) : acc[k];
                     acc[k] = make_float2(0.f, 0.f);
                 }
@@ -1258,7 +1262,7 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_seg(VrGridDev g, vr
     }
     if (spilled) {
 #pragma unroll
-        for (int k = 0; k < LEN; k++) acc[k] = __fadd2_rn(part[k * EVAL_THREADS + tid], acc[k]);
+        for (int k = 0; k < LEN; k++) acc[k] = __fadd2_rn(part[k * THREADS + tid], acc[k]);
     }
 
     // ---- full unit: out = w * total. Slice unit: the running total lives in `out`, the last slice applies the weight
@@ -1924,50 +1928,57 @@ static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* sampl
     }
 }
 
-// resident CTAs of a segment kernel on this GPU (the "wave" its tail distribution is planned for); also opts the kernel
-// into its dynamic shared memory on the current device (function attributes are per device: vr_group drives several)
-template <class K>
-static uint32_t seg_slots(K kernel, uint32_t smem, uint32_t (&cache)[64]) {
-    int dev = 0, sms = 0, per_sm = 0;
+// one launch of a segment kernel instance over a table of at most `cap` entries: all full units, or up to one resident
+// wave of chunks in SEG_SPLIT slice units each; CTAs whose ticket is beyond the work leave at once (the table lengths
+// live on the device). The resident wave ("slots") is asked from the occupancy calculator once per device, which is also
+// where the kernel is opted into its dynamic shared memory (function attributes are per device: vr_group drives several).
+template <int THREADS, int MINB, bool SPHERE, int LEN, bool SLICE, class... Args>
+static void launch_seg(cudaStream_t st, uint64_t cap, uint32_t slots_override, Args... args) {
+    if (!cap) return;
+    auto kernel = k_eval_seg<THREADS, MINB, SPHERE, LEN, SLICE>;
+    constexpr uint32_t smem = seg_smem_bytes(SLICE ? 0 : LEN, THREADS);
+    static uint32_t cache[64];  // (benign race: every thread computes the same value)
+    int dev = 0;
     cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && cache[dev]) return cache[dev];
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, EVAL_THREADS, smem);
-    const uint32_t slots = (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
-    if (dev >= 0 && dev < 64) cache[dev] = slots;
-    return slots;
+    uint32_t slots = dev >= 0 && dev < 64 ? cache[dev] : 0;
+    if (!slots) {
+        // the resident wave of the FULL instance on this device (the slice instance is planned for the same number)
+        auto full = k_eval_seg<THREADS, MINB, SPHERE, LEN, false>;
+        constexpr uint32_t smem_full = seg_smem_bytes(LEN, THREADS);
+        int sms = 0, per_sm = 0;
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, full, THREADS, smem_full);
+        slots = (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
+        if (dev >= 0 && dev < 64) cache[dev] = slots;
+    }
+    if (slots_override) slots = slots_override;  // (e.g. every chunk of a small table as slice units)
+    const uint64_t chunks = (cap + 2 * THREADS - 1) / (2 * THREADS);
+    const uint64_t sliced = chunks < slots ? chunks : slots;
+    const uint64_t grid = SLICE ? sliced * SEG_SPLIT : chunks - sliced;
+    if (!grid) return;
+    VR_COUNT(1);
+    kernel<<<(unsigned)grid, THREADS, smem, st>>>(args..., slots);
 }
 // Evaluation pass of the ray-segment path. Main stream: near-light flags, the flagged entries onto the exact kernel's list,
 // then the big segment kernel. Side stream (lower priority, forked once the list is complete): the odd 8-sample segments and
 // the exact kernel over the list (leftovers + near-light segments) -- independent work whose CTAs fill the SMs that the big
 // kernel's end leaves idle. After the join: the exact kernel on whatever the segment kernels handed over themselves
 // (entries whose samples deviate too much from their line; normally none: a small grid-stride launch over the second list).
-void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join, const VrGridDev& g,
-                        const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
+void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaStream_t side2, cudaEvent_t ev_fork, cudaEvent_t ev_join, cudaEvent_t ev_join2,
+                        const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
                         const unsigned long long* nlights_dev, float rho, int sphere, float radius, float* out,
                         unsigned long long* redo_count) {
     if (nsamples == 0) return;
     if (!side) side = st;
-    static uint32_t cache16[64], cache8[64], cache8s[64];  // (benign race: every thread computes the same values)
-    constexpr uint32_t smem16 = seg_smem_bytes(16), smem8 = seg_smem_bytes(8);
-    const uint32_t slots16 = sphere ? 0 : seg_slots(k_eval_seg<2, false, 16>, smem16, cache16);
-    const uint32_t slots8 = sphere ? 0 : seg_slots(k_eval_seg<2, false, 8>, smem8, cache8);
-    const uint32_t slots8s = sphere ? seg_slots(k_eval_seg<2, true, 8>, smem8, cache8s) : 0;
+    if (!side2) side2 = side;
     const uint64_t seg_cap = nsamples / SEG_LEN;
     const bool small = nsamples < 40ull * 1000 * 1000;  // short lists: 4 samples per thread, twice the CTAs at half the duration
     const uint64_t cap16 = sphere ? 0 : seg_cap / 2;
     const uint64_t cap8 = sphere ? seg_cap : (seg_cap < npix ? seg_cap : npix);  // point-type: at most one odd segment per pixel
-    // launches are sized by the tables' upper bounds (the lengths live on the device): all full units, or up to `slots`
-    // chunks in SEG_SPLIT slice units each; CTAs whose ticket is beyond the work leave at once
-    auto grid_of = [](uint64_t cap, uint32_t slots) {
-        const uint64_t chunks = (cap + SEG_PER_CTA - 1) / SEG_PER_CTA;
-        const uint64_t sliced = chunks < slots ? chunks : slots;
-        return (unsigned)(chunks - sliced + sliced * SEG_SPLIT);
-    };
-    cudaMemsetAsync(sl.sched16, 0, sl.sched_bytes, st);  // ticket counters and per-chunk slice counters of both kernels
+    cudaMemsetAsync(sl.sched16, 0, sl.sched_bytes, st);  // ticket counters and per-chunk slice counters of both tables
     VR_COUNT(1);
     k_seg_begin<<<1, 1, 0, st>>>(sl);
     if (seg_cap) {
@@ -1986,22 +1997,30 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork,
     if (side != st) {
         cudaEventRecord(ev_fork, st);
         cudaStreamWaitEvent(side, ev_fork, 0);
+        if (side2 != side) cudaStreamWaitEvent(side2, ev_fork, 0);
     }
+    // Launch order = the order in which the pieces should start: the full units (longest), then the slice units of the big
+    // table's last wave, the odd 8-sample segments (all as slice units: the table is small), the exact kernel's short CTAs.
+    constexpr uint32_t WAVE = 0u, ALL = 0xffffffffu;  // chunks that run as slice units: the last resident wave / all
     if (seg_cap) {
-        VR_COUNT(1);
         if (sphere) {
-            k_eval_seg<2, true, 8><<<grid_of(cap8, slots8s), EVAL_THREADS, smem8, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out, slots8s);
+            launch_seg<256, 2, true, 8, false>(st, cap8, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+            launch_seg<256, 2, true, 8, true>(side, cap8, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
         } else {
-            if (cap16) k_eval_seg<2, false, 16><<<grid_of(cap16, slots16), EVAL_THREADS, smem16, st>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots16);
-            VR_COUNT(1);
-            k_eval_seg<2, false, 8><<<grid_of(cap8, slots8), EVAL_THREADS, smem8, side>>>(g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out, slots8);
+            launch_seg<256, 2, false, 16, false>(st, cap16, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 16, true>(side, cap16, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 8, true>(side2, cap8, ALL, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
         }
     }
     // the list is complete since k_list_flagged (the segment kernels hand over into the second list)
-    launch_exact_list(side, sphere, samples, nsamples, small, false, sl.list, sl.counts + 2, lights2, nlights_dev, radius, out, redo_count);
+    launch_exact_list(side2, sphere, samples, nsamples, small, false, sl.list, sl.counts + 2, lights2, nlights_dev, radius, out, redo_count);
     if (side != st) {
         cudaEventRecord(ev_join, side);
         cudaStreamWaitEvent(st, ev_join, 0);
+        if (side2 != side) {
+            cudaEventRecord(ev_join2, side2);
+            cudaStreamWaitEvent(st, ev_join2, 0);
+        }
     }
     launch_exact_list(st, sphere, samples, seg_cap * SEG_LEN, true, true, sl.list2, sl.counts + 7, lights2, nlights_dev, radius, out, redo_count);
 }

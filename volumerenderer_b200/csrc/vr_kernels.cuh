@@ -108,8 +108,9 @@ struct VrSegLists {
 void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
                         int pairs);
 // lights / lights2: the same list in both layouts; nlights_capacity sizes the flagging launch (one block per light)
-// side (may be NULL = st): a second stream for the independent small kernels; ev_fork / ev_join order the two streams
-void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join, const VrGridDev& g,
+// side, side2 (may be NULL = st): lower-priority streams for the slice units and the small kernels (they run next to the
+// full units of the big kernel and fill its tail); ev_fork / ev_join / ev_join2 order the streams
+void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaStream_t side2, cudaEvent_t ev_fork, cudaEvent_t ev_join, cudaEvent_t ev_join2, const VrGridDev& g,
                         const vr_ubo& u, float tan_scale, vr_tile tile, const VrSample* samples,
                         uint64_t nsamples, uint64_t npix, const uint32_t* counts, const unsigned long long* offsets, const VrSegLists& sl,
                         const VrEvalLight* lights, const float4* lights2, uint64_t nlights_capacity,
