@@ -174,6 +174,7 @@ struct vr_ctx {
     DevBuf<float> contrib;
     // ray-segment evaluation (eval_variant 8): segment table + index list of the exact kernel, rebuilt with the march
     DevBuf<uint32_t> seg_first, seg_pix, seg_flag, seg16_first, seg16_pix, seg16_flag, seg_list, seg_list2, seg_base, seg_sched;
+    DevBuf<float> seg_part16, seg_part8;  // scratch of the slice units of k_eval_seg
     DevBuf<uint8_t> seg_flags;
     unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
     bool seg_valid = false;                    // tables match the cached march
@@ -194,7 +195,6 @@ struct vr_ctx {
     struct Scalars {
         unsigned long long nsamples, neval, S_ref, S_eff;
         uint32_t light_count, overflow;
-        unsigned long long seg_stalled;
     };
     Scalars* scalars_host = nullptr;
     cudaEvent_t ev_scalars = nullptr;
@@ -408,7 +408,6 @@ int enqueue_scalars(vr_ctx* c, cudaStream_t st, bool have_march) {
     if (have_march) VR_CUDA(c, cudaMemcpyAsync(&h->S_ref, c->wc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaMemcpyAsync(&h->light_count, &c->counter->lightCount, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaMemcpyAsync(&h->overflow, c->expand_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    VR_CUDA(c, cudaMemcpyAsync(&h->seg_stalled, c->seg_counts + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     VR_CUDA(c, cudaEventRecord(c->ev_scalars, st));
     c->counters_pending = true;
     c->counters_have_march = have_march;
@@ -424,7 +423,6 @@ int finalize_counters(vr_ctx* c) {
         c->last_counters.S_eff = c->cached_S[1] = h.S_eff;
     }
     if (h.overflow) return fail(c, VR_E_STATE, "internal: the expanded light list overflowed its buffer");
-    if (h.seg_stalled) return fail(c, VR_E_STATE, "internal: a slice-order wait of the segment kernel gave up in an earlier frame");
     if (c->last_algo == VR_ALGO_PATH) {
         c->last_counters.E = h.S_eff;
         return VR_OK;
@@ -593,6 +591,8 @@ int vr_destroy(vr_ctx* c) {
     c->seg_list.release();
     c->seg_list2.release();
     c->seg_sched.release();
+    c->seg_part16.release();
+    c->seg_part8.release();
     c->seg_base.release();
     c->seg_flag.release();
     c->seg16_first.release();
@@ -1138,6 +1138,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
             VR_CUDA(c, c->seg_list2.reserve(nreal + 1));
             VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 128 + 4)));  // per kernel instance: ticket + one word per chunk
             VR_CUDA(c, c->seg_base.reserve(npix + 1));
+            VR_CUDA(c, c->seg_part16.reserve(vrk_seg_part_floats(16)));
+            VR_CUDA(c, c->seg_part8.reserve(vrk_seg_part_floats(8)));
         }
         sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
         sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
@@ -1145,6 +1147,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         {
             const uint64_t per = nreal / 8 / 128 + 4;  // chunks of at least 128 entries (two per thread), at most nreal / 8 entries
             sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
+            sl.part16 = c->seg_part16.p, sl.part8 = c->seg_part8.p;
         }
         sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
         sl.list_capacity = (uint32_t)nreal;

@@ -979,7 +979,7 @@ __global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl, uint32_t bl
 // start of an evaluation pass: the exact kernel's list restarts from the leftovers, nothing handed over yet, no give-up flag
 __global__ void k_seg_begin(VrSegLists sl) {
     sl.counts[2] = sl.counts[1];
-    sl.counts[7] = 0;  // (counts[6], the stall mark of k_eval_seg, is never cleared: it is a bug report)
+    sl.counts[7] = 0;
     *sl.flag_all = 0u;
 }
 
@@ -1018,38 +1018,19 @@ __device__ __forceinline__ float2 seg_dist2(const float2 l2, const float2 nR) {
 // LEN = 8: one segment per half; LEN = 16: two consecutive segments of the same pixel per half (table sl.seg16_*), so the
 // per-light geometry is shared by 16 samples; their weights are read again at the end instead of held in registers.
 //
-// Work distribution. A chunk is SEG_PER_CTA table entries, and every sample's light sum is DEFINED as the sum over
+// Work distribution. A chunk is 2 * THREADS table entries, and every sample's light sum is DEFINED as the sum over
 // SEG_SPLIT consecutive slices of the light list, added in slice order and weighted once: out = w*(((S0 + S1) + S2) + S3).
 // A "full" unit is one CTA that walks the whole list for a chunk in one uninterrupted loop (entries stay in registers); at
 // a slice boundary it moves its accumulators into a running total in shared memory (3 x 16 LDS/STS per thread per chunk,
-// no global traffic, no pipeline restart). A "slice" unit is one CTA per (chunk, slice); it keeps the running total in
-// `out`. CTAs take units from a ticket counter in the order they start: first the full units of all chunks but the last
-// `slots` (one resident wave), then the slice units of those last chunks, slice 0 first. So the end of the kernel is made
-// of units a quarter as long, and the GPU drains evenly: the tail of a launch whose chunks fill 3.4 waves (one of eight
-// GPUs' bands) costs a quarter of a CTA time instead of a whole one. Slice units of a chunk add to `out` in slice order
-// (a per-chunk counter; a unit's predecessor always holds an earlier ticket, i.e. is running or done: no deadlock), so
-// the result does not depend on which kind of unit produced it -- a tiled render equals the whole frame bit for bit
-// (tests/test_gpu_configs.py).
+// no global traffic, no pipeline restart). A "slice" unit is one CTA per (chunk, slice): it writes its slice's sums to a
+// scratch buffer, and whichever of a chunk's SEG_SPLIT units finishes last (a per-chunk counter) adds the four partial
+// sums in slice order and stores the results -- nobody waits for anybody. The full units (instance SLICE = false, main
+// stream) cover all chunks but the last `slots` (one resident wave); those last chunks run as slice units (instance
+// SLICE = true, a lower-priority stream: its CTAs take the SM slots the full units free). So the end of the pass is made
+// of units a quarter as long, and the GPU drains evenly: the tail of a launch whose chunks fill 3.05 waves (one of eight
+// GPUs' bands) costs a quarter of a CTA time instead of a whole one. The result does not depend on which kind of unit
+// produced it -- a tiled render equals the whole frame bit for bit (tests/test_gpu_configs.py).
 constexpr int SEG_SPLIT = 4;
-__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-// wait until *p >= want. The unit waited for always holds an earlier ticket (it is running or done), so this ends; the
-// bound only keeps a bug from hanging the GPU: it leaves a mark (counts[6]) that the host reports.
-__device__ __forceinline__ void wait_slices(const uint32_t* p, uint32_t want, unsigned long long* stalled) {
-    for (uint32_t spin = 0; ld_acquire_u32(p) < want; spin++) {
-        __nanosleep(100);
-        if (spin > (1u << 24)) {
-            atomicExch(stalled, 1ull);
-            break;
-        }
-    }
-}
-__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 // lights per slice: a quarter of the list rounded up to whole pairs (the loop shares one reciprocal between two lights, so
 // slice boundaries must not split the pairs the unsliced list would form), at least 64
 __host__ __device__ __forceinline__ uint64_t seg_slice_len(uint64_t nlights) {
@@ -1086,11 +1067,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
     uint32_t chunk = blockIdx.x, q0 = 0;
     constexpr bool sliced = SLICE;
     if (SLICE) {
-        __shared__ uint32_t s_unit;
-        if (tid == 0) s_unit = atomicAdd(sched, 1u);
-        __syncthreads();
-        const uint32_t r = s_unit;
-        chunk = nfull + r / SEG_SPLIT, q0 = r % SEG_SPLIT;
+        chunk = nfull + blockIdx.x / SEG_SPLIT, q0 = blockIdx.x % SEG_SPLIT;
         if (chunk >= nchunks) return;  // the launch is sized by the capacity, the segment count lives on the device
     } else if (chunk >= nfull) {
         return;
@@ -1112,13 +1089,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
         }
         idle = __syncthreads_and(listed) != 0;
     }
-    if (idle) {
-        if (sliced && tid == 0) {  // keep the chunk's slice order going for the units behind this one
-            wait_slices(done, q0, &sl.counts[6]);
-            st_release_u32(done, q0 + 1);
-        }
-        return;
-    }
+    if (idle) return;  // (all SEG_SPLIT slice units of a chunk see the same flags: none of them reports to the chunk's counter)
     // (list lengths are below 2^32: vr_dispatch_compute_color refuses longer expansions; 32-bit counters spare registers)
     const uint32_t nlights = (uint32_t)*nlights_dev;
     const uint32_t slice_len = (uint32_t)seg_slice_len(nlights);
@@ -1265,28 +1236,48 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
         for (int k = 0; k < LEN; k++) acc[k] = __fadd2_rn(part[k * THREADS + tid], acc[k]);
     }
 
-    // ---- full unit: out = w * total. Slice unit: the running total lives in `out`, the last slice applies the weight
-    if (sliced && q0 > 0) {
-        if (tid == 0) wait_slices(done, q0, &sl.counts[6]);
-        __syncthreads();
-    }
-    const bool last = !sliced || q0 == SEG_SPLIT - 1;
+    // ---- full unit: out = w * total
+    if (!SLICE) {
 #pragma unroll
-    for (int h = 0; h < 2; h++) {
-        if (first[h] == 0xffffffffu || skip[h]) continue;
+        for (int h = 0; h < 2; h++) {
+            if (first[h] == 0xffffffffu || skip[h]) continue;
 #pragma unroll
-        for (int k = 0; k < LEN; k++) {
-            float* o = out + first[h] + k;
-            float v = h == 0 ? acc[k].x : acc[k].y;
-            if (sliced && q0 > 0) v = __fadd_rn(__ldcg(o), v);
-            if (last) v = (KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w)) * v;
-            *o = v;
+            for (int k = 0; k < LEN; k++) {
+                const float v = h == 0 ? acc[k].x : acc[k].y;
+                out[first[h] + k] = (KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w)) * v;
+            }
         }
-    }
-    if (sliced) {
+    } else {
+        // ---- slice unit: partial sums to the scratch buffer ([slice][k][entry of the chunk]: coalesced); the unit that
+        // finishes last adds the chunk's SEG_SPLIT partial sums in slice order
+        float* __restrict__ pc = (LEN == 16 ? sl.part16 : sl.part8) + (uint64_t)(chunk - nfull) * (SEG_SPLIT * LEN * SEG_PER_CTA);
+        float* __restrict__ pq = pc + q0 * (LEN * SEG_PER_CTA);
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            if (first[h] == 0xffffffffu || skip[h]) continue;
+#pragma unroll
+            for (int k = 0; k < LEN; k++) __stcg(pq + k * SEG_PER_CTA + h * THREADS + tid, h == 0 ? acc[k].x : acc[k].y);
+        }
         __threadfence();
+        __shared__ uint32_t s_arrived;
         __syncthreads();
-        if (tid == 0) st_release_u32(done, q0 + 1);
+        if (tid == 0) s_arrived = atomicAdd(done, 1u);
+        __syncthreads();
+        if (s_arrived == SEG_SPLIT - 1) {
+            __threadfence();
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                if (first[h] == 0xffffffffu || skip[h]) continue;
+#pragma unroll
+                for (int k = 0; k < LEN; k++) {
+                    const float* pe = pc + k * SEG_PER_CTA + h * THREADS + tid;
+                    float t = __ldcg(pe);
+#pragma unroll
+                    for (int q = 1; q < SEG_SPLIT; q++) t = __fadd_rn(t, __ldcg(pe + q * (LEN * SEG_PER_CTA)));
+                    out[first[h] + k] = (KEEP_W ? sw[h][k] : __ldg(&samples[first[h] + k].w)) * t;
+                }
+            }
+        }
     }
 
     if (q0 == 0) {  // entries handed over to the exact kernel (second list): announced once per chunk
@@ -1932,27 +1923,37 @@ static void launch_exact_list(cudaStream_t st, int sphere, const VrSample* sampl
 // wave of chunks in SEG_SPLIT slice units each; CTAs whose ticket is beyond the work leave at once (the table lengths
 // live on the device). The resident wave ("slots") is asked from the occupancy calculator once per device, which is also
 // where the kernel is opted into its dynamic shared memory (function attributes are per device: vr_group drives several).
-template <int THREADS, int MINB, bool SPHERE, int LEN, bool SLICE, class... Args>
-static void launch_seg(cudaStream_t st, uint64_t cap, uint32_t slots_override, Args... args) {
-    if (!cap) return;
-    auto kernel = k_eval_seg<THREADS, MINB, SPHERE, LEN, SLICE>;
-    constexpr uint32_t smem = seg_smem_bytes(SLICE ? 0 : LEN, THREADS);
+// resident wave of the full-unit instance on the current device (cached per device)
+template <int THREADS, int MINB, bool SPHERE, int LEN>
+static uint32_t seg_wave() {
     static uint32_t cache[64];  // (benign race: every thread computes the same value)
     int dev = 0;
     cudaGetDevice(&dev);
     uint32_t slots = dev >= 0 && dev < 64 ? cache[dev] : 0;
     if (!slots) {
-        // the resident wave of the FULL instance on this device (the slice instance is planned for the same number)
         auto full = k_eval_seg<THREADS, MINB, SPHERE, LEN, false>;
-        constexpr uint32_t smem_full = seg_smem_bytes(LEN, THREADS);
+        auto slice = k_eval_seg<THREADS, MINB, SPHERE, LEN, true>;
+        constexpr uint32_t smem_full = seg_smem_bytes(LEN, THREADS), smem_slice = seg_smem_bytes(0, THREADS);
         int sms = 0, per_sm = 0;
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(full, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full);
+        cudaFuncSetAttribute(slice, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_slice);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, full, THREADS, smem_full);
         slots = (uint32_t)(sms * (per_sm > 0 ? per_sm : 1));
         if (dev >= 0 && dev < 64) cache[dev] = slots;
     }
-    if (slots_override) slots = slots_override;  // (e.g. every chunk of a small table as slice units)
+    return slots;
+}
+uint64_t vrk_seg_part_floats(int len) {
+    const uint32_t slots = len == 16 ? seg_wave<256, 2, false, 16>() : max(seg_wave<256, 2, false, 8>(), seg_wave<256, 2, true, 8>());
+    return (uint64_t)slots * SEG_SPLIT * (uint64_t)len * 512u;
+}
+template <int THREADS, int MINB, bool SPHERE, int LEN, bool SLICE, class... Args>
+static void launch_seg(cudaStream_t st, uint64_t cap, Args... args) {
+    if (!cap) return;
+    auto kernel = k_eval_seg<THREADS, MINB, SPHERE, LEN, SLICE>;
+    constexpr uint32_t smem = seg_smem_bytes(SLICE ? 0 : LEN, THREADS);
+    const uint32_t slots = seg_wave<THREADS, MINB, SPHERE, LEN>();
     const uint64_t chunks = (cap + 2 * THREADS - 1) / (2 * THREADS);
     const uint64_t sliced = chunks < slots ? chunks : slots;
     const uint64_t grid = SLICE ? sliced * SEG_SPLIT : chunks - sliced;
@@ -1999,17 +2000,18 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaStream_t side2, 
         cudaStreamWaitEvent(side, ev_fork, 0);
         if (side2 != side) cudaStreamWaitEvent(side2, ev_fork, 0);
     }
-    // Launch order = the order in which the pieces should start: the full units (longest), then the slice units of the big
-    // table's last wave, the odd 8-sample segments (all as slice units: the table is small), the exact kernel's short CTAs.
-    constexpr uint32_t WAVE = 0u, ALL = 0xffffffffu;  // chunks that run as slice units: the last resident wave / all
+    // Launch order = the order in which the pieces should start: the full units (longest) on the main stream; on the
+    // lower-priority streams the slice units of the big table's last wave, the odd 8-sample segments, the exact kernel's
+    // short CTAs.
     if (seg_cap) {
         if (sphere) {
-            launch_seg<256, 2, true, 8, false>(st, cap8, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
-            launch_seg<256, 2, true, 8, true>(side, cap8, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+            launch_seg<256, 2, true, 8, false>(st, cap8, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
+            launch_seg<256, 2, true, 8, true>(side, cap8, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, radius, out);
         } else {
-            launch_seg<256, 2, false, 16, false>(st, cap16, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
-            launch_seg<256, 2, false, 16, true>(side, cap16, WAVE, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
-            launch_seg<256, 2, false, 8, true>(side2, cap8, ALL, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 16, false>(st, cap16, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 16, true>(side, cap16, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 8, false>(side2, cap8, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
+            launch_seg<256, 2, false, 8, true>(side2, cap8, g, u, tan_scale, tile, samples, sl, lights2, nlights_dev, rho, 0.0f, out);
         }
     }
     // the list is complete since k_list_flagged (the segment kernels hand over into the second list)

@@ -95,16 +95,19 @@ struct VrSegLists {
     uint32_t* list;               // samples for the exact kernel: leftovers, then the near-light entries (k_list_flagged)
     uint32_t* list2;              // samples the segment kernels hand over themselves (residual check): evaluated after the join
     unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + near-light), [3] flag_all,
-                                  // [4] seg16 entries, [5] segments (flag numbers), [6] set if a slice-order wait of
-                                  // k_eval_seg ever gave up (must stay 0), [7] list2 length
+                                  // [4] seg16 entries, [5] segments (flag numbers), [6] unused, [7] list2 length
     uint32_t list_capacity;       // of list and of list2
-    // work distribution of k_eval_seg: [0] ticket counter, [1 + c] slices of chunk c accumulated; one array per kernel
-    // instance (16- and 8-sample tables run concurrently), allocated back to back (sched_bytes from sched16), zeroed per pass
+    // work distribution of k_eval_seg: [1 + c] = slice units of chunk c that have delivered their partial sums; one array per
+    // table (the kernels of both run concurrently), allocated back to back (sched_bytes from sched16), zeroed per pass
     uint32_t *sched16, *sched8;
+    // scratch of the slice units: [chunk of the last wave][slice][sample of the entry][entry]: vrk_seg_part_floats(len) floats
+    float *part16, *part8;
     uint64_t sched_bytes;
 };
 // builds seg_first / seg_pix / the leftover part of list from the per-pixel sample counts and offsets (nsamples < 2^32)
 // pairs != 0: pairs of segments go to the 16-sample table (point-type lists); 0: every segment to the 8-sample table
+// floats of VrSegLists::part16 (len 16) / part8 (len 8) on the current device
+uint64_t vrk_seg_part_floats(int len);
 void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
                         int pairs);
 // lights / lights2: the same list in both layouts; nlights_capacity sizes the flagging launch (one block per light)
