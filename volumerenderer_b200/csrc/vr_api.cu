@@ -175,6 +175,7 @@ struct vr_ctx {
     // ray-segment evaluation (eval_variant 8): segment table + index list of the exact kernel, rebuilt with the march
     DevBuf<uint32_t> seg_first, seg_pix, seg_flag, seg16_first, seg16_pix, seg16_flag, seg_list, seg_list2, seg_base, seg_sched;
     DevBuf<float> seg_part16, seg_part8;  // scratch of the slice units of k_eval_seg
+    uint64_t seg_reserved_for = 0, seg_reserved_npix = 0;  // sample count / pixels the tables were last sized for
     DevBuf<uint8_t> seg_flags;
     unsigned long long* seg_counts = nullptr;  // device: [0] segments, [1] leftovers, [2] exact-list length
     bool seg_valid = false;                    // tables match the cached march
@@ -879,6 +880,38 @@ static int check_light_gen_args(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t g
     return VR_OK;
 }
 
+// buffers of the ray-segment evaluation for a march with `nreal` samples (tables, index lists, flags, work distribution)
+static int reserve_seg_tables(vr_ctx* c, uint64_t nreal, uint64_t npix) {
+    const uint64_t n8 = nreal / 8 + 1;
+    VR_CUDA(c, c->seg_first.reserve(n8));
+    VR_CUDA(c, c->seg_pix.reserve(n8));
+    VR_CUDA(c, c->seg_flag.reserve(n8));
+    VR_CUDA(c, c->seg16_first.reserve(nreal / 16 + 1));
+    VR_CUDA(c, c->seg16_pix.reserve(nreal / 16 + 1));
+    VR_CUDA(c, c->seg16_flag.reserve(nreal / 16 + 1));
+    VR_CUDA(c, c->seg_flags.reserve(nreal / 8 + 2));
+    VR_CUDA(c, c->seg_list.reserve(nreal + 1));
+    VR_CUDA(c, c->seg_list2.reserve(nreal + 1));
+    VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 128 + 4)));  // per table: one word per chunk (+ spare)
+    VR_CUDA(c, c->seg_base.reserve(npix + 1));
+    VR_CUDA(c, c->seg_part16.reserve(vrk_seg_part_floats(16)));
+    VR_CUDA(c, c->seg_part8.reserve(vrk_seg_part_floats(8)));
+    c->seg_reserved_for = nreal;
+    c->seg_reserved_npix = npix;
+    return VR_OK;
+}
+static void fill_seg_lists(vr_ctx* c, uint64_t nreal, VrSegLists* out) {
+    VrSegLists& sl = *out;
+    sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
+    sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
+    sl.list = c->seg_list.p, sl.list2 = c->seg_list2.p, sl.counts = c->seg_counts;
+    const uint64_t per = nreal / 8 / 128 + 4;  // chunks of at least 128 entries (two per thread), at most nreal / 8 entries
+    sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
+    sl.part16 = c->seg_part16.p, sl.part8 = c->seg_part8.p;
+    sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
+    sl.list_capacity = (uint32_t)nreal;
+}
+
 // everything vr_dispatch_compute_color rejects that does not depend on the tile: checked before anything is enqueued
 static int check_gather_args(vr_ctx* c, vr_algo algo) {
     if (!c->have_grid) return fail(c, VR_E_STATE, "no grid: call vr_set_grid first");
@@ -979,6 +1012,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     bool same_key = (key == c->march_key);  // same rays over the same grid as the previous gather
     const bool reuse = c->march_cache && same_key;
     uint64_t nsamples = c->cached_samples, nreal = c->cached_real;
+    int built_by_march = -1;  // 0 / 1: the march wrote the segment tables itself (without / with 16-sample pairs)
     if (!reuse) {
         VR_CUDA(c, c->px_counts.reserve(npix));
         VR_CUDA(c, c->px_offsets.reserve(npix));
@@ -1017,7 +1051,20 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         if (key.gaps) nsamples = c->bound_extent;
         if (key.gaps) {
             // same rays as before: the slots (offsets, total) are still valid, the march alone runs again
-            vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 2, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, c->wc);
+            // Same rays over the same grid as the previous gather (the steady state of a progressive render: the reference
+            // marches every frame): the sample count, hence the size of every segment table, is known, and the march writes
+            // the tables itself -- one launch less between the march and the evaluation.
+            const int pairs = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 0 : 1;
+            if (same_key && c->cached_real > 0 && c->cached_real < 0xffffffffull && c->seg_reserved_for == c->cached_real &&
+                c->seg_reserved_npix >= npix) {
+                VrSegLists sl;
+                fill_seg_lists(c, c->cached_real, &sl);
+                vrk_march_build(st, c->gdev, c->ubo, tan_scale, tile, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p,
+                                c->wc, sl, pairs);
+                built_by_march = pairs;
+            } else {
+                vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 2, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, c->wc);
+            }
             if (!same_key) {  // the number of samples sizes the segment tables and the evaluation launches: second blocking read
                 VR_CUDA(c, cudaMemcpyAsync(c->totals_host + 2, &c->wc->S_eff, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
                 VR_CUDA(c, cudaStreamSynchronize(st));
@@ -1045,7 +1092,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         c->cached_samples = nsamples;
         c->cached_real = nreal;
         c->march_key = key;
-        c->seg_valid = false;
+        c->seg_valid = built_by_march >= 0;
+        if (built_by_march >= 0) c->seg_pairs = built_by_march;
     }
     VR_CUDA(c, c->contrib.reserve(nsamples + 1));
     c->nsamples_used = nsamples;
@@ -1126,31 +1174,10 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         VrSegLists sl;
         if (c->seg_pairs != (sphere ? 0 : 1)) c->seg_valid = false;
         if (!c->seg_valid) {
-            const uint64_t n8 = nreal / 8 + 1;
-            VR_CUDA(c, c->seg_first.reserve(n8));
-            VR_CUDA(c, c->seg_pix.reserve(n8));
-            VR_CUDA(c, c->seg_flag.reserve(n8));
-            VR_CUDA(c, c->seg16_first.reserve(nreal / 16 + 1));
-            VR_CUDA(c, c->seg16_pix.reserve(nreal / 16 + 1));
-            VR_CUDA(c, c->seg16_flag.reserve(nreal / 16 + 1));
-            VR_CUDA(c, c->seg_flags.reserve(nreal / 8 + 2));
-            VR_CUDA(c, c->seg_list.reserve(nreal + 1));
-            VR_CUDA(c, c->seg_list2.reserve(nreal + 1));
-            VR_CUDA(c, c->seg_sched.reserve(2 * (nreal / 8 / 128 + 4)));  // per kernel instance: ticket + one word per chunk
-            VR_CUDA(c, c->seg_base.reserve(npix + 1));
-            VR_CUDA(c, c->seg_part16.reserve(vrk_seg_part_floats(16)));
-            VR_CUDA(c, c->seg_part8.reserve(vrk_seg_part_floats(8)));
+            rc = reserve_seg_tables(c, nreal, npix);
+            if (rc != VR_OK) return rc;
         }
-        sl.seg_first = c->seg_first.p, sl.seg_pix = c->seg_pix.p, sl.seg_flag = c->seg_flag.p;
-        sl.seg16_first = c->seg16_first.p, sl.seg16_pix = c->seg16_pix.p, sl.seg16_flag = c->seg16_flag.p;
-        sl.list = c->seg_list.p, sl.list2 = c->seg_list2.p, sl.counts = c->seg_counts;
-        {
-            const uint64_t per = nreal / 8 / 128 + 4;  // chunks of at least 128 entries (two per thread), at most nreal / 8 entries
-            sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
-            sl.part16 = c->seg_part16.p, sl.part8 = c->seg_part8.p;
-        }
-        sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
-        sl.list_capacity = (uint32_t)nreal;
+        fill_seg_lists(c, nreal, &sl);
         if (!c->seg_valid) {
             vrk_build_segments(st, c->px_counts.p, c->px_offsets.p, npix, sl, sphere ? 0 : 1);
             c->seg_valid = true;

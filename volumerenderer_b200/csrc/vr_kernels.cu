@@ -305,22 +305,67 @@ __global__ void __launch_bounds__(128) k_march_bound(VrGridDev g, vr_ubo u, floa
     bound[(uint64_t)ly * tile.w + lx] = n;
 }
 
+// table entries of one warp's 32 pixels (c = the pixel's sample count, off = its first sample, p = tile-local pixel
+// index; lanes without a pixel pass c = 0). Called by k_build_segments, and by the single-pass march itself when the
+// tables' sizes are known beforehand (same rays over the same grid as the previous frame).
+__device__ __forceinline__ void seg_build_warp(const uint32_t c, const uint32_t off, const uint64_t p, const bool has_pixel,
+                                               const VrSegLists& sl, const int pairs, const uint32_t lane) {
+    // q full segments of 8; r leftovers. pairs: q/2 pairs go to the 16-sample table and an odd last one to the 8-sample
+    // table (point-type lists: the FMA-bound kernel gains from sharing the geometry between 16 samples); else all q go
+    // to the 8-sample table (sphere-type lists: MUFU-bound, nothing to gain, and the flags stay finer)
+    const uint32_t q = c >> 3, r = c & 7u, q16 = pairs ? q >> 1 : 0u, q8 = q - 2u * q16;
+    uint32_t v[4] = {q, q16, q8, r};  // inclusive warp scans
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const uint32_t a = __shfl_up_sync(0xffffffffu, v[i], o);
+            if (lane >= (uint32_t)o) v[i] += a;
+        }
+    }
+    unsigned long long base[4] = {0, 0, 0, 0};
+    if (lane == 31) {
+        unsigned long long* ctr[4] = {&sl.counts[5], &sl.counts[4], &sl.counts[0], &sl.counts[1]};
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            if (v[i]) base[i] = atomicAdd(ctr[i], (unsigned long long)v[i]);
+    }
+    const uint32_t mine[4] = {q, q16, q8, r};
+#pragma unroll
+    for (int i = 0; i < 4; i++) base[i] = __shfl_sync(0xffffffffu, base[i], 31) + (v[i] - mine[i]);
+    const uint32_t fb = (uint32_t)base[0];  // the pixel's segments are numbered fb .. fb + q - 1 for the near-light flags
+    if (has_pixel) sl.seg_base[p] = fb;
+    for (uint32_t i = 0; i < q16; i++) {
+        sl.seg16_first[base[1] + i] = off + 16u * i;
+        sl.seg16_pix[base[1] + i] = (uint32_t)p;
+        sl.seg16_flag[base[1] + i] = fb + 2u * i;
+    }
+    for (uint32_t i = 0; i < q8; i++) {
+        sl.seg_first[base[2] + i] = off + 16u * q16 + 8u * i;
+        sl.seg_pix[base[2] + i] = (uint32_t)p;
+        sl.seg_flag[base[2] + i] = fb + 2u * q16 + i;
+    }
+    for (uint32_t j = 0; j < r; j++) sl.list[base[3] + j] = off + 8u * q + j;
+}
+
 // MODE 0: count the pixel's samples (counts, work counters); 1: write them at offsets[pix] (after a scan of the counts:
 // compact sample buffer); 2: both in one pass, offsets from a scan of k_march_bound's bounds (sample buffer with gaps)
-template <int MODE, bool TRI>
+// BUILD (MODE 2 only): the warp also writes its pixels' entries of the segment tables (what k_build_segments does)
+template <int MODE, bool TRI, bool BUILD = false>
 __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_scale, vr_tile tile,
                                                 uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
-                                                VrSample* __restrict__ samples, VrWorkCounters* wc) {
+                                                VrSample* __restrict__ samples, VrWorkCounters* wc, VrSegLists sl, int pairs) {
     constexpr bool FILL = MODE != 0, COUNT = MODE != 1;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const uint32_t ly = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
     const bool active = lx < tile.w && ly < tile.h;
-    uint32_t n = 0, sref = 0;
+    uint32_t n = 0, sref = 0, first_slot = 0;
     if (active) {
         const uint32_t px = tile.x0 + lx, py = tile.y0 + ly;
         const uint64_t pix = (uint64_t)ly * tile.w + lx;
         const VrCamRay r = vr_camera_ray(g, u, tan_scale, px, py);
+        if (BUILD) first_slot = (uint32_t)offsets[pix];
         if (r.hit && r.tmax > 0.0f) {
             const float step = u.rayMarchingStepSize;
             float t = vr_max(r.tmin, 0.0f);
@@ -359,6 +404,7 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
         }
         if (COUNT) counts[pix] = n;
     }
+    if (BUILD) seg_build_warp(n, first_slot, (uint64_t)ly * tile.w + lx, active, sl, pairs, lane);
     if (COUNT && wc) {
         unsigned long long a = sref, b = n;
 #pragma unroll
@@ -843,45 +889,9 @@ __global__ void __launch_bounds__(EVAL_THREADS, MINB) k_eval_point3(const VrSamp
 __global__ void __launch_bounds__(256) k_build_segments(const uint32_t* __restrict__ counts, const unsigned long long* __restrict__ offsets,
                                                         uint64_t npix, VrSegLists sl, int pairs) {
     const uint64_t p = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-    const uint32_t lane = threadIdx.x & 31;
     const uint32_t c = p < npix ? counts[p] : 0u;
     const uint32_t off = p < npix ? (uint32_t)offsets[p] : 0u;
-    // q full segments of 8; r leftovers. pairs: q/2 pairs go to the 16-sample table and an odd last one to the 8-sample
-    // table (point-type lists: the FMA-bound kernel gains from sharing the geometry between 16 samples); else all q go
-    // to the 8-sample table (sphere-type lists: MUFU-bound, nothing to gain, and the flags stay finer)
-    const uint32_t q = c >> 3, r = c & 7u, q16 = pairs ? q >> 1 : 0u, q8 = q - 2u * q16;
-    uint32_t v[4] = {q, q16, q8, r};  // inclusive warp scans
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const uint32_t a = __shfl_up_sync(0xffffffffu, v[i], o);
-            if (lane >= (uint32_t)o) v[i] += a;
-        }
-    }
-    unsigned long long base[4] = {0, 0, 0, 0};
-    if (lane == 31) {
-        unsigned long long* ctr[4] = {&sl.counts[5], &sl.counts[4], &sl.counts[0], &sl.counts[1]};
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-            if (v[i]) base[i] = atomicAdd(ctr[i], (unsigned long long)v[i]);
-    }
-    const uint32_t mine[4] = {q, q16, q8, r};
-#pragma unroll
-    for (int i = 0; i < 4; i++) base[i] = __shfl_sync(0xffffffffu, base[i], 31) + (v[i] - mine[i]);
-    const uint32_t fb = (uint32_t)base[0];  // the pixel's segments are numbered fb .. fb + q - 1 for the near-light flags
-    if (p < npix) sl.seg_base[p] = fb;
-    for (uint32_t i = 0; i < q16; i++) {
-        sl.seg16_first[base[1] + i] = off + 16u * i;
-        sl.seg16_pix[base[1] + i] = (uint32_t)p;
-        sl.seg16_flag[base[1] + i] = fb + 2u * i;
-    }
-    for (uint32_t i = 0; i < q8; i++) {
-        sl.seg_first[base[2] + i] = off + 16u * q16 + 8u * i;
-        sl.seg_pix[base[2] + i] = (uint32_t)p;
-        sl.seg_flag[base[2] + i] = fb + 2u * q16 + i;
-    }
-    for (uint32_t j = 0; j < r; j++) sl.list[base[3] + j] = off + 8u * q + j;
+    seg_build_warp(c, off, p, p < npix, sl, pairs, threadIdx.x & 31);
 }
 
 // Which segments come closer than rho to a light? Decided geometrically, from the light's side, before the evaluation:
@@ -1063,7 +1073,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
     uint32_t* __restrict__ sched = LEN == 16 ? sl.sched16 : sl.sched8;  // [0] ticket counter, [1 + c] slices of chunk c done
     const uint32_t tid = threadIdx.x;
     const uint32_t nchunks = (uint32_t)((nseg + SEG_PER_CTA - 1) / SEG_PER_CTA);
-    const uint32_t nsliced = nchunks < slots ? nchunks : slots, nfull = nchunks - nsliced;
+    const uint32_t nsliced = nchunks < slots ? nchunks : slots;
+    const uint32_t nfull = nchunks - nsliced;
     uint32_t chunk = blockIdx.x, q0 = 0;
     constexpr bool sliced = SLICE;
     if (SLICE) {
@@ -1823,7 +1834,8 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
                uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc) {
     VR_COUNT(1);
     dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
-#define VR_MARCH(M, T) k_march<M, T><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc)
+    const VrSegLists none{};
+#define VR_MARCH(M, T) k_march<M, T><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc, none, 0)
     if (trilinear) {
         if (mode == 0) VR_MARCH(0, true);
         else if (mode == 1) VR_MARCH(1, true);
@@ -1834,6 +1846,15 @@ void vrk_march(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_s
         else VR_MARCH(2, false);
     }
 #undef VR_MARCH
+}
+void vrk_march_build(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int trilinear,
+                     uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc, const VrSegLists& sl,
+                     int pairs) {
+    cudaMemsetAsync(sl.counts, 0, 8 * sizeof(unsigned long long), st);
+    VR_COUNT(1);
+    dim3 grid((tile.w + 15) / 16, (tile.h + 7) / 8);
+    if (trilinear) k_march<2, true, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc, sl, pairs);
+    else k_march<2, false, true><<<grid, 128, 0, st>>>(g, u, tan_scale, tile, counts, offsets, samples, wc, sl, pairs);
 }
 void vrk_march_bound(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, uint32_t* bound) {
     VR_COUNT(1);

@@ -106,6 +106,11 @@ struct VrSegLists {
 };
 // builds seg_first / seg_pix / the leftover part of list from the per-pixel sample counts and offsets (nsamples < 2^32)
 // pairs != 0: pairs of segments go to the 16-sample table (point-type lists); 0: every segment to the 8-sample table
+// single-pass march (mode 2 of vrk_march) that also writes the segment tables (= vrk_march + vrk_build_segments in one
+// launch); the tables must have been sized for this march's sample count beforehand
+void vrk_march_build(cudaStream_t st, const VrGridDev& g, const vr_ubo& u, float tan_scale, vr_tile tile, int trilinear,
+                     uint32_t* counts, const unsigned long long* offsets, VrSample* samples, VrWorkCounters* wc, const VrSegLists& sl,
+                     int pairs);
 // floats of VrSegLists::part16 (len 16) / part8 (len 8) on the current device
 uint64_t vrk_seg_part_floats(int len);
 void vrk_build_segments(cudaStream_t st, const uint32_t* counts, const unsigned long long* offsets, uint64_t npix, const VrSegLists& sl,
