@@ -561,8 +561,8 @@ def main():
         except Exception as e:  # noqa: BLE001
             traffic_note = f"unavailable: {type(e).__name__}"
         point_kernels = {0: "k_eval<point,8>", 1: "k_eval_point2<8>", 2: "k_eval_point3<8,3,2>", 3: "k_eval_point3<6,4,2>",
-                         8: "k_eval_seg<2,point,16> (+ k_eval_seg<2,point,8> on odd segments, k_eval_point3<8,3,2,list> on leftovers and near-light segments)"}
-        kernel_name = point_kernels[args.eval_variant] if algo in ("point", "ray") else {0: "k_eval<sphere,8>", 8: "k_eval_seg<2,sphere,8> (+ k_eval_sphere2<8,list> on leftovers and near-light segments)"}.get(args.eval_variant, "k_eval_sphere2<8>")
+                         8: "k_eval_seg<256,2,point,16,full> (+ its slice-unit instance on the last wave, k_eval_seg<256,2,point,8,*> on odd segments, k_eval_point3<8,3,2,list> on leftovers and near-light segments)"}
+        kernel_name = point_kernels[args.eval_variant] if algo in ("point", "ray") else {0: "k_eval<sphere,8>", 8: "k_eval_seg<256,2,sphere,8,full> (+ its slice-unit instance on the last wave, k_eval_sphere2<8,list> on leftovers and near-light segments)"}.get(args.eval_variant, "k_eval_sphere2<8>")
         # MUFU.RCP per evaluation: the exact kernels need one (plus a rsqrt for sphere lists); the ray-segment kernel shares
         # one reciprocal between two lights
         mufu_per_eval = (0.5 if args.eval_variant == 8 else 1.0) if algo in ("point", "ray") else (1.5 if args.eval_variant == 8 else 2.0)

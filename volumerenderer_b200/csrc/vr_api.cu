@@ -444,7 +444,7 @@ int finalize_counters(vr_ctx* c) {
 extern "C" {
 
 // bump the kernel revision (kN) whenever an evaluation kernel changes: profiles/eval_traffic.json entries are stamped with it
-const char* vr_version(void) { return "libvr 0.2-k1 (sm_100a)"; }
+const char* vr_version(void) { return "libvr 0.2-k2 (sm_100a)"; }
 
 const char* vr_last_error(const vr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
