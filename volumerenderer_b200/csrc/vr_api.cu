@@ -441,10 +441,24 @@ int finalize_counters(vr_ctx* c) {
 
 }  // namespace
 
+#ifdef VR_CHECKED
+void vrk_check_selftest(cudaStream_t st);
+#endif
 extern "C" {
 
 // bump the kernel revision (kN) whenever an evaluation kernel changes: profiles/eval_traffic.json entries are stamped with it
+#ifdef VR_CHECKED
+const char* vr_version(void) { return "libvr 0.2-k2 (sm_100a) VR_CHECKED"; }
+// diagnostic build only (not in include/vr.h): violates a check on purpose; the next vr_sync must report mask 0x80000000
+int vr_checked_selftest(vr_ctx* c) {
+    if (!c) return VR_E_ARG;
+    cudaSetDevice(c->device);
+    vrk_check_selftest(c->stream);
+    return VR_OK;
+}
+#else
 const char* vr_version(void) { return "libvr 0.2-k2 (sm_100a)"; }
+#endif
 
 const char* vr_last_error(const vr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
 
@@ -910,6 +924,10 @@ static void fill_seg_lists(vr_ctx* c, uint64_t nreal, VrSegLists* out) {
     sl.part16 = c->seg_part16.p, sl.part8 = c->seg_part8.p;
     sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
     sl.list_capacity = (uint32_t)nreal;
+    sl.cap16 = (uint32_t)(nreal / 16 + 1), sl.cap8 = (uint32_t)(nreal / 8 + 1), sl.cap_flags = (uint32_t)(nreal / 8 + 2);
+    sl.sched_words = (uint32_t)per;
+    sl.part16_floats = c->seg_part16.cap, sl.part8_floats = c->seg_part8.cap;
+    sl.nslots = c->samples.cap;
 }
 
 // everything vr_dispatch_compute_color rejects that does not depend on the tile: checked before anything is enqueued
@@ -1300,6 +1318,8 @@ int vr_sync(vr_ctx* c) {
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     int rc = finalize_counters(c);
     if (rc != VR_OK) return rc;
+    if (const unsigned int mask = vrk_check_flags())  // (always 0 in the product build)
+        return fail(c, VR_E_STATE, "VR_CHECKED: device bounds check failed, mask 0x%x (bits: VR_CHK_* in vr_kernels.cu)", mask);
     return check_stream(c);
 }
 

@@ -23,6 +23,25 @@
 
 #include "vr_kernels.cuh"
 
+// ---- bounds checks of the diagnostic build (-DVR_CHECKED). compute-sanitizer cannot be run on this pool, so the indices the
+// segment path computes (tables built with atomics, index lists, scratch of the slice units, slots of the sample buffer)
+// are checked by the kernels themselves; a violated check sets a bit that vr_sync reports. Compiled out otherwise.
+enum {
+    VR_CHK_SEG16_TABLE = 0, VR_CHK_SEG8_TABLE, VR_CHK_LIST, VR_CHK_FLAGS, VR_CHK_SLOTS, VR_CHK_SCHED, VR_CHK_PART, VR_CHK_LIGHTS,
+    VR_CHK_MARCH_SLOT
+};
+#ifdef VR_CHECKED
+__device__ unsigned int g_vr_check = 0;
+#define VR_CHECK(cond, bit)                                  \
+    do {                                                     \
+        if (!(cond)) atomicOr(&g_vr_check, 1u << (bit));     \
+    } while (0)
+#else
+#define VR_CHECK(cond, bit) \
+    do {                    \
+    } while (0)
+#endif
+
 namespace {
 
 // =====================================================================================================
@@ -334,6 +353,11 @@ __device__ __forceinline__ void seg_build_warp(const uint32_t c, const uint32_t 
 #pragma unroll
     for (int i = 0; i < 4; i++) base[i] = __shfl_sync(0xffffffffu, base[i], 31) + (v[i] - mine[i]);
     const uint32_t fb = (uint32_t)base[0];  // the pixel's segments are numbered fb .. fb + q - 1 for the near-light flags
+    VR_CHECK(base[1] + q16 <= sl.cap16, VR_CHK_SEG16_TABLE);
+    VR_CHECK(base[2] + q8 <= sl.cap8, VR_CHK_SEG8_TABLE);
+    VR_CHECK(base[3] + r <= sl.list_capacity, VR_CHK_LIST);
+    VR_CHECK((uint64_t)fb + q <= sl.cap_flags, VR_CHK_FLAGS);
+    VR_CHECK((uint64_t)off + c <= sl.nslots, VR_CHK_SLOTS);
     if (has_pixel) sl.seg_base[p] = fb;
     for (uint32_t i = 0; i < q16; i++) {
         sl.seg16_first[base[1] + i] = off + 16u * i;
@@ -403,6 +427,9 @@ __global__ void __launch_bounds__(128) k_march(VrGridDev g, vr_ubo u, float tan_
             }
         }
         if (COUNT) counts[pix] = n;
+#ifdef VR_CHECKED
+        if (MODE == 2 && FILL && pix + 1 < (uint64_t)tile.w * tile.h) VR_CHECK(n <= offsets[pix + 1] - offsets[pix], VR_CHK_MARCH_SLOT);
+#endif
     }
     if (BUILD) seg_build_warp(n, first_slot, (uint64_t)ly * tile.w + lx, active, sl, pairs, lane);
     if (COUNT && wc) {
@@ -961,6 +988,7 @@ __global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* _
                 if (k0 + q >= nseg) break;
                 const float s0 = (p0[q].x - cx) * dx + (p0[q].y - cy) * dy + (p0[q].z - cz) * dz;
                 const float s1 = (p1[q].x - cx) * dx + (p1[q].y - cy) * dy + (p1[q].z - cz) * dz;
+                VR_CHECK(sb + k0 + q < sl.cap_flags, VR_CHK_FLAGS);
                 if (b > s0 - rho && b < s1 + rho) sl.flags[sb + k0 + q] = 1;
                 beyond = s0 - rho >= b;
             }
@@ -979,6 +1007,7 @@ __global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl, uint32_t bl
     const uint64_t e = (uint64_t)(t16 ? blockIdx.x : blockIdx.x - blocks16) * 256 + threadIdx.x;
     if (e >= nseg) return;
     const uint32_t fi = (t16 ? sl.seg16_flag : sl.seg_flag)[e];
+    VR_CHECK(fi + (t16 ? 1u : 0u) < sl.cap_flags, VR_CHK_FLAGS);
     if (!(*sl.flag_all != 0u || sl.flags[fi] != 0 || (t16 && sl.flags[fi + 1] != 0))) return;
     const uint32_t first = (t16 ? sl.seg16_first : sl.seg_first)[e];
     const uint32_t len = t16 ? 16u : 8u;
@@ -1084,6 +1113,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
         return;
     }
     uint32_t* __restrict__ done = sched + 1 + chunk;
+    VR_CHECK(1 + chunk < sl.sched_words, VR_CHK_SCHED);
     const uint64_t seg_base = (uint64_t)chunk * SEG_PER_CTA;
     const bool redo_all = *sl.flag_all != 0u;
     bool idle;
@@ -1108,6 +1138,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
     const uint32_t lo = sliced ? (q0 * slice_len < nlights ? q0 * slice_len : nlights) : 0u;
     const uint32_t nl = !sliced ? nlights : (nlights - lo < slice_len ? nlights - lo : slice_len);
     const float4* __restrict__ src = lights2 + 2 * (uint64_t)lo;
+    VR_CHECK(lo + nl <= nlights, VR_CHK_LIGHTS);
     const uint32_t ntiles = (nl + EVAL2_TILE - 1) / EVAL2_TILE;
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -1138,6 +1169,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
         }
         if (seg < nseg) {
             first[h] = tab_first[seg];
+            VR_CHECK((uint64_t)first[h] + LEN <= sl.nslots, VR_CHK_SLOTS);
             const uint32_t pix = tab_pix[seg];
             const VrCamRay r = vr_camera_ray(g, u, tan_scale, tile.x0 + pix % tile.w, tile.y0 + pix / tile.w);
             // world direction of the ray: the linear part of the index->world map applied to the index-space direction
@@ -1263,6 +1295,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_eval_seg(VrGridDev g, vr_ubo 
         // finishes last adds the chunk's SEG_SPLIT partial sums in slice order
         float* __restrict__ pc = (LEN == 16 ? sl.part16 : sl.part8) + (uint64_t)(chunk - nfull) * (SEG_SPLIT * LEN * SEG_PER_CTA);
         float* __restrict__ pq = pc + q0 * (LEN * SEG_PER_CTA);
+        VR_CHECK((uint64_t)(chunk - nfull + 1) * (SEG_SPLIT * LEN * SEG_PER_CTA) <= (LEN == 16 ? sl.part16_floats : sl.part8_floats), VR_CHK_PART);
 #pragma unroll
         for (int h = 0; h < 2; h++) {
             if (first[h] == 0xffffffffu || skip[h]) continue;
@@ -1764,6 +1797,20 @@ __global__ void __launch_bounds__(256) k_ubench(float* sink, int iters) {
 
 }  // namespace
 
+#ifdef VR_CHECKED
+__global__ void k_check_selftest() { VR_CHECK(threadIdx.x > 1000u, 31); }  // always violated: proves the reporting path
+void vrk_check_selftest(cudaStream_t st) { k_check_selftest<<<1, 32, 0, st>>>(); }
+#endif
+unsigned int vrk_check_flags() {
+#ifdef VR_CHECKED
+    unsigned int h = 0, zero = 0;
+    cudaMemcpyFromSymbol(&h, g_vr_check, sizeof(h));
+    if (h) cudaMemcpyToSymbol(g_vr_check, &zero, sizeof(zero));
+    return h;
+#else
+    return 0;
+#endif
+}
 static unsigned long long g_launches = 0;
 unsigned long long vrk_launch_count() { return g_launches; }
 #define VR_COUNT(n) (g_launches += (n))

@@ -97,6 +97,10 @@ struct VrSegLists {
     unsigned long long* counts;   // [0] seg entries, [1] leftovers, [2] list length (leftovers + near-light), [3] flag_all,
                                   // [4] seg16 entries, [5] segments (flag numbers), [6] unused, [7] list2 length
     uint32_t list_capacity;       // of list and of list2
+    // capacities, read by the bounds checks of the VR_CHECKED build only: entries of the seg16 / seg tables, flags,
+    // words per sched array, floats of part16 / part8, slots of the sample buffer
+    uint32_t cap16, cap8, cap_flags, sched_words;
+    uint64_t part16_floats, part8_floats, nslots;
     // work distribution of k_eval_seg: [1 + c] = slice units of chunk c that have delivered their partial sums; one array per
     // table (the kernels of both run concurrently), allocated back to back (sched_bytes from sched16), zeroed per pass
     uint32_t *sched16, *sched8;
@@ -151,5 +155,9 @@ void vrk_clear_image(cudaStream_t st, float4* accum, uchar4* rgba8, float* frame
 void vrk_row_sums(cudaStream_t st, const uint32_t* counts, uint32_t w, uint32_t h, unsigned long long* rows);
 // ---- microbenchmarks (roofline denominators); returns the op count launched
 double vrk_ubench(cudaStream_t st, int kind, float* sink, int iters);
+// VR_CHECKED build (-DVR_CHECKED; tools/gpu_checked.sh): every index the segment path computes is checked against its
+// buffer's capacity on the device; a failed check sets a bit (see VR_CHK_* in vr_kernels.cu). Returns the mask and clears it;
+// always 0 in the product build, which carries no checks.
+unsigned int vrk_check_flags();
 // number of kernels launched by the vrk_* functions in this process (monotonic)
 unsigned long long vrk_launch_count();
