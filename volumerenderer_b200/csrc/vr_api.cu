@@ -922,7 +922,7 @@ static void fill_seg_lists(vr_ctx* c, uint64_t nreal, VrSegLists* out) {
     const uint64_t per = nreal / 8 / 128 + 4;  // chunks of at least 128 entries (two per thread), at most nreal / 8 entries
     sl.sched16 = c->seg_sched.p, sl.sched8 = c->seg_sched.p + per, sl.sched_bytes = 2 * per * sizeof(uint32_t);
     sl.part16 = c->seg_part16.p, sl.part8 = c->seg_part8.p;
-    sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = reinterpret_cast<uint32_t*>(c->seg_counts + 3);
+    sl.seg_base = c->seg_base.p, sl.flags = c->seg_flags.p, sl.flag_all = c->seg_sched.p;  // word 0 of the work counters: zeroed with them at the start of every pass
     sl.list_capacity = (uint32_t)nreal;
     sl.cap16 = (uint32_t)(nreal / 16 + 1), sl.cap8 = (uint32_t)(nreal / 8 + 1), sl.cap_flags = (uint32_t)(nreal / 8 + 2);
     sl.sched_words = (uint32_t)per;

@@ -935,7 +935,14 @@ __global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* _
                                                             vr_ubo u, float tan_scale, vr_tile tile, const uint32_t* __restrict__ counts,
                                                             const unsigned long long* __restrict__ offsets,
                                                             const VrSample* __restrict__ samples, VrSegLists sl, float rho) {
+    // start of an evaluation pass (block 0, before k_list_flagged appends): the exact kernel's list restarts from the
+    // leftovers, nothing handed over yet (the give-up flag was zeroed with the work counters)
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+        sl.counts[2] = sl.counts[1];
+        sl.counts[7] = 0;
+    }
     const uint64_t nl = *nlights_dev;
+    // gridDim.y blocks share a light's pixel box (a light inside the frustum can cover thousands of pixels of the tile)
     for (uint64_t li = blockIdx.x; li < nl; li += gridDim.x) {
     const VrEvalLight L = lights[li];
     const float cx = u.cameraPos[0], cy = u.cameraPos[1], cz = u.cameraPos[2];
@@ -960,7 +967,7 @@ __global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* _
     const int32_t bw = px1 - px0 + 1, bh = py1 - py0 + 1;
     if (bw <= 0 || bh <= 0) continue;
     const float rho2 = rho * rho;
-    for (int64_t i = threadIdx.x; i < (int64_t)bw * bh; i += blockDim.x) {
+    for (int64_t i = threadIdx.x + (int64_t)blockIdx.y * blockDim.x; i < (int64_t)bw * bh; i += (int64_t)blockDim.x * gridDim.y) {
         const int32_t px = px0 + (int32_t)(i % bw), py = py0 + (int32_t)(i / bw);
         const float x = ((2.0f * ((float)px + 0.5f)) / W - 1.0f) * aspect * tan_scale;
         const float y = (1.0f - (2.0f * ((float)py + 0.5f)) / H) * tan_scale;
@@ -1015,11 +1022,11 @@ __global__ void __launch_bounds__(256) k_list_flagged(VrSegLists sl, uint32_t bl
     for (uint32_t k = 0; k < len; k++)
         if (slot + k < sl.list_capacity) sl.list[slot + k] = first + k;
 }
-// start of an evaluation pass: the exact kernel's list restarts from the leftovers, nothing handed over yet, no give-up flag
+// start of an evaluation pass without full segments (else k_flag_near_segments does this): the exact kernel's list restarts
+// from the leftovers, nothing handed over yet
 __global__ void k_seg_begin(VrSegLists sl) {
     sl.counts[2] = sl.counts[1];
     sl.counts[7] = 0;
-    *sl.flag_all = 0u;
 }
 
 __device__ __forceinline__ float2 neg2(const float2 v) { return make_float2(-v.x, -v.y); }  // folds into the operand modifier
@@ -2047,21 +2054,20 @@ void vrk_eval_point_seg(cudaStream_t st, cudaStream_t side, cudaStream_t side2, 
     const bool small = nsamples < 40ull * 1000 * 1000;  // short lists: 4 samples per thread, twice the CTAs at half the duration
     const uint64_t cap16 = sphere ? 0 : seg_cap / 2;
     const uint64_t cap8 = sphere ? seg_cap : (seg_cap < npix ? seg_cap : npix);  // point-type: at most one odd segment per pixel
-    cudaMemsetAsync(sl.sched16, 0, sl.sched_bytes, st);  // ticket counters and per-chunk slice counters of both tables
-    VR_COUNT(1);
-    k_seg_begin<<<1, 1, 0, st>>>(sl);
+    cudaMemsetAsync(sl.sched16, 0, sl.sched_bytes, st);  // the give-up flag (word 0) and the per-chunk slice counters of both tables
     if (seg_cap) {
         cudaMemsetAsync(sl.flags, 0, seg_cap, st);
         // sphere-type lists: distances are measured from the sphere's surface, the flags from its centre
         const float margin = 1.02f * (rho + (sphere ? radius : 0.0f)) + 1.0e-3f;
-        if (nlights_capacity) {
-            VR_COUNT(1);
-            k_flag_near_segments<<<(unsigned)(nlights_capacity < 65536u ? nlights_capacity : 65536u), 128, 0, st>>>(
-                lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples, sl, margin);
-        }
+        VR_COUNT(1);  // (also restarts the exact kernel's list: launched even for an empty light list)
+        const unsigned nb = (unsigned)(nlights_capacity < 65536u ? (nlights_capacity ? nlights_capacity : 1) : 65536u);
+        k_flag_near_segments<<<dim3(nb, 4), 128, 0, st>>>(lights, nlights_dev, u, tan_scale, tile, counts, offsets, samples, sl, margin);
         VR_COUNT(1);
         const unsigned b16 = (unsigned)((cap16 + 255) / 256), b8 = (unsigned)((cap8 + 255) / 256);
         k_list_flagged<<<b16 + b8, 256, 0, st>>>(sl, b16);
+    } else {
+        VR_COUNT(1);
+        k_seg_begin<<<1, 1, 0, st>>>(sl);
     }
     if (side != st) {
         cudaEventRecord(ev_fork, st);

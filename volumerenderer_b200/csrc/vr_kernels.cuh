@@ -101,7 +101,8 @@ struct VrSegLists {
     // words per sched array, floats of part16 / part8, slots of the sample buffer
     uint32_t cap16, cap8, cap_flags, sched_words;
     uint64_t part16_floats, part8_floats, nslots;
-    // work distribution of k_eval_seg: [1 + c] = slice units of chunk c that have delivered their partial sums; one array per
+    // work distribution of k_eval_seg: [1 + c] = slice units of chunk c that have delivered their partial sums (sched16[0] is
+    // flag_all); one array per
     // table (the kernels of both run concurrently), allocated back to back (sched_bytes from sched16), zeroed per pass
     uint32_t *sched16, *sched8;
     // scratch of the slice units: [chunk of the last wave][slice][sample of the entry][entry]: vrk_seg_part_floats(len) floats
