@@ -265,6 +265,7 @@ def main():
                     help="N>1: none = every rank keeps the accumulator of its band (default); peer/nccl/auto = all-gather of the "
                          "bands' frame colours every frame (whole image on every GPU)")
     ap.add_argument("--balance-rounds", type=int, default=6, help="N>1: rounds of measured feedback for the band split")
+    ap.add_argument("--polish-moves", type=int, default=8, help="N>1: single-row moves tried after the feedback rounds")
     ap.add_argument("--eval-variant", type=int, default=8, choices=[0, 1, 2, 3, 8],
                     help="evaluation kernel for point/ray lists: 8 = ray-segment kernel (default), 2 = exact packed kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
@@ -300,7 +301,9 @@ def main():
     r = vr.VolumeRenderer(local_rank)
     r.set_eval_variant(args.eval_variant)
     if world > 1:
-        shared = torch.cuda.Stream()
+        # one priority step above the default: libvr's side streams (slice units, odd segments, exact list) have the lowest
+        # priority and must only take the SM slots this stream's kernels leave free (as with the context's own stream)
+        shared = torch.cuda.Stream(priority=-1)
         torch.cuda.set_stream(shared)
         r.set_stream(shared.cuda_stream)  # one stream for the kernels and the NCCL band exchange
     r.set_grid(grid)
@@ -333,25 +336,38 @@ def main():
         fc_t = tiles.frame_color_as_tensor(r)
         # measured feedback (untimed): each rank reports the device time of its band, the row costs are rescaled; the
         # per-band time is a staircase in CTA waves, so the split need not improve monotonically: the best one is kept
-        best = (float("inf"), bands)
-        for rnd in range(args.balance_rounds + 1):
+        def measure(frames=3):
             r.reset_accumulation()
             r.draw_frame(algo, tile)            # the first frame of a new split sizes buffers: not measured
             r.sync()
             r.timings_sum(reset=True)
-            for _ in range(3):
+            for _ in range(frames):
                 r.draw_frame(algo, tile)
             ts, nf = r.timings_sum(reset=True)
             mine = torch.tensor([ts["total_ms"] / max(1, nf)], dtype=torch.float64, device="cuda")
             allms = [torch.zeros_like(mine) for _ in range(world)]
             dist.all_gather(allms, mine)
-            ms = [float(x) for x in allms]
+            return [float(x) for x in allms]
+
+        best = (float("inf"), bands, None)
+        for rnd in range(args.balance_rounds + 1):
+            ms = measure()
             if max(ms) < best[0]:
-                best = (max(ms), bands)
+                best = (max(ms), bands, ms)
             if rnd == args.balance_rounds:
                 break
             cost = tiles.refine_row_costs(cost, bands, ms)
             set_bands(tiles.balanced_row_bands(cost, world))
+        # polish: single-row moves away from the slowest rank, kept while the measured maximum goes down
+        for _ in range(args.polish_moves):
+            cand = tiles.polish_move(best[1], best[2])
+            if cand is None:
+                break
+            set_bands(cand)
+            ms = measure(5)
+            if max(ms) >= best[0]:
+                break
+            best = (max(ms), bands, ms)
         set_bands(best[1])
         r.reset_accumulation()
 

@@ -110,3 +110,18 @@ def test_refine_row_costs_converges():
     rank_ms = np.array([true[y0:y0 + h].sum() for y0, h in bands])
     assert rank_ms.max() / rank_ms.mean() < 1.08
     assert sum(h for _, h in bands) == H
+
+
+def test_polish_move_takes_one_row_from_the_slowest_band():
+    from volumerenderer_b200 import tiles
+    bands = [(0, 10), (10, 5), (15, 5), (20, 12)]
+    # slowest in the middle: the row goes to the faster neighbour, on the right side of the boundary
+    assert tiles.polish_move(bands, [1.0, 1.1, 1.3, 1.2]) == [(0, 10), (10, 6), (16, 4), (20, 12)]
+    assert tiles.polish_move(bands, [1.0, 1.2, 1.3, 1.1]) == [(0, 10), (10, 5), (15, 4), (19, 13)]
+    # slowest at an end: only one neighbour
+    assert tiles.polish_move(bands, [1.5, 1.1, 1.3, 1.2]) == [(0, 9), (9, 6), (15, 5), (20, 12)]
+    assert tiles.polish_move(bands, [1.0, 1.1, 1.3, 1.6]) == [(0, 10), (10, 5), (15, 6), (21, 11)]
+    for out in (tiles.polish_move(bands, [1.0, 1.1, 1.3, 1.6]), tiles.polish_move(bands, [1.5, 1.1, 1.3, 1.2])):
+        assert sum(h for _, h in out) == 32 and all(out[i][0] + out[i][1] == out[i + 1][0] for i in range(3))
+    assert tiles.polish_move([(0, 1), (1, 9)], [2.0, 1.0]) is None       # a one-row band cannot give a row away
+    assert tiles.polish_move([(0, 10)], [1.0]) is None

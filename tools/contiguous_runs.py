@@ -1,4 +1,4 @@
-"""Offline statistic for DESIGN.md section 9 (CPU only, oracle lookups): which share of a frame's camera samples lies in aligned chunks of 32 / 16
+"""Offline statistic for DESIGN.md section 10 (CPU only, oracle lookups): which share of a frame's camera samples lies in aligned chunks of 32 / 16
 consecutive samples that are also consecutive march steps (no zero-density gap inside)? C2 geometry, every 16th x 9th pixel."""
 import sys, math
 sys.path.insert(0, __import__('os').path.dirname(__import__('os').path.dirname(__import__('os').path.abspath(__file__))))

@@ -17,12 +17,12 @@ import sys,json
 d=json.loads(sys.stdin.read()); print('$WL', d['n_gpus'], round(d['ms_per_step'],4), '%.4g'%d['value'], 'e2e', round(d['e2e']['ms_per_step'],4), d.get('multi_gpu_image_equals_single_gpu'))"; done
 done
 H=volumerenderer_b200/vr_headless
-C2ARGS="--grid cloud:256 --algo point --size 1920x1080 --set maxLights=1000 --lightgen 32 --quiet"
+C2ARGS="--grid cloud:256 --algo point --size 1920x1080 --set maxLights=1000 --lightgen 32"
 for N in 1 8; do
   G="--gpus $N"; [ $N = 1 ] && G="--devices 0"
   $H $C2ARGS $G --frames 4 --bench 20 > $OUT/${TAG}_headless_C2_n$N.json 2> $OUT/${TAG}_headless_C2_n$N.err; echo "headless C2 n$N rc=$?"; cut -c1-400 $OUT/${TAG}_headless_C2_n$N.json
 done
-C4ARGS="--grid cloud:512 --algo beam --size 1920x1080 --set maxLights=256 --lightgen 8 --quiet --frames 64"
+C4ARGS="--grid cloud:512 --algo beam --size 1920x1080 --set maxLights=256 --lightgen 8 --frames 64"
 for N in 1 8; do
   G="--gpus $N"; [ $N = 1 ] && G="--devices 0"
   $H $C4ARGS $G --progressive 1 --pfm $OUT/${TAG}_c4a_n$N.pfm > $OUT/${TAG}_headless_C4A_progressive_n$N.json 2> $OUT/${TAG}_headless_C4A_n$N.err; echo "headless C4-A progressive n$N rc=$?"; cut -c1-400 $OUT/${TAG}_headless_C4A_progressive_n$N.json

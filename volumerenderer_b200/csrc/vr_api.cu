@@ -208,7 +208,9 @@ struct vr_ctx {
     bool march_cache = false;
     MarchKey march_key;
     uint64_t cached_samples = 0;  // length of the sample buffer's address range (= sample count when the buffer is compact)
-    uint64_t cached_real = 0;     // number of samples in it
+    uint64_t cached_real = 0;     // number of samples in it, or an upper bound of it (real_exact): sizes tables and launches
+    bool real_exact = false;      // cached_real is the count itself
+    bool cached_S_valid = false;  // cached_S holds the counters of the cached march
     bool march_single = true;     // vr_set_march_single_pass
     uint32_t frame_step = 1;      // vr_set_frame_step: frameCount advances by this much per vr_render_frame
     uint32_t frame_first = 0;     // ... after the next frame, which is number frame_first (0: no override)
@@ -422,6 +424,7 @@ int finalize_counters(vr_ctx* c) {
     if (c->counters_have_march) {
         c->last_counters.S_ref = c->cached_S[0] = h.S_ref;
         c->last_counters.S_eff = c->cached_S[1] = h.S_eff;
+        c->cached_S_valid = true;
     }
     if (h.overflow) return fail(c, VR_E_STATE, "internal: the expanded light list overflowed its buffer");
     if (c->last_algo == VR_ALGO_PATH) {
@@ -435,7 +438,7 @@ int finalize_counters(vr_ctx* c) {
     if (lc > c->light_capacity) lc = c->light_capacity;
     c->last_counters.light_count = lc;
     c->last_counters.eval_lights = h.neval;
-    c->last_counters.E = c->nreal_used * h.neval;
+    c->last_counters.E = c->cached_S[1] * h.neval;  // (cached_S: the counters of the march these samples came from)
     return VR_OK;
 }
 
@@ -894,6 +897,10 @@ static int check_light_gen_args(vr_ctx* c, vr_algo algo, uint32_t gx, uint32_t g
     return VR_OK;
 }
 
+// largest slot total of a single-pass march for which tables and launches are sized by the slot total instead of a
+// blocking read of the sample count (tables: about 10 B per slot)
+constexpr uint64_t kBoundSizingMaxSlots = 64ull << 20;
+
 // buffers of the ray-segment evaluation for a march with `nreal` samples (tables, index lists, flags, work distribution)
 static int reserve_seg_tables(vr_ctx* c, uint64_t nreal, uint64_t npix) {
     const uint64_t n8 = nreal / 8 + 1;
@@ -1031,6 +1038,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     const bool reuse = c->march_cache && same_key;
     uint64_t nsamples = c->cached_samples, nreal = c->cached_real;
     int built_by_march = -1;  // 0 / 1: the march wrote the segment tables itself (without / with 16-sample pairs)
+    if (!same_key) c->cached_S_valid = false;  // (set again when this march's counters arrive)
     if (!reuse) {
         VR_CUDA(c, c->px_counts.reserve(npix));
         VR_CUDA(c, c->px_offsets.reserve(npix));
@@ -1068,27 +1076,46 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         }
         if (key.gaps) nsamples = c->bound_extent;
         if (key.gaps) {
-            // same rays as before: the slots (offsets, total) are still valid, the march alone runs again
-            // Same rays over the same grid as the previous gather (the steady state of a progressive render: the reference
-            // marches every frame): the sample count, hence the size of every segment table, is known, and the march writes
-            // the tables itself -- one launch less between the march and the evaluation.
+            // The slots (offsets, total) are valid: the march alone runs. What sizes the segment tables and the evaluation
+            // launches is an upper bound `nreal` of the sample count:
+            //  * same rays over the same grid as the previous gather (the steady state of a progressive render; the
+            //    reference marches every frame): the previous frame's count, exact;
+            //  * new grid or new rays, small frame (an image band of a multi-GPU run, an animated volume): the slot
+            //    total itself -- every slot could hold a sample -- so the frame needs NO host round trip and frames
+            //    pipeline; launches carry some empty CTAs, which at this size costs less than the bubble of a blocking read;
+            //  * new grid or new rays, large frame: one blocking read of the count after the march (the empty CTAs of a
+            //    4x oversized launch would cost about 0.25 ms on a 1080p frame).
+            // In the first two cases the table sizes are known before the march, and the march writes the tables itself
+            // (one launch and its gap less between the march and the evaluation).
             const int pairs = (algo == VR_ALGO_SPHERE || algo == VR_ALGO_BEAM) ? 0 : 1;
-            if (same_key && c->cached_real > 0 && c->cached_real < 0xffffffffull && c->seg_reserved_for == c->cached_real &&
-                c->seg_reserved_npix >= npix) {
+            bool read_count = false;
+            if (same_key) {
+                if (!c->real_exact && c->cached_S_valid && c->cached_S[1] <= nreal) nreal = c->cached_S[1], c->real_exact = true;
+            } else if (c->bound_extent <= kBoundSizingMaxSlots) {
+                nreal = c->bound_extent, c->real_exact = false;
+            } else {
+                read_count = true;
+            }
+            if (!read_count && nreal > 0 && nreal < 0xffffffffull) {
+                if (c->seg_reserved_for < nreal || c->seg_reserved_npix < npix) {
+                    rc = reserve_seg_tables(c, nreal, npix);
+                    if (rc != VR_OK) return rc;
+                }
                 VrSegLists sl;
-                fill_seg_lists(c, c->cached_real, &sl);
+                fill_seg_lists(c, nreal, &sl);
                 vrk_march_build(st, c->gdev, c->ubo, tan_scale, tile, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p,
                                 c->wc, sl, pairs);
                 built_by_march = pairs;
             } else {
                 vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 2, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, c->wc);
             }
-            if (!same_key) {  // the number of samples sizes the segment tables and the evaluation launches: second blocking read
+            if (read_count) {
                 VR_CUDA(c, cudaMemcpyAsync(c->totals_host + 2, &c->wc->S_eff, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
                 VR_CUDA(c, cudaStreamSynchronize(st));
                 rc = check_stream(c);
                 if (rc != VR_OK) return rc;
                 nreal = c->totals_host[2];
+                c->real_exact = true;
             }
         } else {
             vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 0, (int)c->phys.trilinear, c->px_counts.p, nullptr, nullptr, c->wc);
@@ -1105,6 +1132,7 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
                 VR_CUDA(c, c->samples.reserve(nsamples + 1));
             }
             nreal = nsamples;
+            c->real_exact = true;
             vrk_march(st, c->gdev, c->ubo, tan_scale, tile, 1, (int)c->phys.trilinear, c->px_counts.p, c->px_offsets.p, c->samples.p, nullptr);
         }
         c->cached_samples = nsamples;
@@ -1693,7 +1721,11 @@ int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {
     if (!c) return VR_E_ARG;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    const uint64_t n = c->cached_real;
+    {
+        const int frc = finalize_counters(c);  // the sample count may only be known as the frame's S_eff counter
+        if (frc != VR_OK) return frc;
+    }
+    const uint64_t n = (c->real_exact || !c->cached_S_valid) ? c->cached_real : c->cached_S[1];
     if (count) *count = n;
     const uint64_t m = n < capacity ? n : capacity;
     if (m && !out) return fail(c, VR_E_ARG, "vr_read_samples: NULL output buffer");
@@ -1729,9 +1761,11 @@ int vr_read_samples(vr_ctx* c, float* out, uint64_t capacity, uint64_t* count) {
 
 int vr_get_march_info(vr_ctx* c, uint64_t out[3]) {
     if (!c || !out) return VR_E_ARG;
+    const int rc = finalize_counters(c);  // (waits for the last frame's scalars: the sample count may only be known from them)
+    if (rc != VR_OK) return rc;
     out[0] = (c->march_key.valid && c->march_key.gaps) ? 1u : 0u;
     out[1] = c->cached_samples;
-    out[2] = c->cached_real;
+    out[2] = (c->real_exact || !c->cached_S_valid) ? c->cached_real : c->cached_S[1];
     return VR_OK;
 }
 

@@ -537,25 +537,26 @@ int vr_group_balance(vr_group* g, vr_algo algo, uint32_t rounds) {
     }
     g->band = split_rows(cost, g->n, g->width);
     std::vector<vr_tile> best = g->band;
+    std::vector<double> best_per(g->n, 0.0);
     double best_ms = 1e300;
-    const int frames = 3;
-    for (uint32_t round = 0; round <= rounds; round++) {
-        rc = vr_group_reset_accumulation(g);
-        if (rc != VR_OK) return rc;
-        std::vector<double> ms(g->n, 0.0);
-        for (int f = 0; f < frames + 1 && rc == VR_OK; f++) {
-            if (f == 1) {  // the first frame of a new split re-sizes buffers: not measured
-                rc = on_all(g, [=](uint32_t i) {
+    // device time per GPU of `frames` frames of the current split (after one unmeasured frame, which re-sizes buffers)
+    auto measure = [&](int frames, std::vector<double>& ms) -> int {
+        int r0 = vr_group_reset_accumulation(g);
+        if (r0 != VR_OK) return r0;
+        ms.assign(g->n, 0.0);
+        for (int f = 0; f < frames + 1 && r0 == VR_OK; f++) {
+            if (f == 1) {
+                r0 = on_all(g, [=](uint32_t i) {
                     int r = vr_sync(g->ctx[i]);
                     if (r == VR_OK) r = vr_get_timings_sum(g->ctx[i], nullptr, nullptr, 1);
                     return r;
                 });
-                if (rc != VR_OK) break;
+                if (r0 != VR_OK) break;
             }
-            rc = vr_group_render_frame(g, algo);
+            r0 = vr_group_render_frame(g, algo);
         }
-        if (rc != VR_OK) return rc;
-        rc = on_all(g, [&](uint32_t i) {
+        if (r0 != VR_OK) return r0;
+        return on_all(g, [&](uint32_t i) {
             vr_timings s{};
             uint64_t nf = 0;
             int r = vr_sync(g->ctx[i]);
@@ -563,12 +564,36 @@ int vr_group_balance(vr_group* g, vr_algo algo, uint32_t rounds) {
             ms[i] = nf ? (double)s.total_ms / (double)nf : 0.0;
             return r;
         });
+    };
+    std::vector<double> ms;
+    for (uint32_t round = 0; round <= rounds; round++) {
+        rc = measure(3, ms);
         if (rc != VR_OK) return rc;
         const double worst = *std::max_element(ms.begin(), ms.end());
-        if (worst < best_ms) best_ms = worst, best = g->band;
+        if (worst < best_ms) best_ms = worst, best = g->band, best_per = ms;
         if (round == rounds) break;
         refine_costs(cost, g->band, ms);
         g->band = split_rows(cost, g->n, g->width);
+    }
+    // polish (same rule as tiles.polish_move): the slowest band gives one boundary row to the faster of its neighbours,
+    // kept while the measured maximum goes down
+    for (int move = 0; move < 8 && rounds > 0; move++) {
+        const uint32_t w = (uint32_t)(std::max_element(best_per.begin(), best_per.end()) - best_per.begin());
+        if (best[w].h <= 1) break;
+        uint32_t t = w;
+        if (w > 0) t = w - 1;
+        if (w + 1 < g->n && (t == w || best_per[w + 1] < best_per[t])) t = w + 1;
+        if (t == w) break;
+        std::vector<vr_tile> cand = best;
+        cand[w].h -= 1, cand[t].h += 1;
+        if (t < w) cand[w].y0 += 1;
+        else cand[t].y0 -= 1;
+        g->band = cand;
+        rc = measure(5, ms);
+        if (rc != VR_OK) return rc;
+        const double worst = *std::max_element(ms.begin(), ms.end());
+        if (worst >= best_ms) break;
+        best_ms = worst, best = cand, best_per = ms;
     }
     g->band = best;
     rc = vr_group_reset_accumulation(g);

@@ -135,6 +135,30 @@ def refine_row_costs(row_cost, bands, rank_ms):
     return cost
 
 
+def polish_move(bands, rank_ms):
+    """One local move after the feedback rounds: the slowest band gives one boundary row to the faster of its two
+    neighbours. Row costs differ by two orders of magnitude between the image's empty top and its centre, so where the
+    model's residual is a fraction of a band's time a single measured row move is finer than another rescaling of the
+    model. Returns the new bands, or None when the slowest band cannot give a row away."""
+    ms = [float(x) for x in rank_ms]
+    n = len(bands)
+    if n < 2 or len(ms) != n:
+        return None
+    w = max(range(n), key=lambda i: ms[i])
+    if bands[w][1] <= 1:
+        return None
+    nb = [i for i in (w - 1, w + 1) if 0 <= i < n]
+    t = min(nb, key=lambda i: ms[i])
+    out = [list(b) for b in bands]
+    out[w][1] -= 1
+    out[t][1] += 1
+    if t < w:          # the upper neighbour takes the slowest band's first row
+        out[w][0] += 1
+    else:              # the lower neighbour takes its last row
+        out[t][0] -= 1
+    return [tuple(b) for b in out]
+
+
 class PeerFrameColor:
     """Fused tile all-gather over NVLink peer memory (the "compute + collective in one kernel" form).
 
@@ -227,10 +251,10 @@ def accum_as_tensor(renderer):
 
 class ReplicatedGrid:
     """A new volume every frame on N GPUs with ONE host->device transfer per node: rank `src` uploads the NanoVDB bytes
-    into a device staging buffer (its own stream, two buffers, so the upload of frame k+1 runs under frame k), one NCCL
-    broadcast replicates them over NVLink, and every rank installs them with vr_set_grid_device in stream order. Nothing
-    here blocks the host. The renderer must run on torch's current stream (renderer.set_stream), which is also the
-    stream the broadcast is ordered on."""
+    into a device staging buffer and one NCCL broadcast replicates them over NVLink -- both on a side stream, with two
+    staging buffers, so the upload and the broadcast of frame k+1 run underneath frame k's kernels and the per-frame
+    rendezvous of the ranks is off the render stream --, then every rank installs them with vr_set_grid_device in stream
+    order. Nothing here blocks the host. The renderer must run on torch's current stream (renderer.set_stream)."""
 
     def __init__(self, renderer, nbytes, src=0, group=None):
         import torch
@@ -253,15 +277,15 @@ class ReplicatedGrid:
         main = torch.cuda.current_stream()
         world = dist.get_world_size(self.group) if dist.is_initialized() else 1
         rank = dist.get_rank(self.group) if dist.is_initialized() else 0
-        if rank == self.src:
-            if self.consumed[i] is not None:
-                self.upload.wait_event(self.consumed[i])  # the broadcast of two frames ago has read this buffer
-            with torch.cuda.stream(self.upload):
+        if self.consumed[i] is not None:
+            self.upload.wait_event(self.consumed[i])  # the frame of two calls ago has installed this buffer's contents
+        with torch.cuda.stream(self.upload):
+            if rank == self.src:
                 self.staging[i].copy_(pinned_grid, non_blocking=True)
-                self.uploaded[i].record(self.upload)
-            main.wait_event(self.uploaded[i])
-        if world > 1:
-            dist.broadcast(self.staging[i], src=self.src, group=self.group)
+            if world > 1:
+                dist.broadcast(self.staging[i], src=self.src, group=self.group)  # ordered on the side stream
+            self.uploaded[i].record(self.upload)
+        main.wait_event(self.uploaded[i])
         self.r.set_grid_device(self.staging[i].data_ptr(), self.nbytes, header)
         ev = torch.cuda.Event()
         ev.record(main)
