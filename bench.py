@@ -498,6 +498,7 @@ def main():
     r.read_wait()
     barrier()
     e2e_ceff = 0
+    r.timings_sum(reset=True)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
@@ -506,6 +507,8 @@ def main():
     r.read_wait()                                   # the last frame's image has arrived
     barrier()
     e2e_s = time.perf_counter() - t0
+    e2e_tsum, e2e_tframes = r.timings_sum(reset=True)   # this rank's per-pass device times of the end-to-end frames
+    e2e_passes = {k: round(v / max(1, e2e_tframes), 4) for k, v in e2e_tsum.items()}
     te = torch.tensor([e2e_s, float(e2e_ceff)], dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = te.clone()
@@ -618,7 +621,9 @@ def main():
             "e2e": {"value": e2e_value, "unit": "contributions/s", "ms_per_step": e2e_s * 1e3 / args.steps,
                     "h2d_bytes_per_step": int(grid.nbytes) + 96 * world, "d2h_bytes_per_step": int(W * H * 16),
                     "d2h": "every rank copies the rows it rendered into one shared, page-locked host image" if world > 1 else "rank 0",
-                    "nvlink_broadcast_bytes_per_step": int(grid.nbytes) * (world - 1) if world > 1 else 0},
+                    "nvlink_broadcast_bytes_per_step": int(grid.nbytes) * (world - 1) if world > 1 else 0,
+                    "volume_replication": replicated.mode if replicated is not None else "single GPU: vr_set_grid from pinned host memory",
+                    "passes_ms_per_step_rank0": e2e_passes},
             "gpu_launches": int(launches),
             "roofline": roofline,
             "cpu_baseline": cpu_baseline,

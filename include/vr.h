@@ -108,6 +108,14 @@ int vr_set_grid(vr_ctx* ctx, const void* nanovdb_bytes, uint64_t size);
  * the root node's fixed part (1024 bytes cover every grid the NanoVDB writers lay out, where the root follows the tree);
  * it supplies what the host must know: map, bounding box, root offset, tile count. No host synchronisation. */
 int vr_set_grid_device(vr_ctx* ctx, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size);
+/* As vr_set_grid_device, for bytes that are produced in the order of ANOTHER stream of the caller (`ready_stream`, a
+ * cudaStream_t: e.g. the side stream on which a replication of the volume runs): the copy into the grid buffer that no
+ * enqueued frame reads runs on the library's upload stream behind that stream's current tail, i.e. next to the frames in
+ * flight instead of behind them; the render stream and the light-generation stream wait for it. With it the next
+ * frame's light generation (which needs the new grid, but not the previous frame) runs underneath the previous frame's
+ * evaluation. `device_bytes` may be overwritten once work enqueued on the context's stream after this call has started. */
+int vr_set_grid_device_from_stream(vr_ctx* ctx, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size,
+                                   void* ready_stream);
 
 /* ---- binding 0: rgba8 storage image sized to the swapchain extent, recreated on resize (src/main.cpp:338-378, :950).
  * Allocates the rgba8 image plus a float4 accumulator and resets the progressive state (frameCount = 0, :937). */

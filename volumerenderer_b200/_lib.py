@@ -62,7 +62,7 @@ EXPORTS = [
     "vr_reset_accumulation", "vr_sync", "vr_read_lights", "vr_read_light_counter", "vr_read_image_rgba8",
     "vr_read_accum_f32", "vr_read_frame_color_f32", "vr_write_accum_f32", "vr_write_image_rgba8", "vr_get_counters",
     "vr_get_timings", "vr_get_timings_sum", "vr_get_device_buffers", "vr_row_sample_counts", "vr_accumulate_frame_color", "vr_set_frame_color_peers", "vr_set_march_cache", "vr_set_march_single_pass", "vr_set_light_prefetch", "vr_read_accum_f32_async", "vr_read_wait", "vr_set_options", "vr_get_options", "vr_trilinear_values", "vr_progressive_radius", "vr_set_eval_variant", "vr_set_eval_near_distance", "vr_get_eval_segment_counts", "vr_get_eval_redo_count", "vr_read_samples", "vr_lookup_values", "vr_cpu_test_render",
-    "vr_set_stream", "vr_set_grid_device", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
+    "vr_set_stream", "vr_set_grid_device", "vr_set_grid_device_from_stream", "vr_get_launch_count", "vr_timer_start", "vr_timer_stop", "vr_ubench", "vr_grid_build_cloud", "vr_grid_build_fog_sphere", "vr_grid_build_dense", "vr_grid_free", "vr_version",
     "vr_grid_load_nvdb", "vr_grid_save_nvdb", "vr_image_write_ppm", "vr_image_write_pfm", "vr_snapshot_save", "vr_snapshot_load",
     "vr_io_last_error",
     "vr_read_accum_f32_tile_async", "vr_set_eval_side_stream", "vr_set_frame_step", "vr_set_accumulate_mode", "vr_finish_sum", "vr_get_march_info", "vr_read_image_rgba8_tile",
@@ -144,6 +144,7 @@ def load():
     L.vr_lookup_values.argtypes = [P, P, U64, P]
     L.vr_set_stream.argtypes = [P, P]
     L.vr_set_grid_device.argtypes = [P, P, C.c_uint64, P, C.c_uint64]
+    L.vr_set_grid_device_from_stream.argtypes = [P, P, C.c_uint64, P, C.c_uint64, P]
     L.vr_get_launch_count.argtypes = [P, C.POINTER(U64)]
     L.vr_timer_start.argtypes = [P]
     L.vr_timer_stop.argtypes = [P, C.POINTER(C.c_float)]

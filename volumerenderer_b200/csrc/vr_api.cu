@@ -144,6 +144,11 @@ struct vr_ctx {
     // light generation of vr_render_frame overlaps the camera march on this stream
     cudaStream_t aux_stream = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_lg_done = nullptr;
+    // ev_frame_end[p]: end of the last vr_render_frame that used light pair parity p (its last reader of lights/counter);
+    // ev_grid_ready: the bytes of the installed grid have arrived (vr_set_grid_device*: a copy that may still be in flight)
+    cudaEvent_t ev_frame_end[2] = {nullptr, nullptr}, ev_grid_ready = nullptr;
+    bool frame_end_recorded[2] = {false, false}, grid_ready_pending = false;
+    uint32_t pair_parity = 0;  // toggles with every swap of (lights, counter) <-> (lights_alt, counter_alt)
     cudaStream_t upload_stream = nullptr;  // vr_set_grid: host->device copy of a new grid next to the frames in flight
     uint8_t* grid_alt = nullptr;           // the second grid buffer (vr_set_grid alternates)
     uint64_t grid_alt_cap = 0;
@@ -532,6 +537,9 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_join2, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_lg_done, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_frame_end[0], cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_frame_end[1], cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_grid_ready, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaMalloc(&c->eval_redo, sizeof(unsigned long long)));
     VR_CREATE_CUDA(cudaMalloc(&c->seg_counts, 8 * sizeof(unsigned long long)));  // layout: VrSegLists::counts
     VR_CREATE_CUDA(cudaMemsetAsync(c->seg_counts, 0, 8 * sizeof(unsigned long long), c->stream));
@@ -601,6 +609,9 @@ int vr_destroy(vr_ctx* c) {
     if (c->seg_stream) cudaStreamDestroy(c->seg_stream);
     if (c->seg_stream2) cudaStreamDestroy(c->seg_stream2);
     if (c->ev_lg_done) cudaEventDestroy(c->ev_lg_done);
+    if (c->ev_frame_end[0]) cudaEventDestroy(c->ev_frame_end[0]);
+    if (c->ev_frame_end[1]) cudaEventDestroy(c->ev_frame_end[1]);
+    if (c->ev_grid_ready) cudaEventDestroy(c->ev_grid_ready);
     if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     if (c->eval_redo) cudaFree(c->eval_redo);
     if (c->seg_counts) cudaFree(c->seg_counts);
@@ -740,10 +751,12 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
     c->have_grid = false;
     grid_alt_install(c, b, size, root, tiles);
+    c->grid_ready_pending = false;  // (the host waited for the copy)
     return VR_OK;
 }
 
-int vr_set_grid_device(vr_ctx* c, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size) {
+static int set_grid_device_impl(vr_ctx* c, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size,
+                                bool have_ready_stream, cudaStream_t ready_stream) {
     if (!c) return VR_E_ARG;
     if (!device_bytes || !header) return fail(c, VR_E_ARG, "vr_set_grid_device: NULL buffer");
     uint64_t root = 0;
@@ -755,13 +768,33 @@ int vr_set_grid_device(vr_ctx* c, const void* device_bytes, uint64_t size, const
     c->spec.valid = false;
     rc = grid_alt_prepare(c, size);
     if (rc != VR_OK) return rc;
-    // device -> device (or peer -> device over NVLink) in stream order: behind whatever the caller enqueued on this
-    // context's stream to produce device_bytes (e.g. a broadcast), in front of the next frame; no host synchronisation
-    VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, device_bytes, size, cudaMemcpyDefault, c->stream));
+    if (have_ready_stream) {
+        // the bytes are produced in the order of the caller's `ready_stream` (e.g. the side stream of a replication): the
+        // copy into the free grid buffer runs on the upload stream behind that, NEXT TO the frames in flight; whoever
+        // reads the new grid (the render stream, the light-generation stream) waits for ev_grid_ready
+        VR_CUDA(c, cudaEventRecord(c->ev_grid_ready, ready_stream));
+        VR_CUDA(c, cudaStreamWaitEvent(c->upload_stream, c->ev_grid_ready, 0));
+        VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, device_bytes, size, cudaMemcpyDefault, c->upload_stream));
+        VR_CUDA(c, cudaEventRecord(c->ev_grid_ready, c->upload_stream));
+        VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_grid_ready, 0));
+    } else {
+        // device -> device (or peer -> device over NVLink) in stream order: behind whatever the caller enqueued on this
+        // context's stream to produce device_bytes (e.g. a broadcast), in front of the next frame; no host synchronisation
+        VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, device_bytes, size, cudaMemcpyDefault, c->stream));
+        VR_CUDA(c, cudaEventRecord(c->ev_grid_ready, c->stream));
+    }
     VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
     c->have_grid = false;
     grid_alt_install(c, (const uint8_t*)header, size, root, tiles);
+    c->grid_ready_pending = true;
     return VR_OK;
+}
+int vr_set_grid_device(vr_ctx* c, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size) {
+    return set_grid_device_impl(c, device_bytes, size, header, header_size, false, nullptr);
+}
+int vr_set_grid_device_from_stream(vr_ctx* c, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size,
+                                   void* ready_stream) {
+    return set_grid_device_impl(c, device_bytes, size, header, header_size, true, (cudaStream_t)ready_stream);
 }
 
 int vr_resize(vr_ctx* c, uint32_t w, uint32_t h) {
@@ -824,9 +857,13 @@ int vr_set_max_lights_capacity(vr_ctx* c, uint32_t n) {
     VR_CUDA(c, c->lights_alt.reserve(n));
     VR_CUDA(c, cudaMemsetAsync(c->lights.p, 0, c->lights.cap * sizeof(vr_ray_light), c->stream));
     VR_CUDA(c, cudaMemsetAsync(c->lights_alt.p, 0, c->lights_alt.cap * sizeof(vr_ray_light), c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));  // light generation runs on another stream and must not race these memsets
     c->light_capacity = n;
     if (c->ubo.maxLights > n) c->ubo.maxLights = n;
-    return vr_reset_lights(c);
+    int rc = vr_reset_lights(c);
+    if (rc != VR_OK) return rc;
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VR_OK;
 }
 
 int vr_reset_lights(vr_ctx* c) {
@@ -1014,6 +1051,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
         vrk_path(st, c->gdev, c->ubo, tan_scale, tile, c->fc_out, c->accum, c->rgba8, c->wc, nmax ? c->path_tab.p : nullptr, nmax, c->accumulate_mode);
         cudaEventRecord(t->ev[5], st);
         cudaEventRecord(t->ev[6], st);
+    cudaEventRecord(c->ev_frame_end[c->pair_parity], st);  // the last reader of this (lights, counter) pair so far
+    c->frame_end_recorded[c->pair_parity] = true;
         t->pending = true, t->open = false;
         rc = enqueue_scalars(c, st, true);
         if (rc != VR_OK) return rc;
@@ -1248,6 +1287,8 @@ int vr_dispatch_compute_color(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_nu
     range.next("vr:resolve");
     vrk_resolve(st, c->ubo, tile, c->px_counts.p, c->px_offsets.p, c->contrib.p, c->counter, c->fc_out, c->accum, c->rgba8, c->accumulate_mode);
     cudaEventRecord(t->ev[6], st);
+    cudaEventRecord(c->ev_frame_end[c->pair_parity], st);  // the last reader of this (lights, counter) pair so far
+    c->frame_end_recorded[c->pair_parity] = true;
     t->pending = true, t->open = false;
     return check_stream(c);
 }
@@ -1296,10 +1337,22 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
         c->lights_bound = 0, c->gen_pos_state = 0;  // the other pair's counter was reset before its generation
         note_generation(c, c->spec.ubo, algo);
         c->lg_in_flight = true;  // the gather joins on ev_lg_done
+        c->pair_parity ^= 1u;
     } else {
-        if (c->spec.valid) VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_lg_done, 0));  // a stale prefetch must drain first
-        rc = vr_reset_lights(c);  // :722-728
-        if (rc != VR_OK) return rc;
+        // Light generation (:811-814) on the auxiliary stream into the OTHER (lights, counter) pair, which the frame before
+        // the previous one used last: it depends on that frame's end and on the grid's bytes, not on the previous frame, so
+        // when the host runs ahead (an animated volume: new grid, then the next frame, while the GPU still evaluates the
+        // previous one) it runs underneath the previous frame's evaluation kernel instead of in front of this frame's
+        // gather. The counter reset (:722-728) is the memset of that pair's counter. The gather joins on ev_lg_done: the
+        // reference's compute->compute barrier (:817-829).
+        const uint32_t np = c->pair_parity ^ 1u;
+        if (c->frame_end_recorded[np]) VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_frame_end[np], 0));
+        if (c->grid_ready_pending) VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_grid_ready, 0));
+        std::swap(c->lights, c->lights_alt);
+        std::swap(c->counter, c->counter_alt);
+        c->pair_parity = np;
+        c->lights_bound = 0, c->gen_pos_state = 0;
+        VR_CUDA(c, cudaMemsetAsync(c->counter, 0, sizeof(VrLightCounter), c->aux_stream));
     }
     c->spec.valid = false;
     if (c->ubo.frameCount == 1) {  // :731
@@ -1307,11 +1360,6 @@ int vr_render_frame(vr_ctx* c, vr_algo algo, const vr_tile* tile_or_null) {
         if (rc != VR_OK) return rc;
     }
     if (!adopt) {
-        // light generation (:811-814) runs on the auxiliary stream, concurrently with the camera march of the gather
-        // (:832-837), which does not read the lights; the gather joins before it builds its light list. The
-        // reference's compute->compute barrier (:817-829) is that join.
-        VR_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
-        VR_CUDA(c, cudaStreamWaitEvent(c->aux_stream, c->ev_fork, 0));
         rc = enqueue_light_gen(c, c->aux_stream, t, c->ubo, algo, gr[0], gr[1], gr[2], variant, c->lights.p, c->counter);
         if (rc != VR_OK) return rc;
         note_generation(c, c->ubo, algo);

@@ -71,6 +71,13 @@ class VolumeRenderer:
         h = np.ascontiguousarray(np.frombuffer(header, np.uint8) if not isinstance(header, np.ndarray) else header)
         self._check(self._L.vr_set_grid_device(self._ctx, C.c_void_p(int(device_ptr)), int(nbytes), h.ctypes.data_as(C.c_void_p), h.nbytes))
 
+    def set_grid_device_from_stream(self, device_ptr, nbytes, header, ready_stream):
+        """vr_set_grid_device_from_stream: as set_grid_device, for bytes produced in the order of the caller's CUDA stream
+        `ready_stream` (int handle); the copy runs next to the frames in flight on libvr's upload stream."""
+        h = np.ascontiguousarray(np.frombuffer(header, np.uint8) if not isinstance(header, np.ndarray) else header)
+        self._check(self._L.vr_set_grid_device_from_stream(self._ctx, C.c_void_p(int(device_ptr)), int(nbytes),
+                                                           h.ctypes.data_as(C.c_void_p), h.nbytes, C.c_void_p(int(ready_stream))))
+
     def resize(self, width, height):
         """binding 0: storage image sized to the framebuffer; resets the progressive state (src/main.cpp:936-982)."""
         self._check(self._L.vr_resize(self._ctx, width, height))
