@@ -106,7 +106,11 @@ int vr_set_grid(vr_ctx* ctx, const void* nanovdb_bytes, uint64_t size);
  * the caller enqueued there to produce `device_bytes`, and `device_bytes` may be overwritten once later work on that
  * stream has started. `header` is a HOST copy of the first `header_size` bytes of the grid, at least up to the end of
  * the root node's fixed part (1024 bytes cover every grid the NanoVDB writers lay out, where the root follows the tree);
- * it supplies what the host must know: map, bounding box, root offset, tile count. No host synchronisation. */
+ * it supplies what the host must know: map, bounding box, root offset, tile count. No host synchronisation: the grid
+ * lives in two device buffers, the bytes go into the one the installed grid does not occupy, and the copy waits ON THE
+ * DEVICE for that buffer's last readers (the frames and light generations enqueued before the previous install), so a
+ * host that runs ahead may hand over the volume of frame k+1 while the GPU is still on frame k-1 (only a buffer that
+ * has to grow is reallocated behind a host wait). */
 int vr_set_grid_device(vr_ctx* ctx, const void* device_bytes, uint64_t size, const void* header, uint64_t header_size);
 /* As vr_set_grid_device, for bytes that are produced in the order of ANOTHER stream of the caller (`ready_stream`, a
  * cudaStream_t: e.g. the side stream on which a replication of the volume runs): the copy into the grid buffer that no

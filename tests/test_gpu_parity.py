@@ -524,6 +524,52 @@ def test_set_grid_device_equals_set_grid(vr, cloud):
 
 
 @pytest.mark.gpu
+def test_device_grid_installs_do_not_wait_on_the_host(vr, cloud):
+    """A host that runs ahead: a new volume before every frame through vr_set_grid_device / ReplicatedGrid
+    (vr_set_grid_device_from_stream), no host synchronisation anywhere in the sequence. The copy into the spare grid buffer
+    waits ON THE DEVICE for that buffer's last readers (the frame and the light generation of two grids ago), so the
+    accumulated image and the last light list must equal the ones of the same sequence driven through the blocking
+    vr_set_grid."""
+    import torch
+    from volumerenderer_b200 import tiles
+
+    grids = [cloud(64), cloud(64, seed=7), cloud(32)]
+    order = [0, 1, 2, 1, 0, 2, 0, 1, 1, 2]
+    r = vr.VolumeRenderer(0)
+    try:
+        r.resize(160, 96)
+        r.update_ubo(maxLights=96)
+        r.set_light_gen_groups(4)
+
+        def run(install):
+            for g in grids[:2] + grids[:2]:  # both grid buffers at their final capacity before the sequence starts
+                r.set_grid(g)
+            r.reset_accumulation()
+            for i in order:
+                install(i)
+                r.draw_frame("point")
+            r.sync()
+            return r.read_accum(), r.read_lights()[0].tobytes(), r.counters()["S_eff"]
+
+        want = run(lambda i: r.set_grid(grids[i]))
+        assert want[0].any() and len(want[1]) > 0
+        dev = [torch.from_numpy(g).cuda() for g in grids]
+        torch.cuda.synchronize()
+        got = run(lambda i: r.set_grid_device(dev[i].data_ptr(), grids[i].nbytes, grids[i][:4096]))
+        assert np.array_equal(want[0], got[0]) and want[1] == got[1] and want[2] == got[2]
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            r.set_stream(st.cuda_stream)
+            pinned = [torch.from_numpy(g).pin_memory() for g in grids]
+            rg = {g.nbytes: tiles.ReplicatedGrid(r, g.nbytes) for g in grids}
+            got2 = run(lambda i: rg[grids[i].nbytes].set_grid(pinned[i], grids[i][:4096]))
+        r.set_stream(None)
+        assert np.array_equal(want[0], got2[0]) and want[1] == got2[1] and want[2] == got2[2]
+    finally:
+        r.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("algo", ["point", "beam"])
 def test_single_pass_march_equals_two_pass(vr, cloud, algo):
     """The single-pass march (slots from the lookup-free step bound, sample buffer with gaps) and the two-pass march

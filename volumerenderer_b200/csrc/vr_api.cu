@@ -153,7 +153,9 @@ struct vr_ctx {
     uint8_t* grid_alt = nullptr;           // the second grid buffer (vr_set_grid alternates)
     uint64_t grid_alt_cap = 0;
     bool grid_alt_busy = false;
-    cudaEvent_t ev_grid_alt_free = nullptr;
+    // the buffer that is not the installed grid is free for the next grid once the work that was enqueued before the
+    // last install has passed: ev_grid_alt_free on the render stream, ev_grid_alt_free_aux on the light-generation stream
+    cudaEvent_t ev_grid_alt_free = nullptr, ev_grid_alt_free_aux = nullptr;
     cudaStream_t copy_stream = nullptr;  // asynchronous read-back (vr_read_accum_f32_async): copies overlap the next frame
     cudaEvent_t ev_copy_ready = nullptr, ev_copy_done = nullptr;
     DevBuf<float> accum_snapshot;
@@ -531,6 +533,7 @@ int vr_create(int cuda_device, vr_ctx** out) {
     VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     VR_CREATE_CUDA(cudaStreamCreateWithFlags(&c->upload_stream, cudaStreamNonBlocking));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_grid_alt_free, cudaEventDisableTiming));
+    VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_grid_alt_free_aux, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_ready, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_copy_done, cudaEventDisableTiming));
     VR_CREATE_CUDA(cudaEventCreateWithFlags(&c->ev_seg_fork, cudaEventDisableTiming));
@@ -599,6 +602,7 @@ int vr_destroy(vr_ctx* c) {
     }
     if (c->upload_stream) cudaStreamDestroy(c->upload_stream);
     if (c->ev_grid_alt_free) cudaEventDestroy(c->ev_grid_alt_free);
+    if (c->ev_grid_alt_free_aux) cudaEventDestroy(c->ev_grid_alt_free_aux);
     if (c->grid_alt) cudaFree(c->grid_alt);
     if (c->ev_copy_ready) cudaEventDestroy(c->ev_copy_ready);
     if (c->ev_copy_done) cudaEventDestroy(c->ev_copy_done);
@@ -684,9 +688,15 @@ static int parse_grid_header(vr_ctx* c, const uint8_t* b, uint64_t have, uint64_
 }
 
 // the buffer the next grid goes into: the one of the two that no enqueued work reads
-static int grid_alt_prepare(vr_ctx* c, uint64_t size) {
+// The buffer the next grid goes into. Its last readers are the frames and light generations enqueued before the previous
+// install; `copy_stream` != nullptr: the stream that will fill the buffer waits for them on the device and the host does
+// not wait (vr_set_grid_device*), nullptr: the host waits (vr_set_grid, which blocks for its own copy anyway).
+static int grid_alt_prepare(vr_ctx* c, uint64_t size, cudaStream_t copy_stream) {
     if (c->grid_alt && c->grid_alt_cap < size) {
-        if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));
+        if (c->grid_alt_busy) {
+            VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));
+            VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free_aux));
+        }
         cudaFree(c->grid_alt);
         c->grid_alt = nullptr;
         c->grid_alt_cap = 0;
@@ -696,7 +706,21 @@ static int grid_alt_prepare(vr_ctx* c, uint64_t size) {
         c->grid_alt_cap = size;
         c->grid_alt_busy = false;
     }
-    if (c->grid_alt_busy) VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));  // its last readers (two grids ago) are done
+    if (c->grid_alt_busy) {
+        if (copy_stream) {
+            VR_CUDA(c, cudaStreamWaitEvent(copy_stream, c->ev_grid_alt_free, 0));
+            VR_CUDA(c, cudaStreamWaitEvent(copy_stream, c->ev_grid_alt_free_aux, 0));
+        } else {
+            VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free));
+            VR_CUDA(c, cudaEventSynchronize(c->ev_grid_alt_free_aux));
+        }
+    }
+    return VR_OK;
+}
+// after an install: everything enqueued so far reads the buffer that has just become the spare one
+static int grid_alt_mark(vr_ctx* c) {
+    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free_aux, c->aux_stream));
     return VR_OK;
 }
 
@@ -738,17 +762,16 @@ int vr_set_grid(vr_ctx* c, const void* bytes, uint64_t size) {
     int rc = parse_grid_header(c, b, size, size, &root, &tiles);
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
-    c->spec.valid = false;
+    c->spec.valid = false;  // (a prefetched light generation may still read the current grid: grid_alt_mark covers it)
     // Two device buffers: the new grid goes into the one no enqueued work reads, on an upload stream, while the frames
     // already enqueued keep rendering from the other (kernels take the grid pointer by value at launch). The host waits
     // for the copy (the caller may reuse `bytes` on return); the GPU does not wait for anything.
-    rc = grid_alt_prepare(c, size);
+    rc = grid_alt_prepare(c, size, nullptr);
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, bytes, size, cudaMemcpyHostToDevice, c->upload_stream));
     VR_CUDA(c, cudaStreamSynchronize(c->upload_stream));
-    // everything enqueued so far reads the old buffer: it is free again once this event has passed
-    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    rc = grid_alt_mark(c);
+    if (rc != VR_OK) return rc;
     c->have_grid = false;
     grid_alt_install(c, b, size, root, tiles);
     c->grid_ready_pending = false;  // (the host waited for the copy)
@@ -764,9 +787,11 @@ static int set_grid_device_impl(vr_ctx* c, const void* device_bytes, uint64_t si
     int rc = parse_grid_header(c, (const uint8_t*)header, header_size < size ? header_size : size, size, &root, &tiles);
     if (rc != VR_OK) return rc;
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->aux_stream));  // a prefetched light generation may still read the current grid
     c->spec.valid = false;
-    rc = grid_alt_prepare(c, size);
+    // no host wait: the stream that copies waits for the spare buffer's last readers (frames and light generations that
+    // were enqueued before the previous install), so a host that runs ahead hands the next volume over while the GPU is
+    // still one or two frames behind
+    rc = grid_alt_prepare(c, size, have_ready_stream ? c->upload_stream : c->stream);
     if (rc != VR_OK) return rc;
     if (have_ready_stream) {
         // the bytes are produced in the order of the caller's `ready_stream` (e.g. the side stream of a replication): the
@@ -783,7 +808,8 @@ static int set_grid_device_impl(vr_ctx* c, const void* device_bytes, uint64_t si
         VR_CUDA(c, cudaMemcpyAsync(c->grid_alt, device_bytes, size, cudaMemcpyDefault, c->stream));
         VR_CUDA(c, cudaEventRecord(c->ev_grid_ready, c->stream));
     }
-    VR_CUDA(c, cudaEventRecord(c->ev_grid_alt_free, c->stream));
+    rc = grid_alt_mark(c);
+    if (rc != VR_OK) return rc;
     c->have_grid = false;
     grid_alt_install(c, (const uint8_t*)header, size, root, tiles);
     c->grid_ready_pending = true;
