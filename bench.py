@@ -576,7 +576,7 @@ def main():
         # measured DRAM traffic of one launch of the dominant kernel, from a committed ncu --set full capture. The entry is
         # stamped with the library version it was captured on: after a kernel change the stamp no longer matches the built
         # library and the figure is dropped (null + reason) instead of silently going stale.
-        traffic, traffic_note = None, None
+        traffic, traffic_note, ncu_pipes = None, None, None
         try:
             with open(os.path.join(ROOT, "profiles", "eval_traffic.json")) as f:
                 tj = json.load(f)
@@ -584,6 +584,7 @@ def main():
             built = vr.load().vr_version().decode()
             if isinstance(ent, dict) and ent.get("version") == built:
                 traffic, traffic_note = ent["traffic"], f"{ent.get('source', '')} (captured on {ent.get('commit', '?')}, {built})"
+                ncu_pipes = ent.get("ncu")   # pipe utilisation of the same capture: what actually bounds the kernel
             elif ent is not None:
                 cap = ent.get("version") if isinstance(ent, dict) else "an unstamped round-1 build"
                 traffic_note = f"dropped: captured on {cap}, the built library is {built}"
@@ -602,7 +603,7 @@ def main():
             "flop_per_eval": flop, "evals_per_s": evals / eval_s if eval_s > 0 else 0.0,
             "mufu_rcp_peak_per_s": peak_rcp * 1e12, "mufu_per_eval": mufu_per_eval,
             "mufu_frac": (evals / eval_s) * mufu_per_eval / (peak_rcp * 1e12) if peak_rcp and eval_s > 0 else None,
-            "traffic": traffic, "traffic_source": traffic_note,
+            "traffic": traffic, "traffic_source": traffic_note, "ncu_pipes": ncu_pipes,
             "hbm": {"bound": "hbm", "achieved": alg_bytes / (eval_s / args.steps) / 1e9 if eval_s > 0 else 0.0, "peak": hbm_peak,
                     "unit": "GB/s", "frac": (alg_bytes / (eval_s / args.steps) / 1e9) / hbm_peak if eval_s > 0 else None,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (of fallback)",
