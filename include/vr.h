@@ -284,7 +284,10 @@ double vr_progressive_radius(double previous_radius, double alpha);
 /* evaluation-kernel variant for point-type light lists (point, ray): 0 = scalar FP32 kernel, 1 = packed FP32x2 kernel
  * with the d2 < 1e-4 guard in the loop, 2 = packed kernel that runs the loop unguarded and repeats a thread block with the
  * guard when one of its threads saw d2 < 1e-4 (same results as 1), 3 = as 2 with 6 samples per thread, 8 = below. All follow
- * shaders/common_functions.h:186-194; results differ by rounding only. */
+ * shaders/common_functions.h:186-194; results differ by rounding only. The product runs 8 (the default: ray-segment
+ * kernel, with variant 2's kernel for near-light segments and leftover samples); 2 is the exact reference for 8's error
+ * bound; 0, 1 and 3 are kept as CROSS-CHECKS only (0 keeps every rounding of the shader, the tests compare the others
+ * against it) and are not tuned any further. */
 int vr_set_eval_variant(vr_ctx* ctx, int variant);
 /* variant 8 = ray-segment kernel: the samples of one pixel lie on the camera ray, so eight consecutive samples share the
  * per-light geometry (distance of the light from the ray, foot point) and two lights share one reciprocal. The line
