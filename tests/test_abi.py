@@ -93,3 +93,16 @@ def test_nvtx_build_flag_compiles(tmp_path):
                            "-DVR_NVTX", "-c", src, "-o", obj])
     syms = subprocess.run(["nm", obj], capture_output=True, text=True).stdout
     assert "nvtx" in syms.lower()
+
+
+def test_traffic_stamp_matches_the_built_library(vr):
+    """bench.py reports roofline.traffic only when profiles/eval_traffic.json was captured on the library version that is
+    built; a kernel change must come with a version bump and a new capture, so the committed stamp equals vr_version()."""
+    import json
+    import os
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    with open(os.path.join(root, "profiles", "eval_traffic.json")) as f:
+        ent = json.load(f)["C2"]
+    assert ent["version"] == vr.load().vr_version().decode()
+    assert ent["traffic"] > 1.0e9 and "ncu" in ent and 0.5 < ent["ncu"]["fma_pipe_busy"] < 1.0
