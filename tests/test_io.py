@@ -92,6 +92,46 @@ def test_nvdb_rejects_compressed_and_garbage(vr, cloud, tmp_path):
         vr.load_nvdb_grid(p)
 
 
+@pytest.mark.timeout(120)
+def test_nvdb_loader_survives_corrupt_headers(vr, cloud, tmp_path):
+    """Seeded fuzz of vr_grid_load_nvdb (file container and raw buffer): special 64-bit values (0, 2^32, 2^63, 2^64-1, ...) and
+    random words written over the headers, byte flips, truncation. Every case must return -- VR_E_BADGRID or a grid
+    that lies inside the file -- never hang, over-read or grow without bound (sizes near 2^64 used to wrap the bounds check)."""
+    grid = cloud(32)
+    p = str(tmp_path / "g.nvdb")
+    vr.save_nvdb_grid(p, grid)
+    file_bytes = open(p, "rb").read()
+    vr.save_nvdb_grid(p, grid, raw=True)
+    raw_bytes = open(p, "rb").read()
+    rng = np.random.default_rng(7)
+    specials = [0, 1, 31, 32, 2**31, 2**32 - 1, 2**32, 2**63, 2**64 - 1, 2**64 - 32, len(file_bytes), len(file_bytes) + 1]
+    loaded = rejected = 0
+    for it in range(600):
+        data = bytearray(file_bytes if it % 2 == 0 else raw_bytes)
+        mode = it % 5
+        if mode == 0:
+            struct.pack_into("<Q", data, int(rng.integers(0, 128)) * 8, specials[int(rng.integers(0, len(specials)))])
+        elif mode == 1:
+            for _ in range(int(rng.integers(1, 8))):
+                data[int(rng.integers(0, min(len(data), 1400)))] = int(rng.integers(0, 256))
+        elif mode == 2:
+            data = data[:int(rng.integers(0, len(data)))]
+        elif mode == 3:
+            struct.pack_into("<I", data, int(rng.integers(0, 256)) * 4, int(rng.integers(0, 2**32)))
+        else:
+            struct.pack_into("<Q", data, int(rng.integers(0, 90)) * 8, specials[int(rng.integers(0, len(specials)))])
+            data = data[:int(rng.integers(700, len(data)))]
+        open(p, "wb").write(bytes(data))
+        try:
+            g = vr.load_nvdb_grid(p)
+            assert g.nbytes <= len(data) and g.nbytes % 32 == 0, (it, g.nbytes, len(data))
+            loaded += 1
+        except vr.VrError as e:
+            assert e.code in (1, 3), (it, e.code, str(e))   # VR_E_BADGRID; VR_E_ARG for an unreadable file
+            rejected += 1
+    assert loaded > 50 and rejected > 50
+
+
 def test_ppm_and_pfm_writers(vr, tmp_path):
     rng = np.random.default_rng(5)
     img = rng.integers(0, 256, (7, 5, 4), dtype=np.uint8)
