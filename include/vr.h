@@ -139,6 +139,37 @@ int vr_reset_lights(vr_ctx* ctx);
 /* upload a light list (tests; broadcast in multi-GPU runs). count <= capacity. */
 int vr_write_lights(vr_ctx* ctx, const vr_ray_light* lights, uint32_t count);
 
+/* ---- light generation without any device-memory allocation. NO COUNTERPART IN THE REFERENCE (Vulkan gives the shader
+ * no scratch to manage; the need comes from how this library's light_gen pass is built). vr_dispatch_light_gen lets the
+ * context allocate its working buffers (candidate lights per photon, counts, scan) with cudaMalloc. Some hosts cannot
+ * accept that: one that gave the whole GPU to its own pool (a plug-in's cudaMalloc then fails or bypasses the pool's
+ * accounting), or one that calls mid-frame, where cudaMalloc/cudaFree may stall every stream of the device. This call
+ * needs no context and allocates nothing -- no cudaMalloc, no cudaFree, no allocating library routine: the working
+ * memory is one fixed array inside the library image (about 2.1 MB on every GPU that loads libvr, held until exit).
+ *   limit        at most VR_STATIC_MAX_PHOTONS photons per call (gx*4 * gy*4 * gz, work-groups of 4x4x1 as in
+ *                shaders/light_gen.comp:7); more is rejected with VR_E_CAPACITY and a message, nothing is enqueued
+ *   inputs       the volume in DEVICE memory (grid_device_bytes, 32-byte aligned, readable on cuda_device) plus a HOST copy
+ *                of its first bytes up to the end of the root node's fixed part (grid_header; 1024 bytes cover the NanoVDB
+ *                writers' layouts), exactly as for vr_set_grid_device; the UBO
+ *   outputs      lights_device: room for params->maxLights entries of 32 B, 16-byte aligned; counter_device: 16 bytes,
+ *                8-byte aligned: u32 lightCount, u32 contributionCounter, u64 scatter events before the maxLights cap.
+ *                The counter is zeroed first (the per-frame reset, src/main.cpp:722-728), so the result equals
+ *                vr_reset_lights + vr_dispatch_light_gen of a context with the same grid and UBO, byte for byte
+ *   ordering     everything is enqueued on cuda_stream (a cudaStream_t of cuda_device; NULL = the default stream) and the
+ *                call returns without waiting; it makes cuda_device the calling thread's current device
+ *   sharing      all calls on one GPU use the same working memory, which keeps the previous call's contents (the call
+ *                clears what has to start at zero). Calls that can overlap on the GPU -- different streams, other
+ *                threads -- race on it and produce garbage; keep them on one stream or order them with events
+ *   first call   the first call on each GPU looks up the array's device address and thereby loads this code onto that
+ *                GPU; issue it at start-up, before any stream capture begins
+ *   errors       vr_status as everywhere; the text goes to error_text (error_text_size bytes, may be NULL/0) because
+ *                there is no context to keep it. */
+#define VR_STATIC_MAX_PHOTONS 4096u
+int vr_light_gen_static(int cuda_device, void* cuda_stream, const void* grid_device_bytes, uint64_t grid_size,
+                        const void* grid_header, uint64_t grid_header_size, const vr_ubo* params, uint32_t gx, uint32_t gy,
+                        uint32_t gz, vr_lightgen_variant variant, vr_ray_light* lights_device, void* counter_device,
+                        char* error_text, uint64_t error_text_size);
+
 /* ---- image clear to (0,0,0,1) when frameCount == 1 (src/main.cpp:731-808) */
 int vr_clear_image(vr_ctx* ctx);
 

@@ -71,6 +71,7 @@ EXPORTS = [
     "vr_group_set_exchange", "vr_group_reset_accumulation", "vr_group_set_bands", "vr_group_get_bands", "vr_group_balance",
     "vr_group_render_frame", "vr_group_sync", "vr_group_read_accum_f32", "vr_group_read_accum_f32_async", "vr_group_read_wait",
     "vr_group_read_image_rgba8", "vr_group_render_progressive", "vr_group_time_frames",
+    "vr_light_gen_static",
 ]
 
 _lib = None
@@ -195,5 +196,6 @@ def load():
     L.vr_group_read_image_rgba8.argtypes = [P, P]
     L.vr_group_render_progressive.argtypes = [P, I, U32]
     L.vr_group_time_frames.argtypes = [P, I, U32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.vr_light_gen_static.argtypes = [I, P, P, U64, P, U64, C.POINTER(VrUbo), U32, U32, U32, I, P, P, C.c_char_p, U64]
     _lib = L
     return L
