@@ -2,7 +2,7 @@
 # The workload meant for compute-sanitizer (tools/sanitize_frames.py: smoke test, every algorithm whole and tiled with the
 # light prefetch, the exact variants, a 3-band group run with both exchange modes) on the VR_CHECKED build, in which the
 # kernels bounds-check every index of the segment path themselves, plus the GPU parity suite on that build.
-# compute-sanitizer itself is closed on this pool (profiles/r02_sanitize_*.log hold its refusal).
+# compute-sanitizer itself is closed on this pool; nothing in this repository starts it.
 # Build first, in the container: python -c "import __graft_entry__ as g; g.build_checked()"
 TAG=${1:-r02}
 OUT=gpurun_out

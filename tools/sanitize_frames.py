@@ -1,4 +1,4 @@
-"""Workload for compute-sanitizer (tools/gpu_sanitize.sh): __graft_entry__.smoke(), then one 160x96 frame sequence per
+"""Workload written for compute-sanitizer, run on the VR_CHECKED build by tools/gpu_checked.sh: __graft_entry__.smoke(), then one 160x96 frame sequence per
 algorithm on the 64^3 cloud (both streams of the evaluation pass, the light-generation prefetch, tiles), the exact
 evaluation variants, and a 3-band vr_group run with the peer-store exchange on one device. Results are checked against
 each other (tiled == whole), so a sanitizer-clean run is also a correct one."""
