@@ -436,7 +436,10 @@ int vr_group_read_wait(vr_group* g);
 int vr_group_read_image_rgba8(vr_group* g, uint8_t* out);
 /* sample-parallel progressive run (vr_set_frame_step / vr_set_accumulate_mode above): frames 1..frames go round-robin to
  * the GPUs, each renders WHOLE images into a float sum; the first GPU adds the others' sums in GPU order (peer reads over
- * NVLink), divides, and holds the result (float accumulator, rgba8 of the average, frameCount = frames). */
+ * NVLink), divides, and holds the result (float accumulator, rgba8 of the average, frameCount = frames). Until the next
+ * vr_group_reset_accumulation (or resize / balance) the vr_group_read_* calls return that image from the first GPU, and
+ * vr_group_render_frame / vr_group_time_frames return VR_E_STATE: the other GPUs hold partial sums and other frame numbers,
+ * tiled frames cannot continue from them. */
 int vr_group_render_progressive(vr_group* g, vr_algo algo, uint32_t frames);
 /* device time of `frames` tiled frames: CUDA events on every GPU's stream, maximum over the GPUs; per_gpu_ms may be NULL */
 int vr_group_time_frames(vr_group* g, vr_algo algo, uint32_t frames, float* ms_per_frame_max, float* per_gpu_ms);

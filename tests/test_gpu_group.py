@@ -94,6 +94,19 @@ def test_group_sample_parallel_progressive(vr, cloud):
         assert rel <= frames * 2.0 ** -22 and want_a[..., 0].max() > 0.01, (rel, rmse)
         assert np.array_equal(img[..., 0], np.rint(np.clip(got[..., 0], 0, 1) * 255).astype(np.uint8))
         assert g.ubo.frameCount == frames
+        # the result lives on the first GPU only (the others keep raw partial sums): the group's own read-backs return it
+        # whole, blocking and asynchronous, and tiled frames are refused until the accumulation is reset
+        assert np.array_equal(g.read_accum(), got)
+        assert np.array_equal(g.read_image_rgba8(), img)
+        got2 = np.full((H, W, 4), -1.0, np.float32)
+        assert L.vr_group_read_accum_f32_async(g._g, got2.ctypes.data_as(C.c_void_p)) == 0
+        assert L.vr_group_read_wait(g._g) == 0
+        assert np.array_equal(got2, got)
+        with pytest.raises(vr.VrError) as e:
+            g.draw_frame("beam")
+        assert e.value.code == 5 and "vr_group_reset_accumulation" in str(e.value)
+        with pytest.raises(vr.VrError):
+            g.time_frames("beam", 1)
         # the group is back in its default mode: a tiled frame sequence after the progressive run works as before
         g.reset_accumulation()
         g.draw_frame("beam")

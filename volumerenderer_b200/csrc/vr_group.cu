@@ -46,6 +46,7 @@ struct Worker {
     std::condition_variable cv;
     std::function<int()> job;
     bool has_job = false, done = true, quit = false;
+    bool threw = false;  // the last job ended in a C++ exception (out of host memory)
     int rc = 0;
     void loop() {
         for (;;) {
@@ -57,10 +58,17 @@ struct Worker {
                 j = std::move(job);
                 has_job = false;
             }
-            const int r = j();
+            int r = VR_OK;
+            bool t = false;
+            try {  // no exception leaves the thread (std::bad_alloc from a job's containers would end the process)
+                r = j();
+            } catch (...) {
+                r = VR_E_STATE, t = true;
+            }
             {
                 std::lock_guard<std::mutex> l(m);
                 rc = r;
+                threw = t;
                 done = true;
             }
             cv.notify_all();
@@ -116,6 +124,10 @@ struct vr_group {
     std::vector<cudaEvent_t> staged_read[2];   // per GPU: its copy out of staging[k] is done
     uint32_t staging_next = 0;
     bool have_grid = false;
+    // vr_group_render_progressive leaves the finished image (average, rgba8, frameCount) on GPU 0 only; the other GPUs
+    // hold raw partial sums and their own frame numbers. While set, the read-backs take the whole image from GPU 0 and
+    // tiled frames are refused (they would continue from mixed states) until vr_group_reset_accumulation.
+    bool progressive_result = false;
 };
 
 namespace {
@@ -141,6 +153,7 @@ int on_all(vr_group* g, const std::function<int(uint32_t)>& fn) {
         if (rc != VR_OK && first == VR_OK) first = rc, who = i;
     }
     if (first != VR_OK) {
+        if (g->worker[who]->threw) return gfail(g, first, "GPU %u (device %d): out of host memory (C++ exception in the worker)", who, g->dev[who]);
         const char* e = vr_last_error(g->ctx[who]);
         return gfail(g, first, "GPU %u (device %d): %s", who, g->dev[who], e && *e ? e : "failed");
     }
@@ -204,6 +217,12 @@ void refine_costs(std::vector<double>& cost, const std::vector<vr_tile>& bands, 
 int require_image(vr_group* g) {
     if (!g->width) return gfail(g, VR_E_STATE, "no image: call vr_group_resize first");
     return VR_OK;
+}
+
+// the rows GPU i returns in a read-back: its band, or, after a sample-parallel progressive run, everything from GPU 0
+vr_tile read_rows(const vr_group* g, uint32_t i) {
+    if (g->progressive_result) return i == 0 ? vr_tile{0, 0, g->width, g->height} : vr_tile{0, 0, 0, 0};
+    return g->n > 1 ? g->band[i] : vr_tile{0, 0, g->width, g->height};
 }
 
 // the rows GPU i did not render: at most one rectangle above and one below its band
@@ -412,23 +431,35 @@ int vr_group_set_grid(vr_group* g, const void* bytes, uint64_t size) {
 int vr_group_resize(vr_group* g, uint32_t w, uint32_t h) {
     if (!g) return VR_E_ARG;
     if (h < g->n) return gfail(g, VR_E_ARG, "%u rows cannot be split between %u GPUs", h, g->n);
-    int rc = on_all(g, [=](uint32_t i) { return vr_resize(g->ctx[i], w, h); });
-    if (rc != VR_OK) return rc;
+    // Not an image until everything below has succeeded: a failure on one GPU leaves contexts of different sizes behind,
+    // and require_image then refuses frames, balancing and read-backs until a resize goes through.
+    g->width = g->height = 0;
+    g->progressive_result = false;  // vr_resize clears every accumulator
+    int rc = on_all(g, [=](uint32_t i) { return vr_resize(g->ctx[i], w, h); });  // drains each GPU's streams first
+    if (rc != VR_OK)  // a context that refused may not have drained: nothing may still store into the buffers freed next
+        for (uint32_t i = 0; i < g->n; i++) {
+            cudaSetDevice(g->dev[i]);
+            cudaDeviceSynchronize();
+        }
     free_frame_colors(g);
-    g->width = w, g->height = h;
+    if (rc != VR_OK) return rc;
     const size_t bytes = (size_t)w * h * sizeof(float);
     for (int p = 0; p < 2; p++) {
         g->fc[p].assign(g->n, nullptr);
         for (uint32_t i = 0; i < g->n && g->n > 1; i++) {
             cudaSetDevice(g->dev[i]);
-            if (cudaMalloc(&g->fc[p][i], bytes) != cudaSuccess || cudaMemset(g->fc[p][i], 0, bytes) != cudaSuccess)
+            if (cudaMalloc(&g->fc[p][i], bytes) != cudaSuccess || cudaMemset(g->fc[p][i], 0, bytes) != cudaSuccess) {
+                cudaGetLastError();
+                free_frame_colors(g);
                 return gfail(g, VR_E_CUDA, "frame-colour buffers: out of device memory");
+            }
         }
     }
     // even split until vr_group_balance / vr_group_set_bands says otherwise
     std::vector<double> ones(h, 1.0);
     g->band = split_rows(ones, g->n, w);
     g->parity = 0;
+    g->width = w, g->height = h;
     return VR_OK;
 }
 
@@ -454,6 +485,7 @@ int vr_group_set_light_gen_groups(vr_group* g, uint32_t gx, uint32_t gy, uint32_
 
 int vr_group_reset_accumulation(vr_group* g) {
     if (!g) return VR_E_ARG;
+    g->progressive_result = false;
     return on_all(g, [=](uint32_t i) { return vr_reset_accumulation(g->ctx[i]); });
 }
 
@@ -481,6 +513,9 @@ int vr_group_render_frame(vr_group* g, vr_algo algo) {
     if (!g) return VR_E_ARG;
     int rc = require_image(g);
     if (rc != VR_OK) return rc;
+    if (g->progressive_result)
+        return gfail(g, VR_E_STATE, "the accumulators hold a sample-parallel progressive run (result on GPU 0, partial sums elsewhere): "
+                                    "call vr_group_reset_accumulation before tiled frames");
     const uint32_t parity = g->parity, epoch = ++g->epoch;
     g->parity ^= 1u;
     rc = on_all(g, [=](uint32_t i) { return frame_on(g, i, algo, parity, epoch); });
@@ -497,12 +532,27 @@ int vr_group_sync(vr_group* g) {
     if (!g) return VR_E_ARG;
     int rc = on_all(g, [=](uint32_t i) { return vr_sync(g->ctx[i]); });
     if (rc != VR_OK) return rc;
-    for (uint32_t i = 0; i < g->n && g->exchange == VR_EXCHANGE_ALLGATHER; i++) {  // a barrier wait that gave up (k_peer_barrier)
+    // A barrier wait that gave up (k_peer_barrier) left the epoch it was waiting for in its GPU's mark word. Every mark is
+    // read and cleared here (the streams are idle), so that a later sync reports later timeouts only; the frames since the
+    // timeout averaged rows that had not arrived: the caller resets the accumulation before it goes on.
+    int bad_gpu = -1;
+    uint32_t bad_epoch = 0;
+    for (uint32_t i = 0; i < g->n && g->exchange == VR_EXCHANGE_ALLGATHER; i++) {
+        if (!g->flags[i]) continue;
         uint32_t mark = 0;
         cudaSetDevice(g->dev[i]);
-        if (cudaMemcpy(&mark, g->flags[i] + VR_MAX_PEERS, sizeof(mark), cudaMemcpyDeviceToHost) != cudaSuccess || mark != 0)
-            return gfail(g, VR_E_CUDA, "GPU %u: the cross-GPU barrier of frame epoch %u timed out (a peer never arrived)", i, mark);
+        if (cudaMemcpy(&mark, g->flags[i] + VR_MAX_PEERS, sizeof(mark), cudaMemcpyDeviceToHost) != cudaSuccess)
+            return gfail(g, VR_E_CUDA, "GPU %u: cannot read the barrier state", i);
+        if (mark == 0) continue;
+        if (cudaMemset(g->flags[i] + VR_MAX_PEERS, 0, sizeof(mark)) != cudaSuccess)
+            return gfail(g, VR_E_CUDA, "GPU %u: cannot clear the barrier state", i);
+        if (bad_gpu < 0) bad_gpu = (int)i, bad_epoch = mark;
     }
+    if (bad_gpu >= 0)
+        return gfail(g, VR_E_CUDA,
+                     "GPU %d: the cross-GPU barrier of frame epoch %u timed out, a peer never arrived (the group is at epoch %u); the "
+                     "accumulated image is incomplete: call vr_group_reset_accumulation before rendering on",
+                     bad_gpu, bad_epoch, g->epoch);
     return VR_OK;
 }
 
@@ -514,6 +564,7 @@ int vr_group_balance(vr_group* g, vr_algo algo, uint32_t rounds) {
     int rc = require_image(g);
     if (rc != VR_OK) return rc;
     if (g->n == 1) return VR_OK;
+    g->progressive_result = false;  // balancing renders into the accumulators and resets them at the end
     vr_ctx* c0 = g->ctx[0];
     vr_ubo saved;
     vr_get_params(c0, &saved);
@@ -605,7 +656,7 @@ int vr_group_read_accum_f32(vr_group* g, float* out) {
     if (!g || !out) return VR_E_ARG;
     int rc = require_image(g);
     if (rc != VR_OK) return rc;
-    if (g->n == 1) return vr_read_accum_f32(g->ctx[0], out);
+    if (g->n == 1 || g->progressive_result) return vr_read_accum_f32(g->ctx[0], out);
     // after the exchange every GPU holds the whole accumulator; each returns the rows it rendered over its own PCIe link
     rc = on_all(g, [=](uint32_t i) {
         const vr_tile& b = g->band[i];
@@ -620,7 +671,8 @@ int vr_group_read_accum_f32_async(vr_group* g, float* out) {
     int rc = require_image(g);
     if (rc != VR_OK) return rc;
     return on_all(g, [=](uint32_t i) {
-        const vr_tile b = g->n > 1 ? g->band[i] : vr_tile{0, 0, g->width, g->height};
+        const vr_tile b = read_rows(g, i);
+        if (b.h == 0) return (int)VR_OK;
         return vr_read_accum_f32_tile_async(g->ctx[i], &b, out + (size_t)b.y0 * g->width * 4, (uint64_t)g->width * 16);
     });
 }
@@ -635,7 +687,8 @@ int vr_group_read_image_rgba8(vr_group* g, uint8_t* out) {
     int rc = require_image(g);
     if (rc != VR_OK) return rc;
     return on_all(g, [=](uint32_t i) {
-        const vr_tile b = g->n > 1 ? g->band[i] : vr_tile{0, 0, g->width, g->height};
+        const vr_tile b = read_rows(g, i);
+        if (b.h == 0) return (int)VR_OK;
         return vr_read_image_rgba8_tile(g->ctx[i], &b, out + (size_t)b.y0 * g->width * 4, (uint64_t)g->width * 4);
     });
 }
@@ -655,6 +708,7 @@ int vr_group_render_progressive(vr_group* g, vr_algo algo, uint32_t frames) {
     if (rc != VR_OK) return rc;
     if (frames == 0) return gfail(g, VR_E_ARG, "vr_group_render_progressive: frames must be >= 1");
     const uint32_t n = g->n;
+    g->progressive_result = n > 1;  // from here on (also after a failure below) the GPUs' accumulators are out of step
     rc = on_all(g, [=](uint32_t i) {
         vr_ctx* c = g->ctx[i];
         int r = vr_set_frame_color_peers(c, nullptr, nullptr, 0);
