@@ -270,6 +270,9 @@ def main():
                     help="evaluation kernel for point/ray lists: 8 = ray-segment kernel (default), 2 = exact packed kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target duration of the cpu_baseline sample")
+    ap.add_argument("--configs", default="all",
+                    help="N=1: the other BASELINE.json configurations measured after the headline and reported in the line's `configs` "
+                         "array (bench_configs.py): all | none | comma-separated subset of C1,C3,C4A,C5S,C5P")
     args = ap.parse_args()
     cfg = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))
@@ -644,6 +647,14 @@ def main():
             "multi_gpu_image_equals_single_gpu": verified,
             "contributions_per_frame": ceff_total / args.steps,
         }
+        if world == 1 and args.configs != "none" and args.workload == "C2":
+            # the other BASELINE.json configurations (C1, C3, C4-A over all 64 frames, C5 sphere and path), each with its own
+            # device time, roofline entry, CPU port on a pixel stride, end-to-end figure and parity against the oracle; the
+            # headline keys above stay what they were (C2), so lines compare across rounds
+            import bench_configs
+            r.close()
+            names = bench_configs.ORDER if args.configs == "all" else [n for n in args.configs.split(",") if n]
+            line["configs"] = bench_configs.run_all(vr, names, log, ffma_tflops=peak_fma, mufu_rcp_tops=peak_rcp, hbm_gbs=hbm_peak)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
