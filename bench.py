@@ -655,7 +655,25 @@ def main():
             r.close()
             names = bench_configs.ORDER if args.configs == "all" else [n for n in args.configs.split(",") if n]
             line["configs"] = bench_configs.run_all(vr, names, log, ffma_tflops=peak_fma, mufu_rcp_tops=peak_rcp, hbm_gbs=hbm_peak)
+        if world > 1 and args.configs != "none" and args.workload == "C2":
+            # N > 1: C3 and C5 sphere as row bands, C5 path sample-parallel with its reduce over NVLink, on all GPUs of the node
+            # through the C++ multi-GPU host (vr_group_*) from this process; the other ranks wait at the barrier below
+            import bench_configs
+            names = bench_configs.GROUP_ORDER if args.configs == "all" else [n for n in args.configs.split(",") if n in bench_configs.GROUP_ORDER]
+            line["configs"] = bench_configs.run_group(vr, world, names, log)
         print(json.dumps(line), flush=True)
+    if world > 1 and args.configs != "none" and args.workload == "C2":
+        # the other ranks wait for rank 0's vr_group runs on the rendezvous store, not inside an NCCL barrier: a spinning NCCL
+        # kernel would hold SMs of the very GPUs rank 0 is driving
+        try:
+            from datetime import timedelta
+            store = dist.distributed_c10d._get_default_store()
+            if rank == 0:
+                store.set("vr_bench_configs_done", "1")
+            else:
+                store.wait(["vr_bench_configs_done"], timedelta(minutes=30))
+        except Exception as e:  # noqa: BLE001
+            log(f"rank {rank}: store wait unavailable ({type(e).__name__}: {e}); falling back to the NCCL barrier")
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

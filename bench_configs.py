@@ -272,3 +272,135 @@ def run_all(vr, names, log, ffma_tflops=None, mufu_rcp_tops=None, hbm_gbs=None):
         log(f"[configs] {name}: " + (res.get("error") or f"{res['ms_per_step']:.3f} ms/step, parity {res['parity']}") + f" ({res['wall_s']} s)")
     r.close()
     return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# N > 1: the same configurations on all GPUs of the node through libvr's C++ multi-GPU host (vr_group_*: one process, one
+# context and worker thread per GPU, peer access over NVLink). bench.py's rank 0 calls this after the headline; the other
+# ranks wait at a barrier with their GPUs idle.
+#   bands        C3 and C5 sphere as row bands balanced by measured feedback (vr_group_balance), timed on the devices
+#                (vr_group_time_frames: CUDA events on every GPU's stream, maximum over the GPUs)
+#   progressive  C5 path sample-parallel (vr_group_render_progressive): frame f on GPU f mod N, float sums, one reduce over
+#                NVLink (peer reads on GPU 0), division
+# Each entry also renders the same frames on ONE GPU in this run (device-timed), for the bit-equality check of the bands
+# (or the reassociation bound of the sums) and as the in-run single-GPU time the multi-GPU time is divided into.
+GROUP_ORDER = ["C3", "C5S", "C5P"]
+
+
+def _configure(x, c, grid):
+    x.set_grid(grid)
+    x.resize(c["W"], c["H"])
+    x.set_max_lights_capacity(max(87500, c["ml"]))
+    x.ubo = x.default_ubo()
+    x.update_ubo(maxLights=c["ml"])
+    x.set_light_gen_groups(c["gx"], 1, 1)
+
+
+def run_group_entry(name, vr, g, r1, ndev, grids, log):
+    c = CONFIGS[name]
+    n, W, H, algo, K = c["n"], c["W"], c["H"], c["algo"], c["steps"]
+    if n not in grids:
+        t0 = time.perf_counter()
+        grids.clear()
+        grids[n] = vr.build_cloud_grid(n)
+        log(f"[{name}] cloud {n}^3: {grids[n].nbytes / 1e6:.1f} MB built in {time.perf_counter() - t0:.1f} s")
+    grid = grids[n]
+    _configure(g, c, grid)
+    _configure(r1, c, grid)
+    progressive = algo == "path"
+    frames = 2 * ndev if progressive else K
+
+    # ---- one GPU, the same frames (device-timed)
+    for _ in range(2):
+        r1.draw_frame(algo)
+    r1.sync()
+    r1.reset_accumulation()
+    units = 0
+    r1.timer_start()
+    for _ in range(frames):
+        r1.draw_frame(algo)
+        k = r1.counters()
+        units += k["S_eff"] * (k["light_count"] if algo != "path" else 1)
+    one_ms = r1.timer_stop() / frames
+    a1, i1 = r1.read_accum(), r1.read_image_rgba8()
+
+    out = {"name": name, "workload": c["desc"], "n_gpus": ndev, "steps": frames,
+           "metric": "light_pixel_contributions_per_s" if algo != "path" else "path_samples_per_s",
+           "unit": "contributions/s" if algo != "path" else "non-zero-density camera samples/s",
+           "host": "vr_group_* (csrc/vr_group.cu): one process, one context + worker thread per GPU, CUDA peer access",
+           "single_gpu_ms_per_step_same_run": one_ms}
+    if not progressive:
+        bands = g.balance(algo, 4)
+        g.time_frames(algo, 1)                       # first frames of the final split size buffers: not measured
+        ms, per = g.time_frames(algo, K)
+        g.reset_accumulation()
+        for _ in range(frames):
+            g.draw_frame(algo)
+        g.sync()
+        a, i = g.read_accum(), g.read_image_rgba8()
+        equal = bool(np.array_equal(a, a1) and np.array_equal(i, i1))
+        # end to end: volume host -> first GPU -> NVLink replication, frame, every GPU returns its rows to one host image
+        Ke = c["e2e_steps"]
+        g.reset_accumulation()
+        g.set_grid(grid)
+        g.draw_frame(algo)
+        g.read_accum()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            g.set_grid(grid)
+            g.draw_frame(algo)
+            g.read_accum()
+        e2e_s = (time.perf_counter() - t0) / Ke
+        out.update({"partition": "row bands balanced by measured per-GPU time (vr_group_balance, 4 rounds); no exchange: every GPU keeps its band",
+                    "bands": bands, "ms_per_step": ms, "per_gpu_ms_per_step": per, "value": units / frames / (ms * 1e-3),
+                    "timing": "CUDA events on every GPU's stream, maximum over the GPUs (vr_group_time_frames)",
+                    "speedup_vs_single_gpu_same_run": one_ms / ms, "scaling": "strong",
+                    "e2e": {"value": units / frames / e2e_s, "ms_per_step": e2e_s * 1e3, "steps": Ke, "timing": "host wall clock, blocking read-back every step",
+                            "h2d_bytes_per_step": int(grid.nbytes) + 96 * ndev, "d2h_bytes_per_step": W * H * 16,
+                            "nvlink_replication_bytes_per_step": int(grid.nbytes) * (ndev - 1)},
+                    "parity": {"multi_gpu_image_equals_single_gpu": equal, "frames": frames, "compared": "float accumulator and rgba8 image, bit for bit",
+                               "ok": equal}})
+    else:
+        g.render_progressive(algo, ndev)             # warm-up: buffers on every GPU
+        t0 = time.perf_counter()
+        g.render_progressive(algo, frames)           # returns when GPU 0 holds the finished average
+        wall_s = time.perf_counter() - t0
+        a = g.read_accum()                           # (from GPU 0: the group routes read-backs there after a progressive run)
+        rel, rmse = rel_err(a[..., 0], a1[..., 0])
+        bound = frames * 2.0 ** -22
+        g.reset_accumulation()
+        out.update({"partition": f"sample-parallel: frame f on GPU f mod {ndev}, whole images, float sums; reduce = GPU 0 adds the other GPUs' "
+                                 "accumulators in GPU order with peer reads over NVLink (k_add_accum), one division",
+                    "ms_per_step": wall_s * 1e3 / frames, "value": units / wall_s,
+                    "timing": "host wall clock around the blocking vr_group_render_progressive call (rendering on all GPUs + reduce + division); "
+                              "the call spans N streams and a cross-GPU reduce, so no single stream's events cover it",
+                    "speedup_vs_single_gpu_same_run": one_ms * frames / (wall_s * 1e3), "scaling": "strong (frames of one accumulation split over the GPUs)",
+                    "nvlink_reduce_bytes": (ndev - 1) * W * H * 16,
+                    "parity": {"max_rel_vs_sequential_average": rel, "rmse": rmse, "bound": bound, "frames": frames,
+                               "compared": "float average against the one-GPU sequential running average of the same frames (equal up to float reassociation)",
+                               "ok": bool(rel <= bound)}})
+    return out
+
+
+def run_group(vr, ndev, names, log):
+    out = []
+    g = r1 = None
+    try:
+        g = vr.RendererGroup(list(range(ndev)))
+        r1 = vr.VolumeRenderer(0)
+    except Exception as e:  # noqa: BLE001
+        return [{"name": "group", "error": f"{type(e).__name__}: {e}"}]
+    grids = {}
+    for name in names:
+        t0 = time.perf_counter()
+        try:
+            res = run_group_entry(name, vr, g, r1, ndev, grids, log)
+        except Exception as e:  # noqa: BLE001
+            res = {"name": name, "error": f"{type(e).__name__}: {e}"}
+        res["wall_s"] = round(time.perf_counter() - t0, 2)
+        out.append(res)
+        log(f"[configs x{ndev}] {name}: " + (res.get("error") or f"{res['ms_per_step']:.3f} ms/step, {res['speedup_vs_single_gpu_same_run']:.2f}x of one GPU "
+                                            f"({res['single_gpu_ms_per_step_same_run']:.3f} ms), parity {res['parity']}") + f" ({res['wall_s']} s)")
+    r1.close()
+    g.close()
+    return out
