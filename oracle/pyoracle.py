@@ -111,8 +111,12 @@ class Oracle:
         return out
 
     def builtin(self, name, xs):
-        f = getattr(self.lib, "vro_" + name)
-        return np.array([f(float(x)) for x in xs], np.float32)
+        xs = np.ascontiguousarray(xs, np.float32)
+        out = np.empty(xs.shape, np.float32)
+        self.lib.vro_builtin_array.argtypes = [C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]
+        rc = self.lib.vro_builtin_array(("exp", "sin", "cos", "acos", "tan").index(name), _ptr(xs), xs.size, _ptr(out))
+        assert rc == 0
+        return out
 
     def grid_info(self, grid):
         bmin = np.zeros(3, np.int32)

@@ -509,6 +509,15 @@ float vro_sin(float x) { return vr_sin(x); }
 float vro_cos(float x) { return vr_cos(x); }
 float vro_acos(float x) { return vr_acos(x); }
 float vro_tan(float x) { return vr_tan(x); }
+// the same built-ins over an array (exhaustive sweeps in tests/test_builtins.py): which = 0 exp, 1 sin, 2 cos, 3 acos, 4 tan
+int vro_builtin_array(int which, const float* in, uint64_t n, float* out) {
+    if (which < 0 || which > 4) return 1;
+    for (uint64_t i = 0; i < n; i++) {
+        const float x = in[i];
+        out[i] = which == 0 ? vr_exp(x) : which == 1 ? vr_sin(x) : which == 2 ? vr_cos(x) : which == 3 ? vr_acos(x) : vr_tan(x);
+    }
+    return 0;
+}
 
 int vro_grid_info(const void* grid, uint64_t size, int32_t bbox_min[3], int32_t bbox_max[3], float* background,
                   uint32_t node_counts[3], uint32_t* root_tiles) {

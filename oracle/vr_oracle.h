@@ -64,6 +64,7 @@ float vro_sin(float x);
 float vro_cos(float x);
 float vro_acos(float x);
 float vro_tan(float x);
+int vro_builtin_array(int which, const float* in, uint64_t n, float* out);
 
 /* grid header facts: returns 0 if the buffer looks like a float NanoVDB grid */
 int vro_grid_info(const void* grid, uint64_t size, int32_t bbox_min[3], int32_t bbox_max[3], float* background,

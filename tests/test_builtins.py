@@ -67,3 +67,46 @@ def test_random_dir_is_unit(oracle):
         assert abs(np.linalg.norm(d) - 1.0) < 1e-6
     # r1 = 1.0 is a legal roll (randf can return 1.0): theta = acos(-1) = pi
     assert np.isfinite(oracle.random_dir(1.0, 1.0)).all()
+
+
+# ---- exhaustive sweeps where the hot path lives. The kernels, the oracle and the oracle/_ref shim share vr_glsl_math.h, so
+# the bit-exact parity tests cannot see an error in it; these sweeps are its own guard: EVERY float of the range, against
+# double-precision libm.
+def _floats_between(lo, hi, step=1):
+    """every step-th positive float32 from lo to hi inclusive, in chunks of 2^24 bit patterns"""
+    a = int(np.float32(lo).view(np.uint32))
+    b = int(np.float32(hi).view(np.uint32))
+    for start in range(a, b + 1, (1 << 24) * step):
+        yield np.arange(start, min(b + 1, start + (1 << 24) * step), step, dtype=np.uint32).view(np.float32)
+
+
+def test_exp_every_float_of_the_attenuation_range(oracle):
+    """exp(-val * sigma * step) (light_gen.comp:66, point_compute_color.comp:80): arguments in [-0.06, 0] for the UBO
+    defaults (sigma 0.05, step 1, densities up to ~1). Every float in [-0.06, -2^-30], then every 64th down to -2^-60
+    (there exp rounds to 1 or 1 - 2^-24 and nothing can go wrong slowly)."""
+    worst = 0.0
+    for xs in _floats_between(2.0 ** -30, 0.06):
+        x = -xs
+        worst = max(worst, float(_ulps(oracle.builtin("exp", x), np.exp(x.astype(np.float64))).max()))
+    for xs in _floats_between(2.0 ** -60, 2.0 ** -30, 64):
+        x = -xs
+        worst = max(worst, float(_ulps(oracle.builtin("exp", x), np.exp(x.astype(np.float64))).max()))
+    assert worst <= 1.0, worst
+
+
+def test_acos_every_float_near_one_and_sin_cos_on_the_circle(oracle):
+    """randomDir (common_functions.h:24-33): theta = acos(1 - 2 r1), phi = 2 pi r2, then sin/cos of both. acos is
+    ill-conditioned near +-1: every float with 0.5 <= |x| <= 1, every 64th below. sin/cos: every float in [2^-12, 2 pi],
+    every 256th below. Absolute bounds, the ones the sparse sweeps above use."""
+    worst = 0.0
+    for sign in (1.0, -1.0):
+        for xs in list(_floats_between(0.5, 1.0)) + list(_floats_between(2.0 ** -30, 0.5, 64)):
+            x = (xs * np.float32(sign)).astype(np.float32)
+            worst = max(worst, float(np.abs(oracle.builtin("acos", x) - np.arccos(x.astype(np.float64))).max()))
+    assert worst <= 5e-7, worst
+    ws = wc = 0.0
+    for xs in list(_floats_between(2.0 ** -12, 2.0 * np.pi)) + list(_floats_between(2.0 ** -40, 2.0 ** -12, 256)):
+        x64 = xs.astype(np.float64)
+        ws = max(ws, float(np.abs(oracle.builtin("sin", xs) - np.sin(x64)).max()))
+        wc = max(wc, float(np.abs(oracle.builtin("cos", xs) - np.cos(x64)).max()))
+    assert ws <= 1.5e-7 and wc <= 1.5e-7, (ws, wc)
