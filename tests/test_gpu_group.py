@@ -115,6 +115,45 @@ def test_group_sample_parallel_progressive(vr, cloud):
         assert np.array_equal(g.read_accum(), one)
 
 
+@pytest.mark.parametrize("exchange", ["none", "allgather"])
+def test_group_on_distinct_gpus(vr, cloud, exchange):
+    """The same checks with every context on its OWN physical GPU (skipped on a one-GPU box, where the tests above list the
+    device several times): CUDA peer access, k_peer_barrier's flags and the resolve kernel's peer stores cross NVLink, the
+    volume is replicated GPU to GPU, the progressive reduce reads the peers' accumulators."""
+    nd = _ndev()
+    if nd < 2:
+        pytest.skip("needs at least two GPUs")
+    n = min(nd, 4)
+    grid = cloud(64)
+    W, H, frames = 160, 96, 4
+    want_a, want_i = _single(vr, grid, W, H, "point", frames, maxLights=90)
+    with vr.RendererGroup(list(range(n))) as g:
+        g.set_grid(grid)
+        g.resize(W, H)
+        g.ubo = g.default_ubo()
+        g.update_ubo(maxLights=90)
+        g.set_light_gen_groups(6, 1, 1)
+        g.set_exchange(exchange)
+        g.balance("point", rounds=2)
+        for _ in range(frames):
+            g.draw_frame("point")
+        g.sync()
+        assert np.array_equal(g.read_accum(), want_a)
+        assert np.array_equal(g.read_image_rgba8(), want_i)
+        if exchange == "allgather":   # every GPU holds the whole image after the barrier
+            L = vr.load()
+            out = np.zeros((H, W, 4), np.float32)
+            for i in range(n):
+                assert L.vr_read_accum_f32(g.ctx(i), out.ctypes.data_as(C.c_void_p)) == 0
+                assert np.array_equal(out, want_a), i
+        # sample-parallel progressive run: reduce over NVLink on GPU 0, read back through the group
+        pframes = 3 * n
+        seq_a, _ = _single(vr, grid, W, H, "point", pframes, maxLights=90)
+        g.render_progressive("point", pframes)
+        rel, _ = rel_err(g.read_accum()[..., 0], seq_a[..., 0])
+        assert rel <= pframes * 2.0 ** -22, rel
+
+
 def test_group_argument_errors(vr, cloud):
     with pytest.raises(vr.VrError):
         vr.RendererGroup([99])

@@ -222,6 +222,10 @@ __device__ __forceinline__ bool vr_intersect_aabb(vr_f3 o, vr_f3 d, const VrGrid
 }
 
 // camera ray in index space, shaders/point_compute_color.comp:23-58 (same text in sphere/ray/beam/path)
+// The reference camera has a position and a field of view only: it looks down +z, unrotated (:23-33), and the UBO has no
+// field that could say otherwise. Code that inverts this projection (k_flag_near_segments maps a light's ball back to a
+// pixel box) states its dependence on this constant, so that giving the camera an orientation cannot leave it behind.
+#define VR_CAMERA_UNROTATED_PLUS_Z 1
 struct VrCamRay {
     vr_f3 o, d;
     float tmin, tmax;

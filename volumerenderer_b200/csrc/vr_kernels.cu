@@ -931,6 +931,9 @@ __global__ void __launch_bounds__(256) k_build_segments(const uint32_t* __restri
 // depth, the box then covers the tile in that direction and the exact per-pixel test decides. Only an absurdly distant
 // light makes the kernel give up and flag everything (flag_all). Flags are what k_eval_seg reads to hand a segment to
 // the exact kernel.
+#if !VR_CAMERA_UNROTATED_PLUS_Z
+#error "k_flag_near_segments inverts vr_camera_ray's unrotated +z projection: rework its pixel box before changing the camera"
+#endif
 __global__ void __launch_bounds__(128) k_flag_near_segments(const VrEvalLight* __restrict__ lights, const unsigned long long* __restrict__ nlights_dev,
                                                             vr_ubo u, float tan_scale, vr_tile tile, const uint32_t* __restrict__ counts,
                                                             const unsigned long long* __restrict__ offsets,
